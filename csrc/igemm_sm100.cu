@@ -1,0 +1,555 @@
+// Implicit-GEMM convolution kernels for sm_100a: tcgen05.mma with TMEM accumulators, the dense
+// operand staged by TMA, the strided / parity-decomposed im2col operand gathered straight into the
+// 128B-swizzled UMMA smem layout by the producer warps.
+//
+// One kernel template, three modes (geometry is TensorFlow's 5x5 / stride 2 / SAME, i.e. one pixel
+// of padding before and two after -- SURVEY.md 2.4a/b):
+//
+//   MODE_F  "forward-strided":  out[n,oh,ow,:] = sum_{kh,kw} x[n,2oh+kh-1,2ow+kw-1,:] . W[kh,kw]
+//           = tf.nn.conv2d(.., strides 2, SAME)           (reference distriubted_model.py:183)
+//           = data-gradient of conv2d_transpose            (backward of distriubted_model.py:200)
+//   MODE_T  "transposed":       out[n,2q+p,:] = sum_{taps of parity p} x[n,q+(p+1-k)/2,:] . W[kh,kw]
+//           = tf.nn.conv2d_transpose(.., strides 2)        (reference distriubted_model.py:200)
+//           = data-gradient of conv2d                      (backward of distriubted_model.py:183)
+//           blockIdx.z enumerates the 4 output parity classes (3x3, 3x2, 2x3, 2x2 taps).
+//   MODE_W  "weight-gradient":  dW[tap][cg][cd] += sum_pixels G[n,2q+k-1,cg] * D[n,q,cd]
+//           (autodiff of both layer kinds, image_train.py:109-112); K = pixels, both operands
+//           MN-major, split-K over pixel ranges with f32 red.global.add.
+//
+// GEMM view (BLOCK_M = 128, BLOCK_K = 64 bf16 = one 128-byte swizzle row):
+//   F/T : M = pixels (gathered A, K-major), N = out channels (TMA B, K-major), K = taps*Cin
+//   W   : M = dense channels (TMA A, MN-major), N = gathered channels (B, MN-major), K = pixels
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer (one lane),
+// warps 2-5 = im2col gather producers, then the epilogue (one TMEM lane quadrant each).
+#include <mutex>
+#include <unordered_map>
+#include <vector>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+#include "../include/dcgan_b200.h"
+
+namespace dcgan {
+
+enum { MODE_F = 0, MODE_T = 1, MODE_W = 2 };
+
+struct IgemmParams {
+  const __nv_bfloat16* g;  // gathered tensor, NHWC bf16
+  int gH, gW, gC;          // gathered tensor spatial dims / channels
+  int rH_log2, rW_log2;    // row (pixel) space spatial dims, powers of two
+  int rows_total;          // NB * rH * rW
+  int Cn;                  // F/T: output channels.  W: gathered channels (GEMM N extent)
+  int Cd;                  // W: dense channels (GEMM M extent)
+  int num_kb;              // k-blocks per CTA (W: per split)
+  // epilogue
+  void* out;               // F/T: bf16 NHWC.  W: f32 [25][Cn][Cd]
+  const float* bias;       // F/T optional, per out channel
+  int act;                 // F/T activation
+  int oH, oW;              // F/T output spatial dims
+  int* err_flag;           // sticky device error flag (csrc/runtime.cu)
+  const int* mn_variant;   // MN-major descriptor convention switch (bring-up harness only)
+};
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;
+constexpr int kATileBytes = kBlockM * kBlockK * 2;  // 16 KiB
+constexpr int kNumGatherThreads = 128;
+constexpr int kNumThreads = 192;
+
+template <int BLOCK_N, int STAGES>
+struct SmemLayout {
+  static constexpr int kBTileBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+  static constexpr int kBarOffset = STAGES * kStageBytes;
+  static constexpr int kTotal = kBarOffset + 256 + 1024;  // + barriers + alignment slack
+};
+
+// 16-byte chunk (row, chunk) of a [rows][128 B] tile in the SWIZZLE_128B pattern
+__device__ __forceinline__ uint32_t swz128(uint32_t row, uint32_t chunk) {
+  return row * 128u + ((chunk ^ (row & 7u)) << 4);
+}
+
+__device__ __forceinline__ uint4 ldg16(const void* p) {
+  return __ldg(reinterpret_cast<const uint4*>(p));
+}
+
+template <int MODE, int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kNumThreads, 1)
+igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
+  using L = SmemLayout<BLOCK_N, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+
+  // ---- tile coordinates -----------------------------------------------------------------------
+  int m0, n0, tap_fixed = 0, ph = 0, pw = 0, kb_base = 0;
+  if (MODE == MODE_W) {
+    tap_fixed = blockIdx.x;
+    const int n_tiles = p.Cn / BLOCK_N;
+    m0 = (blockIdx.y / n_tiles) * kBlockM;   // dense channel tile
+    n0 = (blockIdx.y % n_tiles) * BLOCK_N;   // gathered channel tile
+    kb_base = blockIdx.z * p.num_kb;
+  } else {
+    m0 = blockIdx.x * kBlockM;  // pixel tile
+    n0 = blockIdx.y * BLOCK_N;  // out channel tile
+    if (MODE == MODE_T) { ph = blockIdx.z >> 1; pw = blockIdx.z & 1; }
+  }
+  const int num_kb = (MODE == MODE_T) ? ((ph ? 3 : 2) * (pw ? 3 : 2) * (p.gC / kBlockK)) : p.num_kb;
+
+  // ---- one-time setup -------------------------------------------------------------------------
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], kNumGatherThreads + 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    *abort_flag = 0;
+    fence_mbar_init();
+    tma_prefetch_desc(&tmap);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr_smem, BLOCK_N);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // =================================== TMA producer ==========================================
+    if (lane == 0) {
+      const int cpt = p.gC / kBlockK;  // F/T: channel chunks per tap
+      const int nkw = pw ? 3 : 2;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % STAGES;
+        const uint32_t phase = (kb / STAGES) & 1;
+        if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) break;
+        uint8_t* sA = smem + s * L::kStageBytes;
+        uint8_t* sB = sA + kATileBytes;
+        if (MODE == MODE_W) {
+          mbar_arrive_expect_tx(&full_bar[s], kATileBytes);
+          const int px0 = (kb_base + kb) * kBlockK;
+          tma_load_2d(sA, &tmap, &full_bar[s], m0, px0);
+          tma_load_2d(sA + kATileBytes / 2, &tmap, &full_bar[s], m0 + 64, px0);
+        } else {
+          int tap;
+          const int lt = kb / cpt;
+          const int c0 = (kb - lt * cpt) * kBlockK;
+          if (MODE == MODE_F) {
+            tap = lt;
+          } else {
+            const int ikh = lt / nkw, ikw = lt - ikh * nkw;
+            const int kh = ph ? 2 * ikh : 2 * ikh + 1;
+            const int kw = pw ? 2 * ikw : 2 * ikw + 1;
+            tap = kh * 5 + kw;
+          }
+          mbar_arrive_expect_tx(&full_bar[s], L::kBTileBytes);
+          tma_load_2d(sB, &tmap, &full_bar[s], c0, tap * p.Cn + n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // =================================== MMA issuer ============================================
+    if (lane == 0) {
+      constexpr bool kMN = (MODE == MODE_W);
+      constexpr uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, kMN, kMN);
+      const bool swap = kMN && (*p.mn_variant != 0);
+      const uint32_t lbo = kMN ? (swap ? 1024u : 8192u) : 16u;
+      const uint32_t sbo = kMN ? (swap ? 8192u : 1024u) : 1024u;
+      const uint32_t kstep = kMN ? 2048u : 32u;  // bytes per UMMA_K=16 step
+      bool ok = true;
+      for (int kb = 0; kb < num_kb && ok; ++kb) {
+        const int s = kb % STAGES;
+        const uint32_t phase = (kb / STAGES) & 1;
+        ok = mbar_wait(&full_bar[s], phase, abort_flag, p.err_flag);
+        if (!ok) break;
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
+        const uint32_t b_addr = a_addr + kATileBytes;
+#pragma unroll
+        for (int k = 0; k < kBlockK / 16; ++k) {
+          const uint64_t da = make_smem_desc_sw128(a_addr + k * kstep, lbo, sbo);
+          const uint64_t db = make_smem_desc_sw128(b_addr + k * kstep, lbo, sbo);
+          umma_bf16(tmem_base, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs retire
+      }
+      umma_commit(tmem_full_bar);  // accumulator complete
+    }
+  } else {
+    // ============================ gather producers, then epilogue ==============================
+    const int gt = tid - 64;       // 0..127
+    const int chunk = gt & 7;      // 16-byte chunk inside the 128-byte row
+    const int rbase = gt >> 3;     // 0..15
+    const int rW = 1 << p.rW_log2, rH = 1 << p.rH_log2;
+    const int stride = (MODE == MODE_T) ? 1 : 2;
+    bool ok = true;
+
+    if (MODE != MODE_W) {
+      // rows are fixed per thread: decode (n, qh, qw) once
+      int pix_base[8];  // n * gH * gW, or -1 when the row is past the end
+      int yx[8];        // (stride*qh) << 16 | (stride*qw)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int R = m0 + rbase + 16 * i;
+        if (R < p.rows_total) {
+          const int qw = R & (rW - 1);
+          const int qh = (R >> p.rW_log2) & (rH - 1);
+          const int n = R >> (p.rW_log2 + p.rH_log2);
+          pix_base[i] = n * p.gH * p.gW;
+          yx[i] = ((stride * qh) << 16) | (stride * qw);
+        } else {
+          pix_base[i] = -1;
+          yx[i] = 0;
+        }
+      }
+      const int cpt = p.gC / kBlockK;
+      const int nkw = pw ? 3 : 2;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % STAGES;
+        const uint32_t phase = (kb / STAGES) & 1;
+        const int lt = kb / cpt;
+        const int c0 = (kb - lt * cpt) * kBlockK;
+        int dy, dx;
+        if (MODE == MODE_F) {
+          const int kh = lt / 5, kw = lt - kh * 5;
+          dy = kh - 1;
+          dx = kw - 1;
+        } else {
+          const int ikh = lt / nkw, ikw = lt - ikh * nkw;
+          const int kh = ph ? 2 * ikh : 2 * ikh + 1;
+          const int kw = pw ? 2 * ikw : 2 * ikw + 1;
+          dy = (ph + 1 - kh) / 2;  // exact: the numerator is even by construction
+          dx = (pw + 1 - kw) / 2;
+        }
+        uint4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int y = (yx[i] >> 16) + dy;
+          const int x = (yx[i] & 0xffff) + dx;
+          const bool valid = pix_base[i] >= 0 && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW;
+          v[i] = make_uint4(0, 0, 0, 0);
+          if (valid) {
+            const size_t off = ((size_t)(pix_base[i] + y * p.gW + x)) * p.gC + c0 + chunk * 8;
+            v[i] = ldg16(p.g + off);
+          }
+        }
+        if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+        uint8_t* sA = smem + s * L::kStageBytes;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<uint4*>(sA + swz128(rbase + 16 * i, chunk)) = v[i];
+        fence_proxy_async_smem();
+        mbar_arrive(&full_bar[s]);
+      }
+    } else {
+      // W mode: rows are pixels of the K dimension and change every k-block
+      const int kh = tap_fixed / 5, kw = tap_fixed - kh * 5;
+      constexpr int kSub = BLOCK_N / 64;  // 64-channel sub-tiles of the gathered operand
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % STAGES;
+        const uint32_t phase = (kb / STAGES) & 1;
+        const int px0 = (kb_base + kb) * kBlockK;
+        uint4 v[4 * kSub];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int R = px0 + rbase + 16 * i;
+          const int qw = R & (rW - 1);
+          const int qh = (R >> p.rW_log2) & (rH - 1);
+          const int n = R >> (p.rW_log2 + p.rH_log2);
+          const int y = 2 * qh + kh - 1, x = 2 * qw + kw - 1;
+          const bool valid = R < p.rows_total && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW;
+          const size_t off = ((size_t)((n * p.gH + y) * p.gW + x)) * p.gC + n0 + chunk * 8;
+#pragma unroll
+          for (int j = 0; j < kSub; ++j) {
+            v[i * kSub + j] = make_uint4(0, 0, 0, 0);
+            if (valid) v[i * kSub + j] = ldg16(p.g + off + 64 * j);
+          }
+        }
+        if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+        uint8_t* sB = smem + s * L::kStageBytes + kATileBytes;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < kSub; ++j)
+            *reinterpret_cast<uint4*>(sB + j * 8192 + swz128(rbase + 16 * i, chunk)) = v[i * kSub + j];
+        fence_proxy_async_smem();
+        mbar_arrive(&full_bar[s]);
+      }
+    }
+
+    // ------------------------------------ epilogue ----------------------------------------------
+    if (ok) ok = mbar_wait(tmem_full_bar, 0, abort_flag, p.err_flag);
+    tc_fence_after();
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    const int row_in_tile = q * 32 + lane;
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    if (MODE != MODE_W) {
+      const int R = m0 + row_in_tile;
+      const bool valid = ok && R < p.rows_total;
+      __nv_bfloat16* orow = nullptr;
+      if (valid) {
+        const int qw = R & (rW - 1);
+        const int qh = (R >> p.rW_log2) & (rH - 1);
+        const int n = R >> (p.rW_log2 + p.rH_log2);
+        int oh, ow;
+        if (MODE == MODE_F) { oh = qh; ow = qw; } else { oh = 2 * qh + ph; ow = 2 * qw + pw; }
+        orow = reinterpret_cast<__nv_bfloat16*>(p.out) + ((size_t)((n * p.oH + oh) * p.oW + ow)) * p.Cn + n0;
+      }
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + c, v);
+        tmem_ld_wait();
+        if (valid) {
+          uint32_t packed[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            float a = __uint_as_float(v[2 * j]), b = __uint_as_float(v[2 * j + 1]);
+            if (p.bias != nullptr) {
+              a += __ldg(p.bias + n0 + c + 2 * j);
+              b += __ldg(p.bias + n0 + c + 2 * j + 1);
+            }
+            a = apply_act(a, p.act);
+            b = apply_act(b, p.act);
+            packed[j] = pack_bf16x2(a, b);
+          }
+          uint4* dst = reinterpret_cast<uint4*>(orow + c);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+        }
+      }
+    } else {
+      float* obase = reinterpret_cast<float*>(p.out) + (size_t)tap_fixed * p.Cn * p.Cd + (m0 + row_in_tile);
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + c, v);
+        tmem_ld_wait();
+        if (ok) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            atomicAdd(obase + (size_t)(n0 + c + j) * p.Cd, __uint_as_float(v[j]));
+        }
+      }
+    }
+  }
+
+  // ---- teardown ---------------------------------------------------------------------------------
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, BLOCK_N);
+}
+
+// =================================================================================================
+// host side
+// =================================================================================================
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr;
+  uint64_t cols, rows;
+  uint32_t box_c, box_r;
+  bool operator==(const MapKey& o) const {
+    return ptr == o.ptr && cols == o.cols && rows == o.rows && box_c == o.box_c && box_r == o.box_r;
+  }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    size_t h = std::hash<const void*>()(k.ptr);
+    h = h * 1000003u ^ std::hash<uint64_t>()(k.cols * 1315423911u + k.rows);
+    h = h * 1000003u ^ (k.box_c * 257u + k.box_r);
+    return h;
+  }
+};
+
+// 2-D row-major bf16 tensor [rows][cols], box [box_r][box_c], SWIZZLE_128B.  Cached per
+// (pointer, shape): encoding costs a driver call and the buffers of the engine are static.
+static int get_tmap_2d(const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_r, uint32_t box_c,
+                       CUtensorMap* out) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  MapKey key{ptr, cols, rows, box_c, box_r};
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) { *out = it->second; return 0; }
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return DCGAN_ERR_DRIVER;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {box_c, box_r};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return DCGAN_ERR_DRIVER;
+  cache.emplace(key, m);
+  *out = m;
+  return 0;
+}
+
+static int ilog2_exact(int v) {
+  int l = 0;
+  while ((1 << l) < v) ++l;
+  return ((1 << l) == v) ? l : -1;
+}
+
+template <int MODE, int BLOCK_N, int STAGES>
+static int launch(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cudaStream_t stream) {
+  using L = SmemLayout<BLOCK_N, STAGES>;
+  auto kern = igemm_kernel<MODE, BLOCK_N, STAGES>;
+  static bool attr_done = false;  // per instantiation
+  if (!attr_done) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal) != cudaSuccess)
+      return DCGAN_ERR_LAUNCH;
+    attr_done = true;
+  }
+  kern<<<grid, kNumThreads, L::kTotal, stream>>>(tmap, p);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+template <int MODE>
+static int dispatch_n(int block_n, const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cudaStream_t st) {
+  switch (block_n) {
+    case 64: return launch<MODE, 64, 6>(tmap, p, grid, st);
+    case 128: return launch<MODE, 128, 5>(tmap, p, grid, st);
+    case 256: return launch<MODE, 256, 4>(tmap, p, grid, st);
+    default: return DCGAN_ERR_SHAPE;
+  }
+}
+
+static int pick_block_n(int Cn, int rows_tiles, int extra_parallel) {
+  // prefer the widest tile that still gives at least ~1 wave of CTAs on 148 SMs
+  const int cands[3] = {256, 128, 64};
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cands[i];
+    if (Cn % bn) continue;
+    if ((long)rows_tiles * (Cn / bn) * extra_parallel >= 120 || bn == 64) return bn;
+  }
+  return (Cn % 64 == 0) ? 64 : -1;
+}
+
+}  // namespace dcgan
+
+using namespace dcgan;
+
+extern "C" {
+
+int dcgan_conv_fprop(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
+                     int Cin, int Cout, int act, int block_n, cudaStream_t stream) {
+  if ((H & 1) || (W & 1) || Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
+  const int oH = H / 2, oW = W / 2;
+  const int lh = ilog2_exact(oH), lw = ilog2_exact(oW);
+  if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;
+  IgemmParams p{};
+  p.err_flag = error_flag_ptr();
+  p.mn_variant = mn_variant_ptr();
+  if (!p.err_flag || !p.mn_variant) return DCGAN_ERR_DRIVER;
+  p.g = reinterpret_cast<const __nv_bfloat16*>(x);
+  p.gH = H; p.gW = W; p.gC = Cin;
+  p.rH_log2 = lh; p.rW_log2 = lw;
+  p.rows_total = NB * oH * oW;
+  p.Cn = Cout; p.Cd = 0;
+  p.num_kb = 25 * (Cin / 64);
+  p.out = out; p.bias = bias; p.act = act; p.oH = oH; p.oW = oW;
+  const int mt = (p.rows_total + kBlockM - 1) / kBlockM;
+  if (block_n <= 0) block_n = pick_block_n(Cout, mt, 1);
+  if (block_n < 0 || Cout % block_n) return DCGAN_ERR_SHAPE;
+  CUtensorMap tmap;
+  int rc = get_tmap_2d(w_nk, (uint64_t)25 * Cout, Cin, block_n, 64, &tmap);
+  if (rc) return rc;
+  dim3 grid(mt, Cout / block_n, 1);
+  return dispatch_n<MODE_F>(block_n, tmap, p, grid, stream);
+}
+
+int dcgan_conv_tconv(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
+                     int Cin, int Cout, int act, int block_n, cudaStream_t stream) {
+  if (Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
+  const int lh = ilog2_exact(H), lw = ilog2_exact(W);
+  if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;
+  IgemmParams p{};
+  p.err_flag = error_flag_ptr();
+  p.mn_variant = mn_variant_ptr();
+  if (!p.err_flag || !p.mn_variant) return DCGAN_ERR_DRIVER;
+  p.g = reinterpret_cast<const __nv_bfloat16*>(x);
+  p.gH = H; p.gW = W; p.gC = Cin;
+  p.rH_log2 = lh; p.rW_log2 = lw;
+  p.rows_total = NB * H * W;
+  p.Cn = Cout; p.Cd = 0;
+  p.num_kb = 0;  // per parity class, derived in-kernel
+  p.out = out; p.bias = bias; p.act = act; p.oH = 2 * H; p.oW = 2 * W;
+  const int mt = (p.rows_total + kBlockM - 1) / kBlockM;
+  if (block_n <= 0) block_n = pick_block_n(Cout, mt, 4);
+  if (block_n < 0 || Cout % block_n) return DCGAN_ERR_SHAPE;
+  CUtensorMap tmap;
+  int rc = get_tmap_2d(w_nk, (uint64_t)25 * Cout, Cin, block_n, 64, &tmap);
+  if (rc) return rc;
+  dim3 grid(mt, Cout / block_n, 4);
+  return dispatch_n<MODE_T>(block_n, tmap, p, grid, stream);
+}
+
+int dcgan_conv_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd,
+                     int splits, int block_n, cudaStream_t stream) {
+  if (Cg % 64 || Cd % 128) return DCGAN_ERR_SHAPE;
+  const int lh = ilog2_exact(Hs), lw = ilog2_exact(Ws);
+  if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;
+  const int rows = NB * Hs * Ws;
+  if (rows % kBlockK) return DCGAN_ERR_SHAPE;
+  const int total_kb = rows / kBlockK;
+  if (block_n <= 0) block_n = (Cg % 256 == 0) ? 256 : (Cg % 128 == 0 ? 128 : 64);
+  if (Cg % block_n) return DCGAN_ERR_SHAPE;
+  const int tiles = 25 * (Cd / kBlockM) * (Cg / block_n);
+  if (splits <= 0) {
+    splits = 1;
+    while (tiles * splits < 148 && splits * 2 <= total_kb && total_kb % (splits * 2) == 0 &&
+           total_kb / (splits * 2) >= 4)
+      splits *= 2;
+  }
+  if (total_kb % splits) return DCGAN_ERR_SHAPE;
+  IgemmParams p{};
+  p.err_flag = error_flag_ptr();
+  p.mn_variant = mn_variant_ptr();
+  if (!p.err_flag || !p.mn_variant) return DCGAN_ERR_DRIVER;
+  p.g = reinterpret_cast<const __nv_bfloat16*>(big);
+  p.gH = 2 * Hs; p.gW = 2 * Ws; p.gC = Cg;
+  p.rH_log2 = lh; p.rW_log2 = lw;
+  p.rows_total = rows;
+  p.Cn = Cg; p.Cd = Cd;
+  p.num_kb = total_kb / splits;
+  p.out = dw; p.bias = nullptr; p.act = 0; p.oH = 0; p.oW = 0;
+  CUtensorMap tmap;
+  int rc = get_tmap_2d(small, (uint64_t)rows, Cd, 64, 64, &tmap);
+  if (rc) return rc;
+  dim3 grid(25, (Cd / kBlockM) * (Cg / block_n), splits);
+  return dispatch_n<MODE_W>(block_n, tmap, p, grid, stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,55 @@
+// Library-wide runtime state: the sticky device error flag that bounded waits set instead of
+// hanging, and its host accessors.  No counterpart in the reference (its runtime is TensorFlow's).
+#include <cuda_runtime.h>
+#include "common.cuh"
+#include "../include/dcgan_b200.h"
+
+namespace dcgan {
+
+static __device__ int g_device_error = 0;
+static __device__ int g_mn_desc_variant = 0;
+
+constexpr int kMaxDevices = 64;
+
+int* error_flag_ptr() {
+  static int* ptrs[kMaxDevices] = {nullptr};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, g_device_error) != cudaSuccess) return nullptr;
+    ptrs[dev] = static_cast<int*>(p);
+  }
+  return ptrs[dev];
+}
+
+int* mn_variant_ptr() {
+  static int* ptrs[kMaxDevices] = {nullptr};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, g_mn_desc_variant) != cudaSuccess) return nullptr;
+    ptrs[dev] = static_cast<int*>(p);
+  }
+  return ptrs[dev];
+}
+
+}  // namespace dcgan
+
+extern "C" {
+
+int dcgan_last_device_error(void) {
+  int v = 0;
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  if (cudaMemcpyFromSymbol(&v, dcgan::g_device_error, sizeof(int)) != cudaSuccess) return -1;
+  if (v != 0) {
+    int z = 0;
+    cudaMemcpyToSymbol(dcgan::g_device_error, &z, sizeof(int));
+  }
+  return v;
+}
+
+void dcgan_set_mn_desc_variant(int v) { cudaMemcpyToSymbol(dcgan::g_mn_desc_variant, &v, sizeof(int)); }
+
+}  // extern "C"
