@@ -1,0 +1,372 @@
+// Batch-norm kernels fused with their activations (forward and backward), NHWC bf16 activations.
+//
+// Reference semantics (distriubted_model.py:15-52): per-channel batch moments over N*H*W with
+// *biased* variance, y = gamma*(x-mean)*rsqrt(var+1e-5)+beta, followed by ReLU (generator,
+// :91-105) or LeakyReLU(0.2) (discriminator, :119-121); the moments feed an exponential moving
+// average with decay 0.9 (:41-45) that the sampler consumes (:131-153).
+//
+// "Groups": the discriminator runs on a [real; fake] batch but the reference computes separate
+// statistics for the two calls, so every kernel takes a group count and treats
+// group g = contiguous slab of rows_per_group rows.  The backward kernels take a third slab (the
+// g_loss gradient through D(fake)) that shares the statistics of slab 1 (stat_group map).
+#include "common.cuh"
+#include "../include/dcgan_b200.h"
+
+namespace dcgan {
+
+constexpr int kBnThreads = 256;
+
+// ---------------------------------------------------------------------------------------------
+// forward statistics: sums[g][0][c] += sum x, sums[g][1][c] += sum x^2   (zeroed by the caller)
+// grid = (row_chunks, groups); thread t handles 8 channels (t % (C/8)) of rows t/(C/8)+k*R
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBnThreads)
+bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, int rows_per_group, int C,
+                int rows_per_block) {
+  extern __shared__ float red[];  // [2][C]
+  const int g = blockIdx.y;
+  const int cvec = C >> 3;
+  const int lanes = kBnThreads / cvec;  // rows processed in parallel (C <= 2048)
+  const int cv = threadIdx.x % cvec;
+  const int rl = threadIdx.x / cvec;
+  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) red[i] = 0.f;
+  __syncthreads();
+  float s[8], ss[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(r0 + rows_per_block, rows_per_group);
+  if (rl < lanes) {
+    const __nv_bfloat16* base = x + ((size_t)g * rows_per_group) * C + cv * 8;
+    for (int r = r0 + rl; r < r1; r += lanes) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(base + (size_t)r * C));
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(w[j]);
+        s[2 * j] += f.x; ss[2 * j] += f.x * f.x;
+        s[2 * j + 1] += f.y; ss[2 * j + 1] += f.y * f.y;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&red[cv * 8 + j], s[j]);
+      atomicAdd(&red[C + cv * 8 + j], ss[j]);
+    }
+  }
+  __syncthreads();
+  float* out = sums + (size_t)g * 2 * C;
+  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) atomicAdd(&out[i], red[i]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward apply: finalises the moments, saves (mean, rstd) for backward, updates the EMA shadows
+// (block 0 of each group) and writes y = act(gamma*(x-mean)*rstd + beta) as bf16.
+// use_ema != 0: normalise with the EMA shadows instead (the sampler path, train=False).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBnThreads)
+bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                const float* __restrict__ sums, const float* __restrict__ gamma,
+                const float* __restrict__ beta, float* __restrict__ saved /*[G][2][C]*/,
+                float* __restrict__ ema_mean /*[G][C] or null*/, float* __restrict__ ema_var,
+                int rows_per_group, int C, float inv_count, float eps, float decay, int act, int use_ema,
+                int rows_per_block) {
+  extern __shared__ float ss[];  // scale[C], shift[C]
+  const int g = blockIdx.y;
+  for (int c = threadIdx.x; c < C; c += kBnThreads) {
+    float mean, var;
+    if (use_ema) {
+      mean = ema_mean[(size_t)g * C + c];
+      var = ema_var[(size_t)g * C + c];
+    } else {
+      mean = sums[((size_t)g * 2) * C + c] * inv_count;
+      var = fmaxf(sums[((size_t)g * 2 + 1) * C + c] * inv_count - mean * mean, 0.f);
+    }
+    const float rstd = rsqrtf(var + eps);
+    const float sc = gamma[c] * rstd;
+    ss[c] = sc;
+    ss[C + c] = beta[c] - mean * sc;
+    if (blockIdx.x == 0 && !use_ema) {
+      if (saved) { saved[((size_t)g * 2) * C + c] = mean; saved[((size_t)g * 2 + 1) * C + c] = rstd; }
+      if (ema_mean) {  // shadow -= (1-decay) * (shadow - value)
+        float* em = ema_mean + (size_t)g * C + c;
+        float* ev = ema_var + (size_t)g * C + c;
+        *em -= (1.f - decay) * (*em - mean);
+        *ev -= (1.f - decay) * (*ev - var);
+      }
+    }
+  }
+  __syncthreads();
+  const int cvec = C >> 3;
+  const size_t r0 = (size_t)blockIdx.x * rows_per_block;
+  const size_t r1 = min(r0 + (size_t)rows_per_block, (size_t)rows_per_group);
+  const size_t base = (size_t)g * rows_per_group * cvec;
+  for (size_t i = r0 * cvec + threadIdx.x; i < r1 * cvec; i += kBnThreads) {
+    const int c0 = (int)(i % cvec) * 8;
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(x) + base + i);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = unpack_bf16x2(w[j]);
+      const float a = apply_act(f.x * ss[c0 + 2 * j] + ss[C + c0 + 2 * j], act);
+      const float b = apply_act(f.y * ss[c0 + 2 * j + 1] + ss[C + c0 + 2 * j + 1], act);
+      o[j] = pack_bf16x2(a, b);
+    }
+    reinterpret_cast<uint4*>(y)[base + i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// backward reduce: for upstream slab g (statistics / pre-activations of slab stat_group(g)):
+//   dy = da * act'(gamma*xhat+beta);  red[g][0][c] += sum dy;  red[g][1][c] += sum dy*xhat
+// stat group of slab g is min(g, n_stat_groups-1).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float act_grad(float y, int act) {
+  if (act == kActRelu) return y > 0.f ? 1.f : 0.f;
+  if (act == kActLrelu) return y > 0.f ? 1.f : 0.2f;
+  return 1.f;
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ pre,
+                     const float* __restrict__ saved, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, float* __restrict__ red_out, int rows_per_group, int C,
+                     int n_stat_groups, int act, int rows_per_block) {
+  extern __shared__ float red[];  // [2][C]
+  const int g = blockIdx.y;
+  const int sg = min(g, n_stat_groups - 1);
+  const int cvec = C >> 3;
+  const int lanes = kBnThreads / cvec;
+  const int cv = threadIdx.x % cvec;
+  const int rl = threadIdx.x / cvec;
+  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) red[i] = 0.f;
+  __syncthreads();
+  if (rl < lanes) {
+    float mean[8], rstd[8], gm[8], bt[8], s1[8], s2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = cv * 8 + j;
+      mean[j] = saved[((size_t)sg * 2) * C + c];
+      rstd[j] = saved[((size_t)sg * 2 + 1) * C + c];
+      gm[j] = gamma[c]; bt[j] = beta[c];
+      s1[j] = 0.f; s2[j] = 0.f;
+    }
+    const int r0 = blockIdx.x * rows_per_block;
+    const int r1 = min(r0 + rows_per_block, rows_per_group);
+    const __nv_bfloat16* dab = da + ((size_t)g * rows_per_group) * C + cv * 8;
+    const __nv_bfloat16* prb = pre + ((size_t)sg * rows_per_group) * C + cv * 8;
+    for (int r = r0 + rl; r < r1; r += lanes) {
+      const uint4 dv = __ldg(reinterpret_cast<const uint4*>(dab + (size_t)r * C));
+      const uint4 pv = __ldg(reinterpret_cast<const uint4*>(prb + (size_t)r * C));
+      const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
+      const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 d = unpack_bf16x2(dw[j]);
+        const float2 p = unpack_bf16x2(pw[j]);
+        const float xh0 = (p.x - mean[2 * j]) * rstd[2 * j];
+        const float xh1 = (p.y - mean[2 * j + 1]) * rstd[2 * j + 1];
+        const float dy0 = d.x * act_grad(gm[2 * j] * xh0 + bt[2 * j], act);
+        const float dy1 = d.y * act_grad(gm[2 * j + 1] * xh1 + bt[2 * j + 1], act);
+        s1[2 * j] += dy0; s2[2 * j] += dy0 * xh0;
+        s1[2 * j + 1] += dy1; s2[2 * j + 1] += dy1 * xh1;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&red[cv * 8 + j], s1[j]);
+      atomicAdd(&red[C + cv * 8 + j], s2[j]);
+    }
+  }
+  __syncthreads();
+  float* out = red_out + (size_t)g * 2 * C;
+  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) atomicAdd(&out[i], red[i]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// backward apply: dpre = gamma*rstd*(dy - mean(dy) - xhat*mean(dy*xhat)) as bf16; block (0,0)
+// also emits dgamma = sum over the first n_param_groups slabs of sum(dy*xhat), dbeta likewise.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ pre,
+                    __nv_bfloat16* __restrict__ dpre, const float* __restrict__ saved,
+                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                    const float* __restrict__ red, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                    int rows_per_group, int C, int n_stat_groups, int n_param_groups, float inv_count, int act,
+                    int rows_per_block) {
+  extern __shared__ float sm[];  // mean, rstd, gamma, beta, m1, m2 : 6*C
+  const int g = blockIdx.y;
+  const int sg = min(g, n_stat_groups - 1);
+  float* s_mean = sm; float* s_rstd = sm + C; float* s_g = sm + 2 * C; float* s_b = sm + 3 * C;
+  float* s_m1 = sm + 4 * C; float* s_m2 = sm + 5 * C;
+  for (int c = threadIdx.x; c < C; c += kBnThreads) {
+    s_mean[c] = saved[((size_t)sg * 2) * C + c];
+    s_rstd[c] = saved[((size_t)sg * 2 + 1) * C + c];
+    s_g[c] = gamma[c]; s_b[c] = beta[c];
+    s_m1[c] = red[((size_t)g * 2) * C + c] * inv_count;
+    s_m2[c] = red[((size_t)g * 2 + 1) * C + c] * inv_count;
+    if (blockIdx.x == 0 && g == 0 && dgamma) {
+      float dg = 0.f, db = 0.f;
+      for (int q = 0; q < n_param_groups; ++q) {
+        db += red[((size_t)q * 2) * C + c];
+        dg += red[((size_t)q * 2 + 1) * C + c];
+      }
+      dgamma[c] = dg; dbeta[c] = db;
+    }
+  }
+  __syncthreads();
+  const int cvec = C >> 3;
+  const size_t r0 = (size_t)blockIdx.x * rows_per_block;
+  const size_t r1 = min(r0 + (size_t)rows_per_block, (size_t)rows_per_group);
+  const size_t dbase = (size_t)g * rows_per_group * cvec;
+  const size_t pbase = (size_t)sg * rows_per_group * cvec;
+  for (size_t i = r0 * cvec + threadIdx.x; i < r1 * cvec; i += kBnThreads) {
+    const int c0 = (int)(i % cvec) * 8;
+    const uint4 dv = __ldg(reinterpret_cast<const uint4*>(da) + dbase + i);
+    const uint4 pv = __ldg(reinterpret_cast<const uint4*>(pre) + pbase + i);
+    const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
+    const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 d = unpack_bf16x2(dw[j]);
+      const float2 p = unpack_bf16x2(pw[j]);
+      float r[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int c = c0 + 2 * j + h;
+        const float xh = ((h ? p.y : p.x) - s_mean[c]) * s_rstd[c];
+        const float dy = (h ? d.y : d.x) * act_grad(s_g[c] * xh + s_b[c], act);
+        r[h] = s_g[c] * s_rstd[c] * (dy - s_m1[c] - xh * s_m2[c]);
+      }
+      o[j] = pack_bf16x2(r[0], r[1]);
+    }
+    reinterpret_cast<uint4*>(dpre)[dbase + i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// activation backward without batch norm (d_h0: bias + LeakyReLU only, distriubted_model.py:118):
+// dpre = da * act'(a) using the sign of the saved post-activation; also the bias gradient
+// dbias[c] += sum over the first bias_rows rows of dpre.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBnThreads)
+act_bwd_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ a,
+               __nv_bfloat16* __restrict__ dpre, float* __restrict__ dbias, int rows, int a_rows, int C, int act,
+               int bias_rows, int rows_per_block) {
+  extern __shared__ float red[];  // [C]
+  const int cvec = C >> 3;
+  const int lanes = kBnThreads / cvec;
+  const int cv = threadIdx.x % cvec;
+  const int rl = threadIdx.x / cvec;
+  for (int i = threadIdx.x; i < C; i += kBnThreads) red[i] = 0.f;
+  __syncthreads();
+  if (rl < lanes) {
+    float s[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = 0.f;
+    const int r0 = blockIdx.x * rows_per_block;
+    const int r1 = min(r0 + rows_per_block, rows);
+    for (int r = r0 + rl; r < r1; r += lanes) {
+      const int ar = r < a_rows ? r : r - (rows - a_rows);  // third slab re-uses the fake slab's activations
+      const uint4 dv = __ldg(reinterpret_cast<const uint4*>(da + (size_t)r * C + cv * 8));
+      const uint4 av = __ldg(reinterpret_cast<const uint4*>(a + (size_t)ar * C + cv * 8));
+      const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
+      const uint32_t aw[4] = {av.x, av.y, av.z, av.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 d = unpack_bf16x2(dw[j]);
+        const float2 p = unpack_bf16x2(aw[j]);
+        const float r0v = d.x * act_grad(p.x, act);
+        const float r1v = d.y * act_grad(p.y, act);
+        if (r < bias_rows) { s[2 * j] += r0v; s[2 * j + 1] += r1v; }
+        o[j] = pack_bf16x2(r0v, r1v);
+      }
+      *reinterpret_cast<uint4*>(dpre + (size_t)r * C + cv * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+    if (dbias) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) atomicAdd(&red[cv * 8 + j], s[j]);
+    }
+  }
+  __syncthreads();
+  if (dbias)
+    for (int i = threadIdx.x; i < C; i += kBnThreads) atomicAdd(&dbias[i], red[i]);
+}
+
+static int pick_rows_per_block(int rows, int C, int groups) {
+  // aim for ~2 waves of 148 SMs with at least a few KB of work per block
+  int blocks_target = 296 / (groups > 0 ? groups : 1);
+  if (blocks_target < 1) blocks_target = 1;
+  int rpb = (rows + blocks_target - 1) / blocks_target;
+  const int min_rows = (8192 / C) > 1 ? (8192 / C) : 1;
+  if (rpb < min_rows) rpb = min_rows;
+  return rpb;
+}
+
+}  // namespace dcgan
+
+using namespace dcgan;
+
+extern "C" {
+
+int dcgan_bn_stats(const void* x, float* sums, int groups, int rows_per_group, int C, cudaStream_t st) {
+  if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
+  const int rpb = pick_rows_per_block(rows_per_group, C, groups);
+  dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
+  bn_stats_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(reinterpret_cast<const __nv_bfloat16*>(x), sums,
+                                                                  rows_per_group, C, rpb);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_bn_apply(const void* x, void* y, const float* sums, const float* gamma, const float* beta, float* saved,
+                   float* ema_mean, float* ema_var, int groups, int rows_per_group, int C, float eps, float decay,
+                   int act, int use_ema, cudaStream_t st) {
+  if (C % 8) return DCGAN_ERR_SHAPE;
+  const int rpb = pick_rows_per_block(rows_per_group, C, groups);
+  dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
+  bn_apply_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, saved,
+      ema_mean, ema_var, rows_per_group, C, 1.0f / (float)rows_per_group, eps, decay, act, use_ema, rpb);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_bn_bwd_reduce(const void* da, const void* pre, const float* saved, const float* gamma, const float* beta,
+                        float* red, int groups, int stat_groups, int rows_per_group, int C, int act,
+                        cudaStream_t st) {
+  if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
+  const int rpb = pick_rows_per_block(rows_per_group, C, groups);
+  dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
+  bn_bwd_reduce_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(pre), saved, gamma, beta,
+      red, rows_per_group, C, stat_groups, act, rpb);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_bn_bwd_apply(const void* da, const void* pre, void* dpre, const float* saved, const float* gamma,
+                       const float* beta, const float* red, float* dgamma, float* dbeta, int groups,
+                       int stat_groups, int param_groups, int rows_per_group, int C, int act, cudaStream_t st) {
+  if (C % 8) return DCGAN_ERR_SHAPE;
+  const int rpb = pick_rows_per_block(rows_per_group, C, groups);
+  dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
+  bn_bwd_apply_kernel<<<grid, kBnThreads, 6 * C * sizeof(float), st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(pre),
+      reinterpret_cast<__nv_bfloat16*>(dpre), saved, gamma, beta, red, dgamma, dbeta, rows_per_group, C,
+      stat_groups, param_groups, 1.0f / (float)rows_per_group, act, rpb);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_act_bwd(const void* da, const void* a, void* dpre, float* dbias, int rows, int a_rows, int C, int act,
+                  int bias_rows, cudaStream_t st) {
+  if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
+  const int rpb = pick_rows_per_block(rows, C, 1);
+  dim3 grid((rows + rpb - 1) / rpb);
+  act_bwd_kernel<<<grid, kBnThreads, C * sizeof(float), st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(a),
+      reinterpret_cast<__nv_bfloat16*>(dpre), dbias, rows, a_rows, C, act, bias_rows, rpb);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+}  // extern "C"

@@ -1,0 +1,407 @@
+"""B200 training engine: the whole D+G step as a fixed sequence of hand-written sm_100a kernels.
+
+What the reference does in one ``sess.run([d_loss_fake, d_loss_real, g_loss, d_optim, g_optim,
+global_step])`` (``image_train.py:156-158``) is restated here B200-first:
+
+* every buffer (f32 master weights in TensorFlow layouts, bf16 compute copies, gradients, Adam
+  slots, EMA shadows, activations) is allocated once, so the step is pointer-stable and can be
+  replayed from a CUDA graph;
+* forward and backward are written out by hand (no autograd on the hot path): D runs once on the
+  concatenated [real; fake] batch with per-half batch-norm statistics, and its data-gradient pass
+  carries three slabs -- d_loss through real, d_loss through fake, g_loss through fake -- so the
+  "D(fake) is back-propagated twice" cost of the reference graph becomes one
+  wider GEMM per layer;
+* D and G are updated simultaneously from the same forward pass, as in the reference
+  (``update_mode='simultaneous'``); ``'alternating'`` re-runs D(fake) after the D update.
+
+The optimizer step is pluggable (``self.comm``): single GPU -> fused Adam kernel; multi GPU ->
+the fused reduce-scatter + Adam + all-gather kernel over NVLink peer memory (parallel/sync_dp.py).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from .config import ModelConfig
+from .models import dcgan, manifest
+from .ops import kernels as K
+
+
+class ParamArena:
+    """Flat f32 master / grad / Adam buffers with TF-named, TF-layout views."""
+
+    def __init__(self, cfg: ModelConfig, device, pad_to: int = 1024):
+        self.specs = manifest.trainable_specs(cfg)
+        self.offsets: Dict[str, Tuple[int, Tuple[int, ...]]] = {}
+        off = 0
+        for s in self.specs:
+            self.offsets[s.name] = (off, s.shape)
+            off += (s.numel + 7) // 8 * 8  # keep every tensor 32-byte aligned (vector loads, TMA)
+        self.numel = off
+        self.padded = (off + pad_to - 1) // pad_to * pad_to
+        self.g_end = self.offsets["d_h0_conv/w"][0]  # generator variables come first
+        f32 = dict(dtype=torch.float32, device=device)
+        self.master = torch.zeros(self.padded, **f32)
+        self.m = torch.zeros(self.padded, **f32)
+        self.v = torch.zeros(self.padded, **f32)
+        self.bf16 = torch.zeros(self.padded, dtype=torch.bfloat16, device=device)
+
+    def view(self, flat: torch.Tensor, name: str) -> torch.Tensor:
+        off, shape = self.offsets[name]
+        n = 1
+        for s in shape:
+            n *= s
+        return flat[off:off + n].view(shape)
+
+    def named(self, flat: torch.Tensor) -> Dict[str, torch.Tensor]:
+        return {s.name: self.view(flat, s.name) for s in self.specs}
+
+
+class DCGANEngine:
+    def __init__(self, cfg: ModelConfig = ModelConfig(), device="cuda", seed: int = 0, lr: float = 2e-4,
+                 beta1: float = 0.5, beta2: float = 0.999, eps: float = 1e-8, update_mode: str = "simultaneous",
+                 comm=None, init: Optional[Dict[str, torch.Tensor]] = None):
+        assert update_mode in ("simultaneous", "alternating")
+        from .ops import _lib
+        _lib.load()  # fail loudly if the kernel library is missing
+        self.cfg, self.device = cfg, torch.device(device)
+        self.lr, self.beta1, self.beta2, self.eps = lr, beta1, beta2, eps
+        self.update_mode = update_mode
+        self.comm = comm
+        self.B = B = cfg.batch_size
+        self.arena = A = ParamArena(cfg, self.device)
+        self.params = A.named(A.master)
+        src = init if init is not None else dcgan.init_params(cfg, seed=seed)
+        for n, t in self.params.items():
+            t.copy_(src[n].to(self.device, torch.float32))
+        dev = self.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        bf = dict(dtype=torch.bfloat16, device=dev)
+
+        # ---- layer geometry ---------------------------------------------------------------------------
+        s, gf, df = cfg.output_size, cfg.gf_dim, cfg.df_dim
+        self.g_ch = [gf * 8, gf * 4, gf * 2, gf, cfg.c_dim]
+        self.g_sz = [s // 16, s // 8, s // 4, s // 2, s]
+        self.d_ch = [cfg.c_dim, df, df * 2, df * 4, df * 8]
+        self.d_sz = [s, s // 2, s // 4, s // 8, s // 16]
+        assert cfg.c_dim == 3, "the 3-channel kernels assume RGB"
+
+        # ---- zero-per-step region: gradients + BN reduction scratch, one memset ----------------------
+        def site_sizes(C, groups, slabs):
+            return groups * 2 * C, slabs * 2 * C
+        scratch = 0
+        self._bn_off = {}
+        for i in range(4):
+            a, b = site_sizes(self.g_ch[i], 1, 1)
+            self._bn_off[f"g_bn{i}"] = (scratch, scratch + a)
+            scratch += a + b
+        for i in (1, 2, 3):
+            a, b = site_sizes(self.d_ch[i + 1], 2, 3)
+            self._bn_off[f"d_bn{i}"] = (scratch, scratch + a)
+            scratch += a + b
+        self.zero_region = torch.zeros(A.padded + scratch, **f32)
+        self.grads = self.zero_region[:A.padded]
+        self.grad_views = A.named(self.grads)
+        self._scratch = self.zero_region[A.padded:]
+
+        def bn_bufs(name, C, groups, slabs):
+            o1, o2 = self._bn_off[name]
+            sums = self._scratch[o1:o1 + groups * 2 * C].view(groups, 2, C)
+            red = self._scratch[o2:o2 + slabs * 2 * C].view(slabs, 2, C)
+            return sums, red
+        self.bn: Dict[str, dict] = {}
+        self.ema_flat_parts: List[torch.Tensor] = []
+        for i in range(4):
+            C = self.g_ch[i]
+            sums, red = bn_bufs(f"g_bn{i}", C, 1, 1)
+            self.bn[f"g_bn{i}"] = dict(C=C, groups=1, slabs=1, sums=sums, red=red,
+                                       saved=torch.zeros(1, 2, C, **f32), ema_mean=torch.zeros(1, C, **f32),
+                                       ema_var=torch.zeros(1, C, **f32), act="relu")
+        for i in (1, 2, 3):
+            C = self.d_ch[i + 1]
+            sums, red = bn_bufs(f"d_bn{i}", C, 2, 3)
+            self.bn[f"d_bn{i}"] = dict(C=C, groups=2, slabs=3, sums=sums, red=red,
+                                       saved=torch.zeros(2, 2, C, **f32), ema_mean=torch.zeros(2, C, **f32),
+                                       ema_var=torch.zeros(2, C, **f32), act="lrelu")
+
+        # ---- bf16 compute copies of the weights -------------------------------------------------------
+        self.w_native = A.named(A.bf16)
+        self.w_t: Dict[str, torch.Tensor] = {}
+        for i in (1, 2, 3):
+            co, ci = self.g_ch[i], self.g_ch[i - 1]
+            self.w_t[f"g_h{i}/w"] = torch.zeros(25, ci, co, **bf)      # [25][Cin_d][Cout_d]: deconv data-grad
+            ci, co = self.d_ch[i], self.d_ch[i + 1]
+            self.w_t[f"d_h{i}_conv/w"] = torch.zeros(25, co, ci, **bf)  # [25][Cout][Cin]: conv forward
+
+        # ---- activations ------------------------------------------------------------------------------
+        self.z = torch.zeros(B, cfg.z_dim, **f32)
+        self.real_f32 = torch.zeros(B, s, s, 3, **f32)       # landing buffer of the input pipeline (H2D)
+        self.g_pre = [torch.zeros(B, self.g_sz[i], self.g_sz[i], self.g_ch[i], **bf) for i in range(4)]
+        self.g_act = [torch.zeros_like(t) for t in self.g_pre]
+        self.d_in = torch.zeros(2 * B, s, s, 3, **bf)        # [real; G(z)]
+        self.d_act0 = torch.zeros(2 * B, self.d_sz[1], self.d_sz[1], self.d_ch[1], **bf)
+        self.d_pre = [None] + [torch.zeros(2 * B, self.d_sz[i + 1], self.d_sz[i + 1], self.d_ch[i + 1], **bf)
+                               for i in (1, 2, 3)]
+        self.d_act = [self.d_act0] + [torch.zeros_like(t) for t in self.d_pre[1:]]
+        self.logits = torch.zeros(2 * B, **f32)
+        self.probs = torch.zeros(2 * B, **f32)
+        self.losses = torch.zeros(3, **f32)
+        self.dlogit = torch.zeros(3 * B, **f32)
+        self.counters = torch.zeros(2, dtype=torch.int64, device=dev)  # [adam_t, global_step]
+        # gradients w.r.t. activations (3 slabs through D, 1 through G)
+        self.dd_act = [torch.zeros(3 * B, *t.shape[1:], **bf) for t in self.d_act]
+        self.dd_pre = [torch.zeros(3 * B, *t.shape[1:], **bf) for t in self.d_act]
+        self.dimg = torch.zeros(B, s, s, 3, **bf)             # d g_loss / d (pre-tanh generator output)
+        self.dg_act = [torch.zeros_like(t) for t in self.g_act]
+        self.dg_pre = [torch.zeros_like(t) for t in self.g_act]
+        # sampler buffers (EMA batch norm, train=False)
+        self.s_pre = [torch.zeros_like(t) for t in self.g_pre]
+        self.s_act = [torch.zeros_like(t) for t in self.g_pre]
+        self.s_img = torch.zeros(B, s, s, 3, **bf)
+
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self.refresh_compute_weights()
+
+    # ------------------------------------------------------------------------------------------------
+    # weights
+    # ------------------------------------------------------------------------------------------------
+    def refresh_compute_weights(self, cast: bool = True) -> None:
+        """bf16 copies of the master weights: the flat native cast plus the per-tap transposes."""
+        A = self.arena
+        if cast:
+            K.cast_bf16(A.master, A.bf16)
+        for i in (1, 2, 3):
+            co, ci = self.g_ch[i], self.g_ch[i - 1]
+            K.transpose_taps(self.w_native[f"g_h{i}/w"], self.w_t[f"g_h{i}/w"], 25, co, ci)
+            ci, co = self.d_ch[i], self.d_ch[i + 1]
+            K.transpose_taps(self.w_native[f"d_h{i}_conv/w"], self.w_t[f"d_h{i}_conv/w"], 25, ci, co)
+
+    # ------------------------------------------------------------------------------------------------
+    # forward
+    # ------------------------------------------------------------------------------------------------
+    def _bn_fwd(self, name, pre, act_out, train=True):
+        st = self.bn[name]
+        C, G = st["C"], st["groups"]
+        x2, y2 = pre.view(-1, C), act_out.view(-1, C)
+        p = self.params
+        if train:
+            K.bn_stats(x2, st["sums"], G)
+            if self.comm is not None and getattr(self.comm, "sync_bn", False):
+                self.comm.allreduce_bn(st["sums"])
+            K.bn_apply(x2, y2, st["sums"], p[f"{name}/gamma"], p[f"{name}/beta"], st["saved"], st["ema_mean"],
+                       st["ema_var"], G, st["act"], self.cfg.bn_eps, self.cfg.bn_momentum)
+        else:
+            K.bn_apply(x2, y2, st["sums"], p[f"{name}/gamma"], p[f"{name}/beta"], None, st["ema_mean"],
+                       st["ema_var"], 1, st["act"], self.cfg.bn_eps, self.cfg.bn_momentum, use_ema=True)
+
+    def generator_forward(self, train: bool = True) -> torch.Tensor:
+        """z -> images; training mode writes into the fake half of ``d_in``."""
+        p, B = self.params, self.B
+        pre = self.g_pre if train else self.s_pre
+        act = self.g_act if train else self.s_act
+        K.lin_fwd(self.z, self.w_native["g_h0_lin/Matrix"], p["g_h0_lin/bias"], pre[0].view(B, -1))
+        self._bn_fwd("g_bn0", pre[0], act[0], train)
+        for i in (1, 2, 3):
+            w = self.w_native[f"g_h{i}/w"].view(25, self.g_ch[i], self.g_ch[i - 1])
+            K.conv_tconv(act[i - 1], w, p[f"g_h{i}/biases"], out=pre[i])
+            self._bn_fwd(f"g_bn{i}", pre[i], act[i], train)
+        out = self.d_in[B:] if train else self.s_img
+        K.c3_tconv(act[3], p["g_h4/w"], p["g_h4/biases"], act="tanh", out=out)
+        return out
+
+    def discriminator_forward(self) -> None:
+        p = self.params
+        K.c3_fprop(self.d_in, p["d_h0_conv/w"], p["d_h0_conv/biases"], act="lrelu", out=self.d_act[0])
+        for i in (1, 2, 3):
+            K.conv_fprop(self.d_act[i - 1], self.w_t[f"d_h{i}_conv/w"], p[f"d_h{i}_conv/biases"], out=self.d_pre[i])
+            self._bn_fwd(f"d_bn{i}", self.d_pre[i], self.d_act[i])
+        K.head_fwd(self.d_act[3].view(2 * self.B, -1), p["d_h3_lin/Matrix"], p["d_h3_lin/bias"], self.logits)
+
+    # ------------------------------------------------------------------------------------------------
+    # backward
+    # ------------------------------------------------------------------------------------------------
+    def _bn_bwd(self, name, da, pre, dpre):
+        st = self.bn[name]
+        C = st["C"]
+        p, g = self.params, self.grad_views
+        slabs, G = st["slabs"], st["groups"]
+        K.bn_bwd_reduce(da.view(-1, C), pre.view(-1, C), st["saved"], p[f"{name}/gamma"], p[f"{name}/beta"],
+                        st["red"], slabs, G, st["act"])
+        if self.comm is not None and getattr(self.comm, "sync_bn", False):
+            self.comm.allreduce_bn(st["red"])
+        K.bn_bwd_apply(da.view(-1, C), pre.view(-1, C), dpre.view(-1, C), st["saved"], p[f"{name}/gamma"],
+                       p[f"{name}/beta"], st["red"], g[f"{name}/gamma"], g[f"{name}/beta"], slabs, G, G, st["act"])
+
+    def discriminator_backward(self) -> None:
+        """Three slabs of data gradient ([d_loss|real, d_loss|fake, g_loss|fake]); filter gradients from
+        the first two only (``var_list=d_vars`` for d_loss, image_train.py:109-110)."""
+        p, g, B = self.params, self.grad_views, self.B
+        K.head_bwd(self.d_act[3].view(2 * B, -1), p["d_h3_lin/Matrix"], self.dlogit,
+                   self.dd_act[3].view(3 * B, -1), g["d_h3_lin/Matrix"], g["d_h3_lin/bias"], B)
+        for i in (3, 2, 1):
+            self._bn_bwd(f"d_bn{i}", self.dd_act[i], self.d_pre[i], self.dd_pre[i])
+            ci, co = self.d_ch[i], self.d_ch[i + 1]
+            K.conv_wgrad(self.d_act[i - 1], self.dd_pre[i][:2 * B], g[f"d_h{i}_conv/w"].view(25, ci, co))
+            K.conv_tconv(self.dd_pre[i], self.w_native[f"d_h{i}_conv/w"].view(25, ci, co), None,
+                         out=self.dd_act[i - 1])
+        C0 = self.d_ch[1]
+        K.act_bwd(self.dd_act[0].view(-1, C0), self.d_act[0].view(-1, C0), self.dd_pre[0].view(-1, C0),
+                  g["d_h0_conv/biases"], "lrelu", bias_rows=2 * B * self.d_sz[1] * self.d_sz[1])
+        K.c3_wgrad(self.d_in, self.dd_pre[0][:2 * B], g["d_h0_conv/w"])
+        # g_loss slab only: gradient w.r.t. the generator's pre-tanh output
+        K.c3_tconv(self.dd_pre[0][2 * B:], p["d_h0_conv/w"], None, aux=self.d_in[B:], out=self.dimg)
+
+    def generator_backward(self) -> None:
+        p, g, B = self.params, self.grad_views, self.B
+        K.colsum(self.dimg.view(-1, 3), g["g_h4/biases"])
+        K.c3_wgrad(self.dimg, self.g_act[3], g["g_h4/w"])
+        K.c3_fprop(self.dimg, p["g_h4/w"], None, out=self.dg_act[3])
+        for i in (3, 2, 1):
+            self._bn_bwd(f"g_bn{i}", self.dg_act[i], self.g_pre[i], self.dg_pre[i])
+            co, ci = self.g_ch[i], self.g_ch[i - 1]
+            K.conv_wgrad(self.dg_pre[i], self.g_act[i - 1], g[f"g_h{i}/w"].view(25, co, ci))
+            K.conv_fprop(self.dg_pre[i], self.w_t[f"g_h{i}/w"], None, out=self.dg_act[i - 1])
+        self._bn_bwd("g_bn0", self.dg_act[0], self.g_pre[0], self.dg_pre[0])
+        K.lin_wgrad(self.z, self.dg_pre[0].view(B, -1), g["g_h0_lin/Matrix"], None)
+
+    # ------------------------------------------------------------------------------------------------
+    # optimizer
+    # ------------------------------------------------------------------------------------------------
+    def _adam_range(self, lo: int, hi: int) -> None:
+        A = self.arena
+        K.adam(A.master[lo:hi], self.grads[lo:hi], A.m[lo:hi], A.v[lo:hi], A.bf16[lo:hi], self.counters, self.lr,
+               self.beta1, self.beta2, self.eps, 1.0)
+
+    def optimizer_step(self, which: str = "both") -> None:
+        A = self.arena
+        if self.comm is not None:
+            self.comm.optimizer_step(self, which)
+        else:
+            lo, hi = {"both": (0, A.padded), "g": (0, A.g_end), "d": (A.g_end, A.padded)}[which]
+            self._adam_range(lo, hi)
+        self.refresh_compute_weights(cast=False)
+
+    # ------------------------------------------------------------------------------------------------
+    # the step
+    # ------------------------------------------------------------------------------------------------
+    def step_body(self) -> None:
+        """Everything of one training iteration that runs on the device, in stream order."""
+        B = self.B
+        self.zero_region.zero_()
+        K.f32_to_bf16(self.real_f32, self.d_in[:B])
+        self.generator_forward(train=True)
+        self.discriminator_forward()
+        K.gan_loss(self.logits, self.losses, self.dlogit, self.probs, self.counters, B, 1.0, True)
+        self.discriminator_backward()
+        if self.update_mode == "simultaneous":
+            self.generator_backward()
+            self.optimizer_step("both")
+        else:
+            # D first, then G against the updated D (carpedm20-style alternation)
+            self.optimizer_step("d")
+            self.discriminator_forward()
+            K.gan_loss(self.logits, self.losses[:3], self.dlogit, self.probs, None, B, 1.0, False)
+            self.discriminator_backward()
+            self.generator_backward()
+            self.optimizer_step("g")
+
+    def capture(self) -> None:
+        """Warm up on a side stream and capture the step into a CUDA graph."""
+        state = self.snapshot_state()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self.step_body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.restore_state(state)
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self.step_body()
+        self.restore_state(state)
+
+    def run_step(self) -> None:
+        """One iteration on the inputs currently in ``real_f32`` / ``z`` (no host sync)."""
+        if self._graph is not None:
+            self._graph.replay()
+        else:
+            self.step_body()
+
+    def train_step(self, real: torch.Tensor, z: torch.Tensor) -> Tuple[float, float, float, int]:
+        """Public single-step API: copies the inputs (pinned host or device tensors), runs the step and
+        reads back ``(d_loss_real, d_loss_fake, g_loss, global_step)`` -- the fetches of
+        ``image_train.py:156-158``."""
+        self.real_f32.copy_(real, non_blocking=True)
+        self.z.copy_(z, non_blocking=True)
+        self.run_step()
+        l = self.losses.tolist()
+        return l[0], l[1], l[2], int(self.counters[1].item())
+
+    # ------------------------------------------------------------------------------------------------
+    # sampler / state
+    # ------------------------------------------------------------------------------------------------
+    def sample(self, z: torch.Tensor) -> torch.Tensor:
+        """``sampler(z)`` (distriubted_model.py:131-153): generator with EMA batch-norm statistics."""
+        self.z.copy_(z)
+        return self.generator_forward(train=False)
+
+    def ema_named(self) -> Dict[str, torch.Tensor]:
+        out = {}
+        for i in range(4):
+            m, v = manifest.ema_names(f"g_bn{i}")
+            out[m], out[v] = self.bn[f"g_bn{i}"]["ema_mean"][0], self.bn[f"g_bn{i}"]["ema_var"][0]
+        for i in (1, 2, 3):
+            for gidx, sfx in enumerate(("", "_1")):
+                m, v = manifest.ema_names(f"d_bn{i}{sfx}")
+                out[m], out[v] = self.bn[f"d_bn{i}"]["ema_mean"][gidx], self.bn[f"d_bn{i}"]["ema_var"][gidx]
+        return out
+
+    def snapshot_state(self):
+        A = self.arena
+        return dict(master=A.master.clone(), m=A.m.clone(), v=A.v.clone(), counters=self.counters.clone(),
+                    ema={k: t.clone() for k, t in self.ema_named().items()})
+
+    def restore_state(self, st) -> None:
+        A = self.arena
+        A.master.copy_(st["master"]); A.m.copy_(st["m"]); A.v.copy_(st["v"])
+        self.counters.copy_(st["counters"])
+        for k, t in self.ema_named().items():
+            t.copy_(st["ema"][k])
+        self.refresh_compute_weights()
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        """TF-named checkpoint contents: weights, EMA shadows, global_step, and the Adam slots under
+        TensorFlow's slot names."""
+        A = self.arena
+        sd = {n: t.detach().clone() for n, t in self.params.items()}
+        sd.update({n: t.detach().clone() for n, t in self.ema_named().items()})
+        sd[manifest.GLOBAL_STEP_NAME] = self.counters[1].to(torch.int32).clone()
+        m, v = A.named(A.m), A.named(A.v)
+        for n in self.params:
+            a, b = manifest.adam_slot_names(n)
+            sd[a], sd[b] = m[n].clone(), v[n].clone()
+        t = int(self.counters[0].item())
+        sd["beta1_power"] = torch.tensor(self.beta1 ** (t + 1))
+        sd["beta2_power"] = torch.tensor(self.beta2 ** (t + 1))
+        sd["adam_t"] = self.counters[0].clone()
+        return sd
+
+    def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+        A = self.arena
+        for n, t in self.params.items():
+            t.copy_(sd[n].to(self.device))
+        for n, t in self.ema_named().items():
+            if n in sd:
+                t.copy_(sd[n].to(self.device))
+        m, v = A.named(A.m), A.named(A.v)
+        for n in self.params:
+            a, b = manifest.adam_slot_names(n)
+            if a in sd:
+                m[n].copy_(sd[a].to(self.device)); v[n].copy_(sd[b].to(self.device))
+        if manifest.GLOBAL_STEP_NAME in sd:
+            self.counters[1] = int(sd[manifest.GLOBAL_STEP_NAME])
+        if "adam_t" in sd:
+            self.counters[0] = int(sd["adam_t"])
+        self.refresh_compute_weights()

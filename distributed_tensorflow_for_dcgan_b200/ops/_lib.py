@@ -1,0 +1,123 @@
+"""ctypes binding of libdcgan_b200.so (C ABI in include/dcgan_b200.h).
+
+The library is built in-tree by ``build_ext.py`` (nvcc, sm_100a).  On a machine with a GPU a missing
+library is a hard error -- the CUDA path must never silently fall back to PyTorch ops.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional
+
+import torch
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lib", "libdcgan_b200.so")
+_lib: Optional[ctypes.CDLL] = None
+
+c_int, c_float, c_void_p, c_size_t = ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_size_t
+
+# name -> argument kinds: p = device pointer, i = int, f = float, z = size_t, s = stream
+_SIGNATURES = {
+    "dcgan_conv_fprop": "ppppiiiiiiis",
+    "dcgan_conv_tconv": "ppppiiiiiiis",
+    "dcgan_conv_wgrad": "pppiiiiiiis",
+    "dcgan_c3_fprop": "ppppiiiiis",
+    "dcgan_c3_tconv": "pppppiiiiiis",
+    "dcgan_c3_wgrad": "pppiiiis",
+    "dcgan_bn_stats": "ppiiis",
+    "dcgan_bn_apply": "ppppppppiiiffiis",
+    "dcgan_bn_bwd_reduce": "ppppppiiiiis",
+    "dcgan_bn_bwd_apply": "pppppppppiiiiiis",
+    "dcgan_act_bwd": "ppppiiiiis",
+    "dcgan_lin_fwd": "ppppiiis",
+    "dcgan_lin_wgrad": "ppppiiis",
+    "dcgan_head_fwd": "ppppiis",
+    "dcgan_gan_loss": "pppppifis",
+    "dcgan_head_bwd": "ppppppiis",
+    "dcgan_adam": "ppppppzfffffs",
+    "dcgan_cast_bf16": "ppzs",
+    "dcgan_transpose_taps": "ppiiis",
+    "dcgan_colsum": "ppzis",
+    "dcgan_decode_f64": "ppzffs",
+    "dcgan_f32_to_bf16": "ppzffs",
+    "dcgan_grid_merge": "ppiiiiis",
+    "dcgan_count_zeros": "ppzs",
+}
+_KIND = {"p": c_void_p, "i": c_int, "f": c_float, "z": c_size_t, "s": c_void_p}
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def available() -> bool:
+    return os.path.exists(_LIB_PATH)
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        raise RuntimeError(
+            f"{_LIB_PATH} is missing: run `python build_ext.py` (or __graft_entry__.build()) first. "
+            "The CUDA path does not fall back to PyTorch ops.")
+    lib = ctypes.CDLL(_LIB_PATH)
+    for name, sig in _SIGNATURES.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            continue
+        fn.argtypes = [_KIND[k] for k in sig]
+        fn.restype = c_int
+    lib.dcgan_last_device_error.argtypes = []
+    lib.dcgan_last_device_error.restype = c_int
+    lib.dcgan_set_mn_desc_variant.argtypes = [c_int]
+    lib.dcgan_set_mn_desc_variant.restype = None
+    _lib = lib
+    return lib
+
+
+def register(name: str, sig: str) -> None:
+    """Late registration for entry points added by other modules (comm kernels)."""
+    _SIGNATURES[name] = sig
+    if _lib is not None:
+        fn = getattr(_lib, name)
+        fn.argtypes = [_KIND[k] for k in sig]
+        fn.restype = c_int
+
+
+def ptr(t) -> Optional[int]:
+    if t is None:
+        return None
+    if isinstance(t, int):
+        return t
+    return t.data_ptr()
+
+
+def stream_handle() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+class KernelError(RuntimeError):
+    pass
+
+
+_ERR = {-1: "shape not supported", -2: "driver / tensor-map error", -3: "launch failed", -4: "size limit"}
+
+# number of kernel launches issued through this binding (bench.py reports it as gpu_launches)
+launch_count = 0
+
+
+def call(name: str, *args) -> None:
+    """Invoke an entry point; appends the current stream; raises on a non-zero return code."""
+    global launch_count
+    lib = load()
+    fn = getattr(lib, name)
+    rc = fn(*args, stream_handle())
+    if rc != 0:
+        raise KernelError(f"{name} failed: {_ERR.get(rc, rc)}")
+    launch_count += 1
+
+
+def last_device_error() -> int:
+    return load().dcgan_last_device_error()

@@ -60,6 +60,62 @@ int dcgan_conv_tconv(const void* x, const void* w_nk, const float* bias, void* o
 int dcgan_conv_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd,
                      int splits, int block_n, cudaStream_t stream);
 
+/* ---- 3-channel layers on the CUDA cores (csrc/conv_c3.cu) ------------------------------------------
+ * Filter layout for all three is f32 [25][3][C] (= d_h0_conv/w HWIO and g_h4/w [kh,kw,3,C]). */
+
+/* out[N,H/2,W/2,C] = act(conv5x5s2(x[N,H,W,3]) + bias): d_h0 forward (distriubted_model.py:118) and
+ * the g_h4 data gradient. */
+int dcgan_c3_fprop(const void* x, const float* w, const float* bias, void* out, int N, int H, int W, int C,
+                   int act, cudaStream_t stream);
+/* out[N,2H,2W,3] from x[N,H,W,C]: g_h4 forward (distriubted_model.py:109; mode 0: act(v+bias)) and the
+ * d_h0 data gradient (mode 1: v * (1 - aux^2), the tanh backward against aux = generator output). */
+int dcgan_c3_tconv(const void* x, const float* w, const float* bias, const void* aux, void* out, int N, int H,
+                   int W, int C, int act, int mode, cudaStream_t stream);
+/* dw[25][3][C] += sum x3[N,2Hs,2Ws,3] (gathered) * y[N,Hs,Ws,C]   (f32 atomics; zero first). */
+int dcgan_c3_wgrad(const void* x3, const void* y, float* dw, int N, int Hs, int Ws, int C, cudaStream_t stream);
+
+/* ---- batch norm fused with its activation (csrc/bn_act.cu; reference distriubted_model.py:15-52) --
+ * x/y/da/dpre are bf16 [groups*rows_per_group][C]; sums/saved/red are f32 [groups][2][C]. */
+int dcgan_bn_stats(const void* x, float* sums, int groups, int rows_per_group, int C, cudaStream_t stream);
+int dcgan_bn_apply(const void* x, void* y, const float* sums, const float* gamma, const float* beta, float* saved,
+                   float* ema_mean, float* ema_var, int groups, int rows_per_group, int C, float eps, float decay,
+                   int act, int use_ema, cudaStream_t stream);
+int dcgan_bn_bwd_reduce(const void* da, const void* pre, const float* saved, const float* gamma, const float* beta,
+                        float* red, int groups, int stat_groups, int rows_per_group, int C, int act,
+                        cudaStream_t stream);
+int dcgan_bn_bwd_apply(const void* da, const void* pre, void* dpre, const float* saved, const float* gamma,
+                       const float* beta, const float* red, float* dgamma, float* dbeta, int groups,
+                       int stat_groups, int param_groups, int rows_per_group, int C, int act, cudaStream_t stream);
+/* dpre = da * act'(a) for a layer without batch norm (d_h0), plus its bias gradient. */
+int dcgan_act_bwd(const void* da, const void* a, void* dpre, float* dbias, int rows, int a_rows, int C, int act,
+                  int bias_rows, cudaStream_t stream);
+
+/* ---- skinny layers, losses, optimizer, helpers (csrc/heads_optim.cu) ------------------------------ */
+int dcgan_lin_fwd(const float* z, const void* W_bf16, const float* bias, void* out, int NB, int K, int F,
+                  cudaStream_t stream);
+int dcgan_lin_wgrad(const float* z, const void* dy, float* dW, float* dbias, int NB, int K, int F,
+                    cudaStream_t stream);
+int dcgan_head_fwd(const void* h, const float* w, const float* b, float* logits, int rows, int F,
+                   cudaStream_t stream);
+/* losses[3] = {d_loss_real, d_loss_fake, g_loss} (image_train.py:91-96); dlogit[3B]; advances
+ * counters[0] (Adam t) and counters[1] (global_step) when advance != 0. */
+int dcgan_gan_loss(const float* logits, float* losses, float* dlogit, float* probs, long long* counters, int B,
+                   float grad_div, int advance, cudaStream_t stream);
+int dcgan_head_bwd(const void* h, const float* w, const float* dlogit, void* dh, float* dW, float* db, int B,
+                   int F, cudaStream_t stream);
+/* TensorFlow-form Adam (image_train.py:109-112) over a flat range; t is read from counters[0]. */
+int dcgan_adam(float* p, const float* g, float* m, float* v, void* p_bf16, const long long* counters, size_t n,
+               float lr, float b1, float b2, float eps, float gscale, cudaStream_t stream);
+int dcgan_cast_bf16(const float* src, void* dst, size_t n, cudaStream_t stream);
+int dcgan_transpose_taps(const void* src, void* dst, int taps, int R, int C, cudaStream_t stream);
+int dcgan_colsum(const void* x, float* out, size_t rows, int C, cudaStream_t stream);
+/* float64 records -> bf16 (image_input.py:48,118 decode_raw + cast), with an optional affine map. */
+int dcgan_decode_f64(const double* src, void* dst, size_t n, float scale, float shift, cudaStream_t stream);
+int dcgan_f32_to_bf16(const float* src, void* dst, size_t n, float scale, float shift, cudaStream_t stream);
+/* inverse_transform + merge of the sample grid (image_train.py:205-219) into f32 [rows*H][cols*W][C]. */
+int dcgan_grid_merge(const void* img, float* out, int N, int H, int W, int C, int cols, cudaStream_t stream);
+int dcgan_count_zeros(const void* x, unsigned long long* count, size_t n, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,266 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference of the same op
+(tier "Unit / op parity")."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from distributed_tensorflow_for_dcgan_b200.ops import functional as Fn
+
+
+def _rand(shape, scale=1.0, dtype=torch.bfloat16):
+    return (torch.randn(shape, device="cuda") * scale).to(dtype)
+
+
+def _close(got, ref, rel=1e-2, name=""):
+    got, ref = got.float(), ref.float()
+    err = (got - ref).abs().max().item()
+    den = ref.abs().max().item()
+    assert den > 0, name
+    assert err <= rel * den, f"{name}: max err {err} vs max ref {den}"
+
+
+def _w_hwio_to_nk(w_hwio):  # [5,5,Cin,Cout] -> [25,Cout,Cin]
+    return w_hwio.permute(0, 1, 3, 2).reshape(25, w_hwio.shape[3], w_hwio.shape[2]).contiguous()
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout", [(2, 16, 64, 128), (4, 8, 128, 64), (1, 8, 64, 256)])
+def test_conv_fprop(cuda_lib, N, H, Cin, Cout):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    x = _rand((N, H, H, Cin))
+    w = _rand((5, 5, Cin, Cout), 0.05)
+    b = torch.randn(Cout, device="cuda") * 0.1
+    out = K.conv_fprop(x, _w_hwio_to_nk(w), b, act="lrelu")
+    ref = Fn.lrelu(Fn.conv2d_same(x.float(), w.float(), b))
+    K.check_device_error()
+    _close(out, ref, name="conv_fprop")
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout", [(2, 8, 64, 64), (2, 4, 128, 128), (1, 8, 256, 128)])
+def test_conv_tconv(cuda_lib, N, H, Cin, Cout):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    x = _rand((N, H, H, Cin))
+    w = _rand((5, 5, Cout, Cin), 0.05)  # TF deconv layout [kh,kw,Cout,Cin]
+    b = torch.randn(Cout, device="cuda") * 0.1
+    out = K.conv_tconv(x, w.reshape(25, Cout, Cin), b)
+    ref = Fn.deconv2d(x.float(), w.float(), b)
+    K.check_device_error()
+    _close(out, ref, name="conv_tconv")
+
+
+@pytest.mark.parametrize("N,Hs,Cg,Cd", [(2, 8, 64, 128), (4, 4, 256, 256), (4, 8, 128, 256)])
+def test_conv_wgrad_conv_layer(cuda_lib, N, Hs, Cg, Cd):
+    """conv2d filter gradient: big = layer input, small = output gradient -> HWIO."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    x = _rand((N, 2 * Hs, 2 * Hs, Cg))
+    dy = _rand((N, Hs, Hs, Cd))
+    dw = torch.zeros(25, Cg, Cd, device="cuda")
+    K.conv_wgrad(x, dy, dw)
+    w = torch.zeros(5, 5, Cg, Cd, device="cuda", requires_grad=True)
+    y = Fn.conv2d_same(x.float(), w)
+    ref, = torch.autograd.grad(y, w, dy.float())
+    K.check_device_error()
+    _close(dw.view(5, 5, Cg, Cd), ref, rel=2e-3, name="conv_wgrad")
+
+
+def test_conv_wgrad_deconv_layer(cuda_lib):
+    """conv2d_transpose filter gradient: big = output gradient, small = layer input -> [kh,kw,Cout,Cin]."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    N, Hs, Cout, Cin = 2, 8, 64, 128
+    x = _rand((N, Hs, Hs, Cin))
+    dy = _rand((N, 2 * Hs, 2 * Hs, Cout))
+    dw = torch.zeros(25, Cout, Cin, device="cuda")
+    K.conv_wgrad(dy, x, dw)
+    w = torch.zeros(5, 5, Cout, Cin, device="cuda", requires_grad=True)
+    y = Fn.deconv2d(x.float(), w)
+    ref, = torch.autograd.grad(y, w, dy.float())
+    K.check_device_error()
+    _close(dw.view(5, 5, Cout, Cin), ref, rel=2e-3, name="deconv_wgrad")
+
+
+def test_c3_fprop(cuda_lib):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    x = _rand((3, 64, 64, 3))
+    w = torch.randn(5, 5, 3, 64, device="cuda") * 0.05
+    b = torch.randn(64, device="cuda") * 0.1
+    out = K.c3_fprop(x, w, b, act="lrelu")
+    ref = Fn.lrelu(Fn.conv2d_same(x.float(), w, b))
+    _close(out, ref, name="c3_fprop")
+
+
+def test_c3_tconv_fwd_and_tanh_bwd(cuda_lib):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    x = _rand((2, 32, 32, 64))
+    w = torch.randn(5, 5, 3, 64, device="cuda") * 0.05
+    b = torch.randn(3, device="cuda") * 0.1
+    out = K.c3_tconv(x, w, b, act="tanh")
+    ref = torch.tanh(Fn.deconv2d(x.float(), w, b))
+    _close(out, ref, name="c3_tconv")
+    aux = out
+    out2 = K.c3_tconv(x, w, None, aux=aux)
+    ref2 = Fn.deconv2d(x.float(), w) * (1 - aux.float() ** 2)
+    _close(out2, ref2, name="c3_tconv_tanh_bwd")
+
+
+def test_c3_wgrad(cuda_lib):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    x3 = _rand((4, 64, 64, 3))
+    y = _rand((4, 32, 32, 64))
+    dw = torch.zeros(5, 5, 3, 64, device="cuda")
+    K.c3_wgrad(x3, y, dw)
+    w = torch.zeros(5, 5, 3, 64, device="cuda", requires_grad=True)
+    ref, = torch.autograd.grad(Fn.conv2d_same(x3.float(), w), w, y.float())
+    _close(dw, ref, rel=2e-3, name="c3_wgrad")
+
+
+@pytest.mark.parametrize("groups,rows,C,act", [(1, 1024, 512, "relu"), (2, 4096, 128, "lrelu"), (2, 512, 64, "lrelu")])
+def test_bn_forward_backward(cuda_lib, groups, rows, C, act):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    x = _rand((groups * rows, C)) * 2 + 0.5
+    gamma = 1 + 0.1 * torch.randn(C, device="cuda")
+    beta = 0.1 * torch.randn(C, device="cuda")
+    sums = torch.zeros(groups, 2, C, device="cuda")
+    saved = torch.zeros(groups, 2, C, device="cuda")
+    ema_m = torch.zeros(groups, C, device="cuda")
+    ema_v = torch.zeros(groups, C, device="cuda")
+    y = torch.empty_like(x)
+    K.bn_stats(x, sums, groups)
+    K.bn_apply(x, y, sums, gamma, beta, saved, ema_m, ema_v, groups, act)
+    xr = x.float().view(groups, rows, C).requires_grad_(True)
+    mean = xr.mean(1, keepdim=True)
+    var = ((xr - mean) ** 2).mean(1, keepdim=True)
+    yr = (xr - mean) * torch.rsqrt(var + 1e-5) * gamma + beta
+    ar = torch.relu(yr) if act == "relu" else Fn.lrelu(yr)
+    _close(y.view(groups, rows, C), ar, name="bn_apply")
+    _close(ema_m, 0.1 * mean.squeeze(1), rel=2e-3, name="ema_mean")
+    _close(ema_v, 0.1 * var.squeeze(1), rel=2e-3, name="ema_var")
+    # backward with a third slab sharing the statistics of the last group
+    slabs = groups + 1
+    da = _rand((slabs * rows, C))
+    red = torch.zeros(slabs, 2, C, device="cuda")
+    dpre = torch.empty_like(da)
+    dgamma = torch.zeros(C, device="cuda")
+    dbeta = torch.zeros(C, device="cuda")
+    K.bn_bwd_reduce(da, x, saved, gamma, beta, red, slabs, groups, act)
+    K.bn_bwd_apply(da, x, dpre, saved, gamma, beta, red, dgamma, dbeta, slabs, groups, groups, act)
+    daf = da.float().view(slabs, rows, C)
+    gx, gg, gb = torch.autograd.grad(ar, (xr, gamma.requires_grad_(True), beta.requires_grad_(True)),
+                                     daf[:groups], retain_graph=True) if False else (None, None, None)
+    g2 = gamma.detach().clone().requires_grad_(True)
+    b2 = beta.detach().clone().requires_grad_(True)
+    xr2 = x.float().view(groups, rows, C).detach().requires_grad_(True)
+    mean2 = xr2.mean(1, keepdim=True)
+    var2 = ((xr2 - mean2) ** 2).mean(1, keepdim=True)
+    yr2 = (xr2 - mean2) * torch.rsqrt(var2 + 1e-5) * g2 + b2
+    ar2 = torch.relu(yr2) if act == "relu" else Fn.lrelu(yr2)
+    gx, gg, gb = torch.autograd.grad(ar2, (xr2, g2, b2), daf[:groups], retain_graph=True)
+    _close(dpre.view(slabs, rows, C)[:groups], gx, rel=2e-2, name="bn_bwd dx")
+    _close(dgamma, gg, rel=1e-2, name="dgamma")
+    _close(dbeta, gb, rel=1e-2, name="dbeta")
+    # the extra slab: gradient through the last group's normalisation with its own upstream
+    up = torch.zeros_like(daf[:groups])
+    up[groups - 1] = daf[groups]
+    gx3, = torch.autograd.grad(ar2, xr2, up)
+    _close(dpre.view(slabs, rows, C)[groups], gx3[groups - 1], rel=2e-2, name="bn_bwd extra slab")
+
+
+def test_act_bwd(cuda_lib):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    R, C = 512, 64
+    a = _rand((2 * R, C))
+    da = _rand((3 * R, C))
+    dpre = torch.empty_like(da)
+    dbias = torch.zeros(C, device="cuda")
+    K.act_bwd(da, a, dpre, dbias, "lrelu", bias_rows=2 * R)
+    a3 = torch.cat([a, a[R:]]).float()
+    ref = da.float() * torch.where(a3 > 0, 1.0, 0.2)
+    _close(dpre, ref, name="act_bwd")
+    _close(dbias, ref[:2 * R].sum(0), rel=1e-2, name="act_bwd dbias")
+
+
+def test_linear_and_head(cuda_lib):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    B, Kz, F = 64, 100, 8192
+    z = torch.rand(B, Kz, device="cuda") * 2 - 1
+    W = _rand((Kz, F), 0.02)
+    b = torch.randn(F, device="cuda") * 0.01
+    out = torch.empty(B, F, dtype=torch.bfloat16, device="cuda")
+    K.lin_fwd(z, W, b, out)
+    _close(out, z @ W.float() + b, name="lin_fwd")
+    dy = _rand((B, F))
+    dW = torch.empty(Kz, F, device="cuda")
+    db = torch.empty(F, device="cuda")
+    K.lin_wgrad(z, dy, dW, db)
+    _close(dW, z.t() @ dy.float(), rel=2e-3, name="lin_wgrad")
+    _close(db, dy.float().sum(0), rel=2e-3, name="lin_dbias")
+    # discriminator head
+    h = _rand((2 * B, F))
+    w = torch.randn(F, device="cuda") * 0.02
+    hb = torch.tensor([0.3], device="cuda")
+    logits = torch.empty(2 * B, device="cuda")
+    K.head_fwd(h, w, hb, logits)
+    ref_logits = h.float() @ w + hb
+    _close(logits, ref_logits, rel=2e-3, name="head_fwd")
+    losses = torch.zeros(3, device="cuda")
+    dlogit = torch.zeros(3 * B, device="cuda")
+    probs = torch.zeros(2 * B, device="cuda")
+    counters = torch.zeros(2, dtype=torch.int64, device="cuda")
+    K.gan_loss(logits, losses, dlogit, probs, counters, B)
+    lr_, lf_ = ref_logits[:B], ref_logits[B:]
+    ref_losses = torch.stack([Fn.bce_with_logits_mean(lr_, 1.0), Fn.bce_with_logits_mean(lf_, 0.0),
+                              Fn.bce_with_logits_mean(lf_, 1.0)])
+    _close(losses, ref_losses, rel=1e-4, name="losses")
+    assert counters.tolist() == [1, 1]
+    ref_d = torch.cat([(torch.sigmoid(lr_) - 1) / B, torch.sigmoid(lf_) / B, (torch.sigmoid(lf_) - 1) / B])
+    _close(dlogit, ref_d, rel=1e-3, name="dlogit")
+    dh = torch.empty(3 * B, F, dtype=torch.bfloat16, device="cuda")
+    dWh = torch.zeros(F, device="cuda")
+    dbh = torch.zeros(1, device="cuda")
+    K.head_bwd(h, w, dlogit, dh, dWh, dbh, B)
+    _close(dh, dlogit[:, None] * w[None, :], name="head_bwd dh")
+    _close(dWh, (dlogit[:2 * B, None] * h.float()).sum(0), rel=2e-3, name="head_bwd dW")
+    _close(dbh, dlogit[:2 * B].sum().view(1), rel=2e-3, name="head_bwd db")
+
+
+def test_adam_matches_tf_form(cuda_lib):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    from distributed_tensorflow_for_dcgan_b200.optim.adam_tf import adam_tf_step_
+    n = 100003
+    p = torch.randn(n, device="cuda")
+    m = torch.zeros(n, device="cuda")
+    v = torch.zeros(n, device="cuda")
+    pb = torch.empty(n, dtype=torch.bfloat16, device="cuda")
+    pr, mr, vr = p.clone(), m.clone(), v.clone()
+    counters = torch.zeros(2, dtype=torch.int64, device="cuda")
+    for t in range(1, 4):
+        g = torch.randn(n, device="cuda") * 0.01
+        counters[0] = t
+        K.adam(p, g, m, v, pb, counters)
+        adam_tf_step_(pr, g, mr, vr, t)
+    assert torch.allclose(p, pr, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(m, mr, rtol=1e-5, atol=1e-8)
+    assert torch.equal(pb, p.to(torch.bfloat16))
+
+
+def test_helpers(cuda_lib):
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    src = _rand((25, 64, 128))
+    dst = torch.empty(25, 128, 64, dtype=torch.bfloat16, device="cuda")
+    K.transpose_taps(src, dst, 25, 64, 128)
+    assert torch.equal(dst, src.transpose(1, 2).contiguous())
+    x = _rand((5000, 3))
+    out = torch.zeros(3, device="cuda")
+    K.colsum(x, out)
+    _close(out, x.float().sum(0), rel=1e-3, name="colsum")
+    d = torch.rand(1000, dtype=torch.float64, device="cuda")
+    o = torch.empty(1000, dtype=torch.bfloat16, device="cuda")
+    K.decode_f64(d, o, 2.0, -1.0)
+    assert torch.equal(o, (d.float() * 2 - 1).to(torch.bfloat16))
+    img = (_rand((64, 8, 8, 3)).clamp(-1, 1))
+    grid = K.grid_merge(img, 8)
+    ref = ((img.float() + 1) / 2).view(8, 8, 8, 8, 3).permute(0, 2, 1, 3, 4).reshape(64, 64, 3)
+    assert torch.allclose(grid, ref)
+    zf = K.zero_fraction(torch.relu(_rand((4096,))))
+    assert 0.3 < zf.item() < 0.7
