@@ -263,7 +263,7 @@ class DCGANEngine:
             K.conv_wgrad(self.dg_pre[i], self.g_act[i - 1], g[f"g_h{i}/w"].view(25, co, ci))
             K.conv_fprop(self.dg_pre[i], self.w_t[f"g_h{i}/w"], None, out=self.dg_act[i - 1])
         self._bn_bwd("g_bn0", self.dg_act[0], self.g_pre[0], self.dg_pre[0])
-        K.lin_wgrad(self.z, self.dg_pre[0].view(B, -1), g["g_h0_lin/Matrix"], None)
+        K.lin_wgrad(self.z, self.dg_pre[0].view(B, -1), g["g_h0_lin/Matrix"], g["g_h0_lin/bias"])
 
     # ------------------------------------------------------------------------------------------------
     # optimizer
