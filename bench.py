@@ -1,0 +1,297 @@
+"""Headline benchmark: DCGAN train images/sec (D+G step, device-timed, max over ranks).
+
+Contract (driver): ``python bench.py --gpus N --steps K --warmup W`` (N>1: launched under
+``torch.distributed.run``, one rank per GPU).  Prints ONE JSON line on rank 0.
+
+Config = BASELINE.json config 2: DCGAN 64x64 (ngf=ndf=64, z=100), sync data-parallel, batch 64 per
+GPU, bf16 compute, synthetic images, random-init weights.
+
+Arms:
+  --impl ours       the B200 engine (hand-written sm_100a kernels, CUDA-graph replay)   [default]
+  --impl ddp        the PyTorch DDP + NCCL + cuDNN baseline of BASELINE.md (baseline/ddp_dcgan.py)
+  --impl reference  the unmodified reference from baseline/_ref (TensorFlow 0.x / Python 2: cannot be
+                    installed offline here -> prints {"impl": "reference", "unavailable": ...})
+
+Timing: W >= 3 warm-up steps; every timed step has its own CUDA-event pair on the launching stream
+and the L2 is flushed (256 MiB write) between steps, outside the pairs; the reported time is the sum
+over the K steps, max over ranks.  The e2e figure goes through the public ``train_step`` API with a
+pinned-host -> device copy of the step's inputs and a device -> host read of the losses every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "DCGAN train images/sec (D+G step, device-timed max over ranks)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "ddp", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="images per GPU (reference: 64, hard-coded)")
+    ap.add_argument("--comm", default="fused", choices=["fused", "nccl"], help="multi-GPU gradient path")
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--wide", action="store_true", help="128x128, ngf=ndf=128 (BASELINE.json config 3)")
+    ap.add_argument("--sync-bn", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i",
+                 str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def reference_arm(args):
+    """The reference is three Python-2 / TensorFlow-0.x scripts with no setup.py; see DESIGN.md."""
+    why = None
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    try:
+        sys.path.insert(0, ref_dir)
+        import tensorflow  # noqa: F401
+        why = "tensorflow imported but the reference needs the TF 0.x API (tf.train.Supervisor, tf.app.flags)"
+    except Exception as e:  # pragma: no cover - depends on the image
+        why = ("reference needs Python 2 + TensorFlow 0.7-0.8 (tf.train.Supervisor, tf.histogram_summary, "
+               f"`print len(image)`); no setup.py/pyproject to pip-install and tensorflow is not installable "
+               f"offline ({type(e).__name__})")
+    rank, _, _ = dist_env()
+    if rank == 0:
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+
+    rank, world, local = dist_env()
+    if args.gpus != world and rank == 0 and world > 1:
+        print(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}", file=sys.stderr)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    from distributed_tensorflow_for_dcgan_b200.config import ModelConfig
+    B = args.batch
+    if args.wide:
+        cfg = ModelConfig(output_size=128, gf_dim=128, df_dim=128, batch_size=B)
+    else:
+        cfg = ModelConfig(batch_size=B)
+    S = cfg.output_size
+    K_steps, W = args.steps, max(args.warmup, 3)
+
+    # synthetic data of the named shape, in pinned host memory (float32 NHWC like the reference feed)
+    gen = torch.Generator().manual_seed(1234 + rank)
+    n_host = 4
+    host_real = [torch.empty(B, S, S, 3).uniform_(-1, 1, generator=gen).pin_memory() for _ in range(n_host)]
+    host_z = [torch.empty(B, cfg.z_dim).uniform_(-1, 1, generator=gen).pin_memory() for _ in range(n_host)]
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+    launches_per_step = 0
+    if args.impl == "ours":
+        from distributed_tensorflow_for_dcgan_b200.engine import DCGANEngine
+        from distributed_tensorflow_for_dcgan_b200.ops import _lib, kernels as Kn
+        comm = None
+        if world > 1:
+            from distributed_tensorflow_for_dcgan_b200.parallel.sync_dp import make_comm
+            comm = make_comm(args.comm, dev, sync_bn=args.sync_bn)
+        eng = DCGANEngine(cfg, device=dev, seed=0, comm=comm)
+        if comm is not None:
+            comm.attach(eng)
+        c0 = _lib.launch_count
+        eng.real_f32.copy_(host_real[0]); eng.z.copy_(host_z[0])
+        eng.step_body()
+        launches_per_step = _lib.launch_count - c0
+        torch.cuda.synchronize()
+        if not args.no_graph:
+            eng.capture()
+
+        def device_step(i):
+            eng.run_step()
+
+        def e2e_step(i):
+            return eng.train_step(host_real[i % n_host], host_z[i % n_host])
+
+        def stage_inputs(i):
+            eng.real_f32.copy_(host_real[i % n_host], non_blocking=True)
+            eng.z.copy_(host_z[i % n_host], non_blocking=True)
+        parallelism = f"dp{world}" + ("" if world == 1 else f"-{args.comm}")
+    else:
+        from baseline.ddp_dcgan import BaselineTrainer
+        tr = BaselineTrainer(dev, world=world, batch=B, s=S, gf=cfg.gf_dim, df=cfg.df_dim, z_dim=cfg.z_dim,
+                             sync_bn=args.sync_bn)
+        d_real = torch.empty(B, 3, S, S, device=dev).contiguous(memory_format=torch.channels_last)
+        d_z = torch.empty(B, cfg.z_dim, device=dev)
+        stage_nhwc = torch.empty(B, S, S, 3, device=dev)
+        last = {}
+
+        def stage_inputs(i):
+            stage_nhwc.copy_(host_real[i % n_host], non_blocking=True)
+            d_real.copy_(stage_nhwc.permute(0, 3, 1, 2))
+            d_z.copy_(host_z[i % n_host], non_blocking=True)
+
+        def device_step(i):
+            last["l"] = tr.step(d_real, d_z)
+
+        def e2e_step(i):
+            stage_inputs(i)
+            dl, gl = tr.step(d_real, d_z)
+            return float(dl.item()), float(gl.item())
+        parallelism = f"ddp{world}"
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up ------------------------------------------------------------------------------------
+    for i in range(W):
+        stage_inputs(i)
+        device_step(i)
+    barrier()
+
+    # ---- device-timed region: K steps, one event pair per step, L2 flushed in between -----------------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K_steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(K_steps)]
+    barrier()
+    for i in range(K_steps):
+        stage_inputs(i)
+        flush.fill_(i & 0xff)
+        starts[i].record()
+        device_step(i)
+        ends[i].record()
+    barrier()
+    per_step = [s.elapsed_time(e) for s, e in zip(starts, ends)]
+    dev_ms = sum(per_step)
+
+    # ---- end-to-end region through the public API: H2D inputs + D2H losses every step ----------------
+    for i in range(2):
+        e2e_step(i)
+    barrier()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for i in range(K_steps):
+        out = e2e_step(i)
+    t1.record()
+    barrier()
+    e2e_ms = t0.elapsed_time(t1)
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([dev_ms, e2e_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = t.tolist()
+    if args.impl == "ours":
+        from distributed_tensorflow_for_dcgan_b200.ops import kernels as Kn
+        Kn.check_device_error()
+
+    if rank == 0:
+        gb = B * world
+        value = gb * K_steps / (dev_ms / 1e3)
+        e2e_value = gb * K_steps / (e2e_ms / 1e3)
+        base = None
+        try:
+            with open(os.path.join(ROOT, "baseline", "measured.json")) as f:
+                base = json.load(f).get("images_per_sec", {}).get(str(world))
+        except Exception:
+            pass
+        h2d = B * S * S * 3 * 4 + B * cfg.z_dim * 4
+        d2h = 3 * 4 + 8 if args.impl == "ours" else 8
+        line = {
+            "metric": METRIC, "value": round(value, 1), "unit": "images/s", "n_gpus": world,
+            "steps": K_steps, "warmup": W, "ms_per_step": round(dev_ms / K_steps, 4),
+            "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": (round(value / base, 3) if base else None),
+            "dtype": "bf16", "data": "synthetic (uniform [-1,1] images, random-init weights)",
+            "impl": args.impl,
+            "config": {"model": f"DCGAN {S}x{S} ngf={cfg.gf_dim} ndf={cfg.df_dim} z={cfg.z_dim}",
+                       "global_batch": gb, "batch_per_gpu": B, "seq_len": None, "parallelism": parallelism,
+                       "update_mode": "simultaneous", "cuda_graph": (args.impl == "ours" and not args.no_graph),
+                       "l2": "flushed between timed steps (256 MiB write outside the event pairs)",
+                       "step_ms_min_med_max": [round(min(per_step), 4), round(statistics.median(per_step), 4),
+                                               round(max(per_step), 4)]},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "ms_per_step": round(e2e_ms / K_steps, 4),
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": launches_per_step * K_steps if args.impl == "ours" else 0,
+            "launches_per_step": launches_per_step,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
