@@ -9,6 +9,8 @@
 // statistics for the two calls, so every kernel takes a group count and treats
 // group g = contiguous slab of rows_per_group rows.  The backward kernels take a third slab (the
 // g_loss gradient through D(fake)) that shares the statistics of slab 1 (stat_group map).
+#include <cstdio>
+
 #include "common.cuh"
 #include "../include/dcgan_b200.h"
 
@@ -370,3 +372,81 @@ int dcgan_act_bwd(const void* da, const void* a, void* dpre, float* dbias, int r
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// Allocation-free batch-norm forward.  No counterpart in the reference.
+//
+// dcgan_bn_stats + dcgan_bn_apply need a per-channel sum / sum-of-squares buffer between them, and
+// normally the caller supplies it.  Some callers have nowhere to get one from: a plain C host that was
+// handed its activation buffers by another runtime's memory pool and owns no allocator, or a service
+// loop whose latency budget rules out cudaMalloc because that call stalls the whole device.  For them
+// the buffer lives in the library image itself, below.
+//
+//   * Capacity: kStaticBnFloats floats (64 KiB).  groups * 2 * C must fit; larger requests are refused
+//     with DCGAN_ERR_LIMIT and a message on stderr.  Every GPU that loads the library carries these
+//     64 KiB until the process exits.
+//   * `g_static_bn_sums` is a device symbol.  In host code that name is only a stand-in; handing it to a
+//     kernel would make the kernel fault (or, where the GPU can reach host memory, scribble on the wrong
+//     memory).  The device address is looked up once per device with cudaGetSymbolAddress, with that
+//     device current, and that pointer is what the kernels receive.
+//   * The lookup happens inside the first call made on each device, so make that first call outside of
+//     any stream capture.
+//   * All calls share the one array and it still holds the previous call's sums, so each call clears
+//     the part it uses first (stream-ordered).  Two calls that overlap on the GPU -- different streams,
+//     or different host threads on the same device -- race on it; keep calls on one stream or serialise.
+//   * Nothing here calls cudaMalloc, cudaFree, or any routine that allocates.
+// =================================================================================================
+namespace dcgan {
+
+constexpr int kStaticBnFloats = 16384;
+static __device__ __align__(256) float g_static_bn_sums[kStaticBnFloats];
+
+static float* static_bn_scratch_for_current_device(cudaError_t* err) {
+  constexpr int kMaxDev = 64;
+  static float* per_device[kMaxDev] = {nullptr};
+  int dev = -1;
+  *err = cudaGetDevice(&dev);
+  if (*err != cudaSuccess) return nullptr;
+  if (dev < 0 || dev >= kMaxDev) { *err = cudaErrorInvalidDevice; return nullptr; }
+  if (per_device[dev] == nullptr) {
+    float* ptr = nullptr;
+    *err = cudaGetSymbolAddress((void**)&ptr, g_static_bn_sums);
+    if (*err != cudaSuccess) return nullptr;
+    per_device[dev] = ptr;
+  }
+  return per_device[dev];
+}
+
+}  // namespace dcgan
+
+extern "C" int dcgan_bn_forward_static(const void* x, void* y, const float* gamma, const float* beta,
+                                       float* saved, float* ema_mean, float* ema_var, int groups,
+                                       int rows_per_group, int C, float eps, float decay, int act,
+                                       cudaStream_t st) {
+  using namespace dcgan;
+  if (groups <= 0 || rows_per_group <= 0 || C <= 0 || C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
+  const size_t need = (size_t)groups * 2 * (size_t)C;
+  if (need > (size_t)kStaticBnFloats) {
+    fprintf(stderr,
+            "dcgan_bn_forward_static: groups*2*C = %zu floats exceeds the built-in scratch of %d floats; "
+            "use dcgan_bn_stats + dcgan_bn_apply with a caller-provided buffer instead\n",
+            need, kStaticBnFloats);
+    return DCGAN_ERR_LIMIT;
+  }
+  cudaError_t err = cudaSuccess;
+  float* sums = static_bn_scratch_for_current_device(&err);
+  if (sums == nullptr) {
+    fprintf(stderr, "dcgan_bn_forward_static: cudaGetSymbolAddress failed: %s\n", cudaGetErrorString(err));
+    return DCGAN_ERR_DRIVER;
+  }
+  if (cudaMemsetAsync(sums, 0, need * sizeof(float), st) != cudaSuccess) return DCGAN_ERR_LAUNCH;
+  const int rpb = pick_rows_per_block(rows_per_group, C, groups);
+  dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
+  bn_stats_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(reinterpret_cast<const __nv_bfloat16*>(x), sums,
+                                                                  rows_per_group, C, rpb);
+  if (cudaGetLastError() != cudaSuccess) return DCGAN_ERR_LAUNCH;
+  bn_apply_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, saved,
+      ema_mean, ema_var, rows_per_group, C, 1.0f / (float)rows_per_group, eps, decay, act, 0, rpb);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}

@@ -86,6 +86,16 @@ int dcgan_bn_bwd_reduce(const void* da, const void* pre, const float* saved, con
 int dcgan_bn_bwd_apply(const void* da, const void* pre, void* dpre, const float* saved, const float* gamma,
                        const float* beta, const float* red, float* dgamma, float* dbeta, int groups,
                        int stat_groups, int param_groups, int rows_per_group, int C, int act, cudaStream_t stream);
+/* Batch-norm forward (statistics + normalise + activation) for callers that cannot allocate memory.
+ * No counterpart in the reference.  Same result as dcgan_bn_stats followed by dcgan_bn_apply, but the
+ * per-channel sums live in a 64 KiB array built into the library (groups*2*C <= 16384 floats, otherwise
+ * DCGAN_ERR_LIMIT), so no buffer is asked of the caller and nothing is allocated.  Meant for hosts that
+ * only hold buffers lent by another runtime's pool, or that must not call cudaMalloc because it stalls
+ * the device.  The first call on each device looks the array's address up -- make it outside stream
+ * capture.  All calls share the array: it is cleared per call, and calls that overlap on the GPU race. */
+int dcgan_bn_forward_static(const void* x, void* y, const float* gamma, const float* beta, float* saved,
+                            float* ema_mean, float* ema_var, int groups, int rows_per_group, int C, float eps,
+                            float decay, int act, cudaStream_t stream);
 /* dpre = da * act'(a) for a layer without batch norm (d_h0), plus its bias gradient. */
 int dcgan_act_bwd(const void* da, const void* a, void* dpre, float* dbias, int rows, int a_rows, int C, int act,
                   int bias_rows, cudaStream_t stream);
