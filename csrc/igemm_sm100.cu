@@ -71,9 +71,19 @@ __device__ __forceinline__ uint32_t swz128(uint32_t row, uint32_t chunk) {
   return row * 128u + ((chunk ^ (row & 7u)) << 4);
 }
 
-__device__ __forceinline__ uint4 ldg16(const void* p) {
-  return __ldg(reinterpret_cast<const uint4*>(p));
+// 16-byte asynchronous global->shared copy (L2 only); src_bytes = 0 zero-fills (padding rows)
+__device__ __forceinline__ void cp_async_16(uint32_t smem_dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(src), "r"(src_bytes)
+               : "memory");
 }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// k-blocks whose gather copies are in flight per producer thread before the oldest is published
+constexpr int kGatherDepth = 3;
 
 template <int MODE, int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(kNumThreads, 1)
@@ -216,76 +226,80 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
       }
       const int cpt = p.gC / kBlockK;
       const int nkw = pw ? 3 : 2;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % STAGES;
-        const uint32_t phase = (kb / STAGES) & 1;
-        const int lt = kb / cpt;
-        const int c0 = (kb - lt * cpt) * kBlockK;
-        int dy, dx;
-        if (MODE == MODE_F) {
-          const int kh = lt / 5, kw = lt - kh * 5;
-          dy = kh - 1;
-          dx = kw - 1;
-        } else {
-          const int ikh = lt / nkw, ikw = lt - ikh * nkw;
-          const int kh = ph ? 2 * ikh : 2 * ikh + 1;
-          const int kw = pw ? 2 * ikw : 2 * ikw + 1;
-          dy = (ph + 1 - kh) / 2;  // exact: the numerator is even by construction
-          dx = (pw + 1 - kw) / 2;
-        }
-        uint4 v[8];
+      // cp.async pipeline: the copies of kGatherDepth k-blocks are in flight per thread; a k-block is
+      // published (proxy fence + mbarrier arrive) once its group has landed.
+      for (int it = 0; it < num_kb + kGatherDepth - 1; ++it) {
+        if (it < num_kb) {
+          const int kb = it;
+          const int s = kb % STAGES;
+          const uint32_t phase = (kb / STAGES) & 1;
+          const int lt = kb / cpt;
+          const int c0 = (kb - lt * cpt) * kBlockK;
+          int dy, dx;
+          if (MODE == MODE_F) {
+            const int kh = lt / 5, kw = lt - kh * 5;
+            dy = kh - 1;
+            dx = kw - 1;
+          } else {
+            const int ikh = lt / nkw, ikw = lt - ikh * nkw;
+            const int kh = ph ? 2 * ikh : 2 * ikh + 1;
+            const int kw = pw ? 2 * ikw : 2 * ikw + 1;
+            dy = (ph + 1 - kh) / 2;  // exact: the numerator is even by construction
+            dx = (pw + 1 - kw) / 2;
+          }
+          if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+          const uint32_t sA = smem_u32(smem + s * L::kStageBytes);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int y = (yx[i] >> 16) + dy;
-          const int x = (yx[i] & 0xffff) + dx;
-          const bool valid = pix_base[i] >= 0 && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW;
-          v[i] = make_uint4(0, 0, 0, 0);
-          if (valid) {
-            const size_t off = ((size_t)(pix_base[i] + y * p.gW + x)) * p.gC + c0 + chunk * 8;
-            v[i] = ldg16(p.g + off);
+          for (int i = 0; i < 8; ++i) {
+            const int y = (yx[i] >> 16) + dy;
+            const int x = (yx[i] & 0xffff) + dx;
+            const bool valid =
+                pix_base[i] >= 0 && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW;
+            const size_t off = valid ? ((size_t)(pix_base[i] + y * p.gW + x)) * p.gC + c0 + chunk * 8 : 0;
+            cp_async_16(sA + swz128(rbase + 16 * i, chunk), p.g + off, valid ? 16u : 0u);
           }
         }
-        if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
-        uint8_t* sA = smem + s * L::kStageBytes;
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-          *reinterpret_cast<uint4*>(sA + swz128(rbase + 16 * i, chunk)) = v[i];
-        fence_proxy_async_smem();
-        mbar_arrive(&full_bar[s]);
+        cp_async_commit();
+        if (it >= kGatherDepth - 1) {
+          cp_async_wait<kGatherDepth - 1>();
+          fence_proxy_async_smem();
+          mbar_arrive(&full_bar[(it - (kGatherDepth - 1)) % STAGES]);
+        }
       }
     } else {
       // W mode: rows are pixels of the K dimension and change every k-block
       const int kh = tap_fixed / 5, kw = tap_fixed - kh * 5;
       constexpr int kSub = BLOCK_N / 64;  // 64-channel sub-tiles of the gathered operand
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % STAGES;
-        const uint32_t phase = (kb / STAGES) & 1;
-        const int px0 = (kb_base + kb) * kBlockK;
-        uint4 v[4 * kSub];
+      for (int it = 0; it < num_kb + kGatherDepth - 1; ++it) {
+        if (it < num_kb) {
+          const int kb = it;
+          const int s = kb % STAGES;
+          const uint32_t phase = (kb / STAGES) & 1;
+          const int px0 = (kb_base + kb) * kBlockK;
+          if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+          const uint32_t sB = smem_u32(smem + s * L::kStageBytes + kATileBytes);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int R = px0 + rbase + 16 * i;
-          const int qw = R & (rW - 1);
-          const int qh = (R >> p.rW_log2) & (rH - 1);
-          const int n = R >> (p.rW_log2 + p.rH_log2);
-          const int y = 2 * qh + kh - 1, x = 2 * qw + kw - 1;
-          const bool valid = R < p.rows_total && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW;
-          const size_t off = ((size_t)((n * p.gH + y) * p.gW + x)) * p.gC + n0 + chunk * 8;
+          for (int i = 0; i < 4; ++i) {
+            const int R = px0 + rbase + 16 * i;
+            const int qw = R & (rW - 1);
+            const int qh = (R >> p.rW_log2) & (rH - 1);
+            const int n = R >> (p.rW_log2 + p.rH_log2);
+            const int y = 2 * qh + kh - 1, x = 2 * qw + kw - 1;
+            const bool valid =
+                R < p.rows_total && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW;
+            const size_t off = valid ? ((size_t)((n * p.gH + y) * p.gW + x)) * p.gC + n0 + chunk * 8 : 0;
 #pragma unroll
-          for (int j = 0; j < kSub; ++j) {
-            v[i * kSub + j] = make_uint4(0, 0, 0, 0);
-            if (valid) v[i * kSub + j] = ldg16(p.g + off + 64 * j);
+            for (int j = 0; j < kSub; ++j)
+              cp_async_16(sB + j * 8192 + swz128(rbase + 16 * i, chunk), p.g + off + (valid ? 64 * j : 0),
+                          valid ? 16u : 0u);
           }
         }
-        if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
-        uint8_t* sB = smem + s * L::kStageBytes + kATileBytes;
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int j = 0; j < kSub; ++j)
-            *reinterpret_cast<uint4*>(sB + j * 8192 + swz128(rbase + 16 * i, chunk)) = v[i * kSub + j];
-        fence_proxy_async_smem();
-        mbar_arrive(&full_bar[s]);
+        cp_async_commit();
+        if (it >= kGatherDepth - 1) {
+          cp_async_wait<kGatherDepth - 1>();
+          fence_proxy_async_smem();
+          mbar_arrive(&full_bar[(it - (kGatherDepth - 1)) % STAGES]);
+        }
       }
     }
 
@@ -447,12 +461,13 @@ static int dispatch_n(int block_n, const CUtensorMap& tmap, const IgemmParams& p
 }
 
 static int pick_block_n(int Cn, int rows_tiles, int extra_parallel) {
-  // prefer the widest tile that still gives at least ~1 wave of CTAs on 148 SMs
+  // the kernels are bound by L2 traffic of the im2col gather, so prefer the widest tile (fewest re-reads
+  // of the gathered operand) that still occupies most of the 148 SMs (measured: profiles/igemm_*.log)
   const int cands[3] = {256, 128, 64};
   for (int i = 0; i < 3; ++i) {
     const int bn = cands[i];
     if (Cn % bn) continue;
-    if ((long)rows_tiles * (Cn / bn) * extra_parallel >= 120 || bn == 64) return bn;
+    if ((long)rows_tiles * (Cn / bn) * extra_parallel >= 90 || bn == 64) return bn;
   }
   return (Cn % 64 == 0) ? 64 : -1;
 }
