@@ -1,0 +1,235 @@
+"""Training driver: role dispatch, supervisor, input pipeline and the step loop.
+
+The reference packs cluster bootstrap, graph build, supervision and the loop into one 144-line
+function (``train()``, image_train.py:51-194); here they are separate modules and this file only
+wires them, keeping the observable behaviour: flag dump, mkdirs (``main``, :222-230), the log line
+``Epoch: [%2d] step: [%2d] time: %4.4f, d_loss: %.8f, g_loss: %.8f`` (:160-162), the time-gated
+summaries (:163-178), the chief's 8x8 sample grid whenever ``step % 100 == 1`` (:179-192) and the
+``step < 1200000`` global budget (:150).
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+from . import flags as F
+from .config import steps_per_epoch
+from .parallel import cluster as cl
+from .supervisor import Supervisor
+from .utils import sample as S
+
+SAMPLE_SIZE = 64  # image_train.py:43
+
+
+def _make_reader(FLAGS, data_dir, batch_size, cfg, seed):
+    from .data import loader
+    if FLAGS.synthetic_data:
+        return loader.SyntheticImages(batch_size, cfg.output_size, cfg.c_dim, seed)
+    kw = {}
+    if FLAGS.shuffle_min_after_dequeue >= 0:
+        kw = dict(min_after_dequeue=FLAGS.shuffle_min_after_dequeue,
+                  capacity=FLAGS.shuffle_min_after_dequeue + 3 * batch_size)
+    return loader.distorted_inputs(data_dir, batch_size, cfg.output_size, cfg.c_dim, seed=seed,
+                                   num_threads=FLAGS.num_reader_threads, **kw)
+
+
+def run_ps(FLAGS, role, cfg) -> int:
+    """``server.join()`` (image_train.py:62-63)."""
+    use_cuda = _use_cuda(FLAGS)
+    if use_cuda:
+        # GPU mode: the parameter shards live in the workers' peer-mapped HBM; nothing to serve.
+        cl.init_process_group(role, "gloo")
+        import torch.distributed as dist
+        dist.barrier()   # start
+        dist.barrier()   # workers finished
+        cl.shutdown()
+        return 0
+    from .parallel.ps import PSServer
+    cl.init_process_group(role, "gloo")
+    workers = [role.cluster.worker_rank(i) for i in range(role.cluster.num_workers)]
+    server = PSServer(cfg, role.task_index, role.cluster.num_ps, workers, FLAGS.sync_replicas, FLAGS.learning_rate,
+                      FLAGS.beta1)
+    applies = server.serve()
+    print(f"ps {role.task_index}: served {applies} applies, global_step {server.global_step}")
+    cl.shutdown()
+    return 0
+
+
+def _use_cuda(FLAGS) -> bool:
+    if FLAGS.device == "cpu":
+        return False
+    if FLAGS.device == "cuda":
+        return True
+    return torch.cuda.is_available()
+
+
+def run_worker(FLAGS, role, cfg) -> int:
+    use_cuda = _use_cuda(FLAGS)
+    is_chief = role.is_chief
+    batch = cfg.batch_size
+    spe = steps_per_epoch(batch)
+    ps_client = None
+    comm = None
+    if use_cuda:
+        local = int(os.environ.get("LOCAL_RANK", role.task_index % max(torch.cuda.device_count(), 1)))
+        torch.cuda.set_device(local)
+        device = torch.device("cuda", local)
+        if role.distributed:
+            if role.cluster.num_ps:
+                # ps joiners are CPU-only processes: rendezvous them over gloo, workers among themselves on NCCL
+                raise SystemExit("GPU mode: launch workers only (parameter shards live on the worker GPUs); "
+                                 "omit --ps_hosts or use --device=cpu for the ps plumbing path")
+            cl.init_process_group(role, "nccl", device=device)
+            from .parallel.sync_dp import make_comm
+            if FLAGS.sync_replicas:
+                comm = make_comm(FLAGS.comm_backend, device, sync_bn=FLAGS.sync_bn)
+            else:
+                from .parallel.async_ps import AsyncPSComm
+                comm = AsyncPSComm(device)
+        from .trainer import EngineTrainer
+        trainer = EngineTrainer(cfg, FLAGS.learning_rate, FLAGS.beta1, FLAGS.seed, FLAGS.update_mode, device, comm,
+                                FLAGS.cuda_graph)
+    else:
+        from .trainer import CPUTrainer
+        allreduce_world = 1
+        if role.distributed:
+            cl.init_process_group(role, "gloo")
+        trainer = CPUTrainer(cfg, FLAGS.learning_rate, FLAGS.beta1, FLAGS.seed, FLAGS.update_mode)
+        if role.distributed and role.cluster.num_ps:
+            from .parallel.ps import PSClient
+            ps_client = PSClient(cfg, role.cluster.num_ps, trainer.params)
+            trainer.ps = ps_client
+        elif role.distributed:
+            trainer.allreduce_world = role.cluster.num_workers
+
+    sv = Supervisor(is_chief, FLAGS.checkpoint_dir, FLAGS.save_model_secs, FLAGS.save_summaries_secs,
+                    FLAGS.max_steps)
+    # ---- init or restore on the chief, everyone else waits for it (image_train.py:141-146) -----------------
+    restored = sv.init_or_restore(trainer)
+    if role.distributed:
+        import torch.distributed as dist
+        if ps_client is not None:
+            if is_chief:
+                ps_client.set_params(trainer.global_step, trainer.opt_d.t)
+                if restored:
+                    ps_client.set_slots(*trainer.adam_slots())
+            # workers wait for the chief's initialisation, then pull it
+            worker_group = _worker_barrier(role)
+            ps_client.pull()
+            trainer.global_step = ps_client.global_step
+        elif not use_cuda:
+            for t in trainer.params.values():
+                dist.broadcast(t, src=role.cluster.worker_rank(0))
+        elif restored or True:
+            # GPU sync path: comm.attach() already broadcast rank 0's arena; re-broadcast after a restore
+            if comm is not None and restored is not None:
+                dist.broadcast(trainer.engine.arena.master, src=0)
+                dist.broadcast(trainer.engine.arena.m, src=0)
+                dist.broadcast(trainer.engine.arena.v, src=0)
+                dist.broadcast(trainer.engine.counters, src=0)
+                trainer.engine.refresh_compute_weights()
+
+    replica = 0 if FLAGS.identical_replicas else role.task_index
+    images = _make_reader(FLAGS, FLAGS.data_dir, batch, cfg, FLAGS.seed + 17 * replica)
+    sample_images = None
+    rng = np.random.RandomState(FLAGS.seed + 1000 + replica)
+    sample_z = rng.uniform(-1, 1, size=(SAMPLE_SIZE, cfg.z_dim)).astype(np.float32)  # image_train.py:77
+    prefetch = None
+    if use_cuda:
+        from .data.loader import DevicePrefetcher
+        prefetch = DevicePrefetcher(images, batch, (cfg.output_size, cfg.output_size, cfg.c_dim), trainer.device)
+
+    step = trainer.global_step
+    start_time = time.time()
+    step_times = []
+    local_iters = 0
+    while sv.keep_going(step):
+        batch_z = rng.uniform(-1, 1, [batch, cfg.z_dim]).astype(np.float32)        # image_train.py:151-152
+        if prefetch is not None:
+            real_img = prefetch.next()
+        else:
+            real_img = images.dequeue_many(batch)                                   # sess.run(images), :153
+            if real_img.shape[0] < batch:
+                break
+        want_summary = sv.summary_due()
+        t0 = time.time()
+        d_real, d_fake, g_loss, step = trainer.train_step(real_img, batch_z, record=want_summary)
+        step_times.append(time.time() - t0)
+        local_iters += 1
+        if FLAGS.log_every and local_iters % FLAGS.log_every == 0:
+            print("Epoch: [%2d] step: [%2d] time: %4.4f, d_loss: %.8f, g_loss: %.8f"
+                  % (step // spe, step % spe, time.time() - start_time, d_fake + d_real, g_loss))
+        if want_summary:
+            summ = trainer.summaries(real_img, batch_z, (d_real, d_fake, g_loss)) if is_chief else b""
+            sv.summary_computed(summ, step)
+        if prefetch is not None:
+            prefetch.release()
+        if step % FLAGS.sample_every == 1 and is_chief:                               # image_train.py:179
+            if sample_images is None:
+                sample_dir = FLAGS.sample_image_dir if os.path.isdir(FLAGS.sample_image_dir) else FLAGS.data_dir
+                sample_images = _make_reader(FLAGS, sample_dir, batch, cfg, FLAGS.seed + 999)  # 2nd pipeline, :84
+            sample_image = sample_images.dequeue_many(batch)
+            grid = trainer.sample_grid(sample_z[:batch])
+            d1_loss, g1_loss = trainer.evaluate_losses(sample_image, sample_z[:batch])
+            S.save_merged(grid, S.sample_path(FLAGS.sample_dir, step, spe))
+            print("[Sample] d_loss: %.8f, g_loss: %.8f" % (d1_loss, g1_loss))
+        sv.maybe_checkpoint(trainer, step)
+
+    # ---- orderly shutdown -------------------------------------------------------------------------------------------
+    sv.maybe_checkpoint(trainer, step, force=True)
+    if FLAGS.profile and step_times:
+        st = np.array(step_times[min(3, len(step_times) - 1):])
+        print(f"[profile] {len(st)} steps: mean {st.mean()*1e3:.3f} ms, p50 {np.median(st)*1e3:.3f} ms, "
+              f"{batch / st.mean():.1f} images/s per worker")
+    if ps_client is not None:
+        ps_client.done()
+    if prefetch is not None:
+        prefetch.close()
+    sv.close()
+    if role.distributed:
+        if use_cuda and comm is not None and hasattr(comm, "close"):
+            comm.close()
+        cl.shutdown()
+    return 0
+
+
+def _worker_barrier(role):
+    """Barrier among workers only (ps tasks are busy serving): workers wait for the chief's init."""
+    import torch.distributed as dist
+    ranks = [role.cluster.worker_rank(i) for i in range(role.cluster.num_workers)]
+    # new_group is collective over the whole world in torch; ps tasks never call it, so use p2p tokens
+    chief = ranks[0]
+    token = torch.zeros(1)
+    if role.rank == chief:
+        for r in ranks[1:]:
+            dist.send(token, r)
+    else:
+        dist.recv(token, chief)
+    return None
+
+
+def train(FLAGS) -> int:
+    cfg = F.model_config_from_flags()
+    role = cl.resolve_role(FLAGS.job_name, FLAGS.task_index, FLAGS.ps_hosts, FLAGS.worker_hosts)
+    if role.is_ps:
+        return run_ps(FLAGS, role, cfg)
+    return run_worker(FLAGS, role, cfg)
+
+
+def main(argv=None) -> int:
+    from absl import flags as absl_flags
+    F.define_flags()
+    FLAGS = absl_flags.FLAGS
+    FLAGS(argv if argv is not None else sys.argv)
+    F.pprint_flags()                                      # image_train.py:223
+    os.makedirs(FLAGS.checkpoint_dir, exist_ok=True)      # :225-226
+    os.makedirs(FLAGS.sample_dir, exist_ok=True)          # :227-228
+    return train(FLAGS)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
