@@ -1,0 +1,318 @@
+// In-kernel collectives over NVLink 5 / NVSwitch peer memory -- no NCCL on these paths.
+//
+// These replace the reference's parameter-server traffic: the gradient *push*
+// (worker -> ps, image_train.py:109-112) and the parameter *pull* (ps -> worker, every read of a
+// ps-pinned variable, distriubted_model.py:70) that TensorFlow 0.x moved as gRPC Send/Recv.
+//
+//   rs_adam_ag      sync replicas: ONE kernel = reduce-scatter of the f32 gradients (P2P loads from every
+//                   peer, or an in-switch NVLS multimem.ld_reduce) + average + TF-form Adam on this rank's
+//                   parameter shard (the "ps shard": f32 master and both Adam slots stay sharded) +
+//                   all-gather of the updated bf16 parameters (P2P stores into every peer, or multimem.st).
+//   allreduce_small cross-GPU batch-norm statistics (sum, sum-of-squares / backward reductions).
+//   async_apply     asynchronous parameter-server mode: a worker applies its own stale gradients to the
+//                   owner's shard through peer memory (unlocked, like the reference's use_locking=False)
+//                   and keeps what it read as its fresh local copy.
+//
+// Signalling: every rank owns a small symmetric "signal pad"; a rank announces a phase by a
+// release-store of the epoch into its slot of every peer's pad and waits, bounded, for all slots of its
+// own pad.  Epochs live in device memory so the launches are CUDA-graph replayable.
+#include <cstdio>
+
+#include "common.cuh"
+#include "../include/dcgan_b200.h"
+
+namespace dcgan {
+
+constexpr int kMaxRanks = 16;
+constexpr int kCommThreads = 256;
+
+struct PeerTable {
+  void* buf_a[kMaxRanks];       // rs_adam_ag: f32 gradients        async: f32 master
+  void* buf_b[kMaxRanks];       // rs_adam_ag: bf16 parameters      async: bf16 parameters
+  void* buf_c[kMaxRanks];       // async: Adam m
+  void* buf_d[kMaxRanks];       // async: Adam v
+  unsigned* sig[kMaxRanks];     // signal pads
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_b64(void* mc, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};" ::"l"(mc), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y))
+               : "memory");
+}
+
+// bounded wait until every rank's slot in `mine` has reached `epoch`
+constexpr unsigned kPeerSpinLimit = 1u << 24;
+__device__ __forceinline__ bool wait_all(const unsigned* mine, int world, unsigned epoch, int* err_flag) {
+  bool ok = true;
+  if ((int)threadIdx.x < world) {
+    unsigned spins = 0;
+    while ((int)(ld_acquire_sys(mine + threadIdx.x) - epoch) < 0) {
+      if (++spins > kPeerSpinLimit) {
+        atomicExch(err_flag, (int)kErrPeerTimeout);
+        ok = false;
+        break;
+      }
+      __nanosleep(64);
+    }
+  }
+  return __syncthreads_and((int)ok) != 0;
+}
+
+// signal layout inside a pad: [slot][phase 0/1][src rank], kMaxRanks entries per row
+__device__ __forceinline__ unsigned* sig_row(unsigned* pad, int slot, int phase) {
+  return pad + ((size_t)slot * 2 + phase) * kMaxRanks;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// reduce-scatter + average + Adam + all-gather
+// state[0] = epoch of this slot, state[1] = finished-block counter
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCommThreads)
+rs_adam_ag_kernel(PeerTable peers, float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
+                  const long long* __restrict__ counters, unsigned* __restrict__ state, int rank, int world,
+                  size_t lo, size_t hi, float lr, float b1, float b2, float eps, int slot, int* err_flag,
+                  const float* mc_grad, __nv_bfloat16* mc_bf16) {
+  const unsigned epoch = state[0] + 1;
+  // ---- phase A: every rank's gradients are complete -------------------------------------------------------
+  if (blockIdx.x == 0 && (int)threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(sig_row(peers.sig[threadIdx.x], slot, 0) + rank, epoch);
+  }
+  const bool ok = wait_all(sig_row(peers.sig[rank], slot, 0), world, epoch, err_flag);
+
+  const float t = (float)counters[0];
+  const float lr_t = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
+  const float inv_world = 1.f / (float)world;
+  // shard of [lo, hi) owned by this rank (multiples of 4 elements)
+  const size_t total4 = (hi - lo) / 4;
+  const size_t per4 = (total4 + world - 1) / world;
+  const size_t s0 = lo + min((size_t)rank * per4, total4) * 4;
+  const size_t s1 = lo + min((size_t)(rank + 1) * per4, total4) * 4;
+  if (ok) {
+    for (size_t i = s0 + ((size_t)blockIdx.x * kCommThreads + threadIdx.x) * 4; i < s1;
+         i += (size_t)gridDim.x * kCommThreads * 4) {
+      float4 g;
+      if (mc_grad != nullptr) {
+        g = multimem_ld_reduce_f4(mc_grad + i);  // summed inside the NVSwitch
+      } else {
+        g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+        for (int r = 0; r < world; ++r) {
+          const float4 x = ld_peer_f4(reinterpret_cast<const float*>(peers.buf_a[(rank + r) % world]) + i);
+          g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+        }
+      }
+      float4 pv = *reinterpret_cast<float4*>(master + i);
+      float4 mv = *reinterpret_cast<float4*>(m + i);
+      float4 vv = *reinterpret_cast<float4*>(v + i);
+      float* gp = &g.x; float* pp = &pv.x; float* mp = &mv.x; float* vp = &vv.x;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float gj = gp[j] * inv_world;
+        mp[j] = b1 * mp[j] + (1.f - b1) * gj;
+        vp[j] = b2 * vp[j] + (1.f - b2) * gj * gj;
+        pp[j] -= lr_t * mp[j] / (sqrtf(vp[j]) + eps);
+      }
+      *reinterpret_cast<float4*>(master + i) = pv;
+      *reinterpret_cast<float4*>(m + i) = mv;
+      *reinterpret_cast<float4*>(v + i) = vv;
+      const uint2 packed = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+      if (mc_bf16 != nullptr) {
+        multimem_st_b64(mc_bf16 + i, packed);  // one store, every rank's copy
+      } else {
+#pragma unroll 4
+        for (int r = 0; r < world; ++r)
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[(rank + r) % world]) + i) = packed;
+      }
+    }
+  }
+  // ---- phase B: every owner's parameters have landed everywhere ----------------------------------------------
+  __syncthreads();
+  __shared__ int is_last;
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    is_last = (atomicAdd(&state[1], 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last) {
+    if ((int)threadIdx.x < world) {
+      __threadfence_system();
+      st_release_sys(sig_row(peers.sig[threadIdx.x], slot, 1) + rank, epoch);
+    }
+    wait_all(sig_row(peers.sig[rank], slot, 1), world, epoch, err_flag);
+    if (threadIdx.x == 0) {
+      state[1] = 0;
+      state[0] = epoch;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// small all-reduce (mean) for batch-norm statistics: one block.  staging[rank] is this rank's symmetric
+// staging area (double-buffered by epoch parity, so one signal phase per call is enough).
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_small_kernel(PeerTable peers /* buf_a = staging */, float* __restrict__ data, int n, int staging_stride,
+                       unsigned* __restrict__ state, int rank, int world, int slot, int* err_flag) {
+  const unsigned epoch = state[0] + 1;
+  const int parity = epoch & 1;
+  float* mine = reinterpret_cast<float*>(peers.buf_a[rank]) + (size_t)parity * staging_stride;
+  for (int i = threadIdx.x; i < n; i += kCommThreads) mine[i] = data[i];
+  __syncthreads();
+  if ((int)threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(sig_row(peers.sig[threadIdx.x], slot, 0) + rank, epoch);
+  }
+  const bool ok = wait_all(sig_row(peers.sig[rank], slot, 0), world, epoch, err_flag);
+  if (ok) {
+    const float inv = 1.f / (float)world;
+    for (int i = threadIdx.x; i < n; i += kCommThreads) {
+      float s = 0.f;
+      for (int r = 0; r < world; ++r) {
+        const float* src = reinterpret_cast<const float*>(peers.buf_a[r]) + (size_t)parity * staging_stride + i;
+        float x;
+        asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(x) : "l"(src) : "memory");
+        s += x;
+      }
+      data[i] = s * inv;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) state[0] = epoch;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// asynchronous parameter-server apply: this worker's gradients -> Adam on the owners' shards over P2P.
+// No barrier, no lock: concurrent workers may interleave on an element, as in the reference.
+// step_counters (on every rank; the owner's copy counts): [0] = Adam t of that shard, rank 0's [1] = global_step.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCommThreads)
+async_apply_kernel(PeerTable peers, const float* __restrict__ grad, __nv_bfloat16* __restrict__ local_bf16,
+                   long long* const* __restrict__ peer_counters, int rank, int world, size_t n, float lr, float b1,
+                   float b2, float eps) {
+  const size_t total4 = n / 4;
+  const size_t per4 = (total4 + world - 1) / world;
+  __shared__ float s_lr_t[kMaxRanks];
+  if ((int)threadIdx.x < world) {
+    // every pusher advances the owner's step count (beta powers advance per apply, like TF's shared
+    // beta1_power); block 0 does the increment, the others read a possibly older value
+    long long* c = peer_counters[threadIdx.x];
+    long long t;
+    if (blockIdx.x == 0) {
+      t = atomicAdd_system(reinterpret_cast<unsigned long long*>(c), 1ull) + 1;
+      if (threadIdx.x == 0) atomicAdd_system(reinterpret_cast<unsigned long long*>(peer_counters[0] + 1), 1ull);
+    } else {
+      t = *reinterpret_cast<volatile long long*>(c) + 1;
+    }
+    const float tf = (float)(t < 1 ? 1 : t);
+    s_lr_t[threadIdx.x] = lr * sqrtf(1.f - powf(b2, tf)) / (1.f - powf(b1, tf));
+  }
+  __syncthreads();
+  for (size_t i4 = (size_t)blockIdx.x * kCommThreads + threadIdx.x; i4 < total4;
+       i4 += (size_t)gridDim.x * kCommThreads) {
+    const int owner = (int)min(i4 / per4, (size_t)(world - 1));
+    const size_t i = i4 * 4;
+    float* P = reinterpret_cast<float*>(peers.buf_a[owner]) + i;
+    float* M = reinterpret_cast<float*>(peers.buf_c[owner]) + i;
+    float* V = reinterpret_cast<float*>(peers.buf_d[owner]) + i;
+    float4 pv = ld_peer_f4(P), mv = ld_peer_f4(M), vv = ld_peer_f4(V);
+    const float4 g = *reinterpret_cast<const float4*>(grad + i);
+    const float* gp = &g.x; float* pp = &pv.x; float* mp = &mv.x; float* vp = &vv.x;
+    const float lr_t = s_lr_t[owner];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      mp[j] = b1 * mp[j] + (1.f - b1) * gp[j];
+      vp[j] = b2 * vp[j] + (1.f - b2) * gp[j] * gp[j];
+      pp[j] -= lr_t * mp[j] / (sqrtf(vp[j]) + eps);
+    }
+    *reinterpret_cast<float4*>(P) = pv;
+    *reinterpret_cast<float4*>(M) = mv;
+    *reinterpret_cast<float4*>(V) = vv;
+    const uint2 packed = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+    *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[owner]) + i) = packed;
+    if (owner != rank) *reinterpret_cast<uint2*>(local_bf16 + i) = packed;  // what we just read is our fresh pull
+  }
+}
+
+static void fill(void** dst, const void* const* src, int world) {
+  for (int i = 0; i < kMaxRanks; ++i) dst[i] = i < world ? const_cast<void*>(src[i]) : nullptr;
+}
+
+}  // namespace dcgan
+
+using namespace dcgan;
+
+extern "C" {
+
+int dcgan_comm_rs_adam_ag(const void* const* grad_ptrs, const void* const* bf16_ptrs, const void* const* sig_ptrs,
+                          float* master, float* m, float* v, const long long* counters, unsigned* state, int rank,
+                          int world, size_t lo, size_t hi, float lr, float b1, float b2, float eps, int slot,
+                          const float* mc_grad, void* mc_bf16, int blocks, cudaStream_t st) {
+  if (world < 1 || world > kMaxRanks || (lo % 4) || (hi % 4) || hi < lo) return DCGAN_ERR_SHAPE;
+  PeerTable t{};
+  fill(t.buf_a, grad_ptrs, world);
+  fill(t.buf_b, bf16_ptrs, world);
+  fill(reinterpret_cast<void**>(t.sig), sig_ptrs, world);
+  int* err = error_flag_ptr();
+  if (!err) return DCGAN_ERR_DRIVER;
+  if (blocks <= 0) blocks = 32;
+  rs_adam_ag_kernel<<<blocks, kCommThreads, 0, st>>>(t, master, m, v, counters, state, rank, world, lo, hi, lr, b1,
+                                                     b2, eps, slot, err, mc_grad,
+                                                     reinterpret_cast<__nv_bfloat16*>(mc_bf16));
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_comm_allreduce_small(const void* const* staging_ptrs, const void* const* sig_ptrs, float* data, int n,
+                               int staging_stride, unsigned* state, int rank, int world, int slot,
+                               cudaStream_t st) {
+  if (world < 1 || world > kMaxRanks || n > staging_stride) return DCGAN_ERR_SHAPE;
+  PeerTable t{};
+  fill(t.buf_a, staging_ptrs, world);
+  fill(reinterpret_cast<void**>(t.sig), sig_ptrs, world);
+  int* err = error_flag_ptr();
+  if (!err) return DCGAN_ERR_DRIVER;
+  allreduce_small_kernel<<<1, kCommThreads, 0, st>>>(t, data, n, staging_stride, state, rank, world, slot, err);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_comm_async_apply(const void* const* master_ptrs, const void* const* bf16_ptrs, const void* const* m_ptrs,
+                           const void* const* v_ptrs, const float* grad, void* local_bf16,
+                           long long* const* peer_counters_dev, int rank, int world, size_t n, float lr, float b1,
+                           float b2, float eps, int blocks, cudaStream_t st) {
+  if (world < 1 || world > kMaxRanks || (n % 4)) return DCGAN_ERR_SHAPE;
+  PeerTable t{};
+  fill(t.buf_a, master_ptrs, world);
+  fill(t.buf_b, bf16_ptrs, world);
+  fill(t.buf_c, m_ptrs, world);
+  fill(t.buf_d, v_ptrs, world);
+  if (blocks <= 0) blocks = 148;
+  async_apply_kernel<<<blocks, kCommThreads, 0, st>>>(t, grad, reinterpret_cast<__nv_bfloat16*>(local_bf16),
+                                                      peer_counters_dev, rank, world, n, lr, b1, b2, eps);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+}  // extern "C"

@@ -31,7 +31,7 @@ from .ops import kernels as K
 class ParamArena:
     """Flat f32 master / grad / Adam buffers with TF-named, TF-layout views."""
 
-    def __init__(self, cfg: ModelConfig, device, pad_to: int = 1024):
+    def __init__(self, cfg: ModelConfig, device, pad_to: int = 1024, alloc=None):
         self.specs = manifest.trainable_specs(cfg)
         self.offsets: Dict[str, Tuple[int, Tuple[int, ...]]] = {}
         off = 0
@@ -41,11 +41,12 @@ class ParamArena:
         self.numel = off
         self.padded = (off + pad_to - 1) // pad_to * pad_to
         self.g_end = self.offsets["d_h0_conv/w"][0]  # generator variables come first
-        f32 = dict(dtype=torch.float32, device=device)
-        self.master = torch.zeros(self.padded, **f32)
-        self.m = torch.zeros(self.padded, **f32)
-        self.v = torch.zeros(self.padded, **f32)
-        self.bf16 = torch.zeros(self.padded, dtype=torch.bfloat16, device=device)
+        if alloc is None:
+            alloc = lambda name, numel, dtype: torch.zeros(numel, dtype=dtype, device=device)
+        self.master = alloc("master", self.padded, torch.float32)
+        self.m = alloc("adam_m", self.padded, torch.float32)
+        self.v = alloc("adam_v", self.padded, torch.float32)
+        self.bf16 = alloc("bf16", self.padded, torch.bfloat16)
 
     def view(self, flat: torch.Tensor, name: str) -> torch.Tensor:
         off, shape = self.offsets[name]
@@ -70,7 +71,12 @@ class DCGANEngine:
         self.update_mode = update_mode
         self.comm = comm
         self.B = B = cfg.batch_size
-        self.arena = A = ParamArena(cfg, self.device)
+        # the communication backend may hand out peer-mapped (symmetric) memory for the buffers it touches
+        alloc = None
+        if comm is not None and hasattr(comm, "alloc"):
+            alloc = lambda name, numel, dtype: comm.alloc(name, numel, dtype)
+        pad_to = 1024 * (comm.world if comm is not None and hasattr(comm, "world") else 1)
+        self.arena = A = ParamArena(cfg, self.device, pad_to=pad_to, alloc=alloc)
         self.params = A.named(A.master)
         src = init if init is not None else dcgan.init_params(cfg, seed=seed)
         for n, t in self.params.items():
@@ -100,7 +106,8 @@ class DCGANEngine:
             a, b = site_sizes(self.d_ch[i + 1], 2, 3)
             self._bn_off[f"d_bn{i}"] = (scratch, scratch + a)
             scratch += a + b
-        self.zero_region = torch.zeros(A.padded + scratch, **f32)
+        self.zero_region = (alloc("zero_region", A.padded + scratch, torch.float32) if alloc is not None
+                            else torch.zeros(A.padded + scratch, **f32))
         self.grads = self.zero_region[:A.padded]
         self.grad_views = A.named(self.grads)
         self._scratch = self.zero_region[A.padded:]
@@ -148,7 +155,8 @@ class DCGANEngine:
         self.probs = torch.zeros(2 * B, **f32)
         self.losses = torch.zeros(3, **f32)
         self.dlogit = torch.zeros(3 * B, **f32)
-        self.counters = torch.zeros(2, dtype=torch.int64, device=dev)  # [adam_t, global_step]
+        self.counters = (alloc("counters", 2, torch.int64) if alloc is not None
+                         else torch.zeros(2, dtype=torch.int64, device=dev))  # [adam_t, global_step]
         # gradients w.r.t. activations (3 slabs through D, 1 through G)
         self.dd_act = [torch.zeros(3 * B, *t.shape[1:], **bf) for t in self.d_act]
         self.dd_pre = [torch.zeros(3 * B, *t.shape[1:], **bf) for t in self.d_act]
@@ -295,8 +303,16 @@ class DCGANEngine:
         K.gan_loss(self.logits, self.losses, self.dlogit, self.probs, self.counters, B, 1.0, True)
         self.discriminator_backward()
         if self.update_mode == "simultaneous":
-            self.generator_backward()
-            self.optimizer_step("both")
+            if self.comm is not None and getattr(self.comm, "overlap", False):
+                # D's gradient exchange + Adam runs on the communication stream under G's backward pass
+                self.comm.launch_bucket(self, "d", side_stream=True)
+                self.generator_backward()
+                self.comm.launch_bucket(self, "g", side_stream=False)
+                self.comm.join()
+                self.refresh_compute_weights(cast=False)
+            else:
+                self.generator_backward()
+                self.optimizer_step("both")
         else:
             # D first, then G against the updated D (carpedm20-style alternation)
             self.optimizer_step("d")
@@ -373,8 +389,11 @@ class DCGANEngine:
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
         """TF-named checkpoint contents: weights, EMA shadows, global_step, and the Adam slots under
-        TensorFlow's slot names."""
+        TensorFlow's slot names.  With sharded optimizer state (multi-GPU) this is a
+        collective: every rank must call it."""
         A = self.arena
+        if self.comm is not None and hasattr(self.comm, "gather_state"):
+            self.comm.gather_state(self)
         sd = {n: t.detach().clone() for n, t in self.params.items()}
         sd.update({n: t.detach().clone() for n, t in self.ema_named().items()})
         sd[manifest.GLOBAL_STEP_NAME] = self.counters[1].to(torch.int32).clone()

@@ -1,0 +1,91 @@
+"""Asynchronous parameter-server mode on GPUs (BASELINE.json config 4).
+
+Rank r *owns* shard r of the flat parameter space -- f32 master weights and both Adam slots -- in
+peer-mapped HBM: that is the "variables live on the ps job" placement of the reference
+(distriubted_model.py:66-72) with real sharding.  After its backward pass a worker runs one kernel
+(csrc/comm_sm100.cu: ``async_apply_kernel``) that, for every element, loads (p, m, v) from the owner
+over NVLink, applies TF-form Adam with its *own* gradient -- stale with respect to whatever the other
+workers did meanwhile -- stores the result back and keeps the value as its fresh local bf16 copy.
+There is no barrier, no lock and no aggregation, like the reference's ``use_locking=False`` applies
+(SURVEY.md 2.3); ``global_step`` (rank 0) and the per-shard Adam step count advance once per push.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+from .fused_comm import _ptr_array
+
+
+class AsyncPSComm:
+    overlap = False
+    sync_bn = False
+
+    def __init__(self, device, blocks: int = 148):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.symm_mem = symm_mem
+        self.device, self.blocks = device, blocks
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.group = dist.group.WORLD
+        self.handles: Dict[str, object] = {}
+
+    def _symmetric(self, name: str, numel: int, dtype) -> torch.Tensor:
+        t = self.symm_mem.empty(numel, dtype=dtype, device=self.device)
+        t.zero_()
+        torch.cuda.synchronize(self.device)
+        self.handles[name] = self.symm_mem.rendezvous(t, self.group.group_name)
+        return t
+
+    def alloc(self, name: str, numel: int, dtype) -> torch.Tensor:
+        if name in ("master", "adam_m", "adam_v", "bf16"):
+            return self._symmetric(name, numel, dtype)
+        return torch.zeros(numel, dtype=dtype, device=self.device)
+
+    def attach(self, engine) -> None:
+        A = engine.arena
+        dist.broadcast(A.master, src=0)
+        engine.refresh_compute_weights()
+        self._p = _ptr_array(self.handles["master"].buffer_ptrs)
+        self._b = _ptr_array(self.handles["bf16"].buffer_ptrs)
+        self._m = _ptr_array(self.handles["adam_m"].buffer_ptrs)
+        self._v = _ptr_array(self.handles["adam_v"].buffer_ptrs)
+        # per-shard push counters ([0] = Adam t of this rank's shard, rank 0's [1] = global_step), symmetric
+        self.shard_counters = self._symmetric("shard_counters", 2, torch.int64)
+        self._counter_ptrs = torch.tensor([int(p) for p in self.handles["shard_counters"].buffer_ptrs],
+                                          dtype=torch.int64, device=self.device)
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+
+    def optimizer_step(self, engine, which: str = "both") -> None:
+        A = engine.arena
+        _lib.call("dcgan_comm_async_apply", self._p, self._b, self._m, self._v, engine.grads.data_ptr(),
+                  A.bf16.data_ptr(), self._counter_ptrs.data_ptr(), self.rank, self.world, A.padded, engine.lr,
+                  engine.beta1, engine.beta2, engine.eps, self.blocks)
+
+    def global_step(self) -> int:
+        """Applies of all workers so far (rank 0's counter, read through peer memory)."""
+        torch.cuda.synchronize(self.device)
+        if self.rank == 0:
+            return int(self.shard_counters[1].item())
+        return -1
+
+    def gather_state(self, engine) -> None:
+        """Collective: every rank copies the owners' shards (call at a quiescent point)."""
+        A = engine.arena
+        total4 = A.padded // 4
+        per4 = (total4 + self.world - 1) // self.world
+        mask = torch.zeros(A.padded, dtype=torch.bool, device=self.device)
+        mask[min(self.rank * per4, total4) * 4:min((self.rank + 1) * per4, total4) * 4] = True
+        dist.barrier()
+        for t in (A.master, A.m, A.v):
+            tmp = torch.where(mask, t, torch.zeros_like(t))
+            dist.all_reduce(tmp)
+            t.copy_(tmp)
+
+    def close(self) -> None:
+        torch.cuda.synchronize(self.device)
+        dist.barrier()

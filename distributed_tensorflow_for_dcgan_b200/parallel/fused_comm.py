@@ -1,0 +1,153 @@
+"""Fused communication over NVLink peer memory (the product path; NCCL is only the baseline).
+
+``FusedComm`` plugs into the engine as ``engine.comm``:
+
+* it hands the engine *symmetric* (peer-mapped) memory for the buffers other ranks must reach -- the
+  flat gradient region and the bf16 parameter copy -- allocated and exchanged once with
+  ``torch.distributed._symmetric_memory`` (``torch.distributed`` is the plumbing; no collective runs
+  through it on the hot path);
+* ``launch_bucket`` runs ONE kernel per bucket (D variables, G variables) that does the gradient
+  reduce-scatter + average + partitioned TF-form Adam + bf16 parameter all-gather
+  (csrc/comm_sm100.cu: ``rs_adam_ag_kernel``); the D bucket is launched on a side stream as soon as
+  D's backward is done, so it overlaps G's backward pass;
+* f32 master weights and both Adam slots exist only on the owning rank's shard -- the B200 analogue of
+  the reference's variables-on-ps placement with real sharding; ``gather_state``
+  reassembles them for checkpoints;
+* ``allreduce_bn`` averages batch-norm statistics across replicas (BASELINE.json config 3).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+
+SLOT_G, SLOT_D, SLOT_BN = 0, 1, 2
+N_SLOTS = 4
+MAX_RANKS = 16
+BN_STAGING = 8192  # floats per parity (largest site: 3 slabs x 2 x 1024 channels)
+
+
+def _ptr_array(ptrs):
+    arr = (ctypes.c_void_p * len(ptrs))(*[int(p) for p in ptrs])
+    return arr
+
+
+class FusedComm:
+    def __init__(self, device, sync_bn: bool = False, overlap: bool = True, use_multicast: bool = True,
+                 blocks: int = 32):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.symm_mem = symm_mem
+        self.device, self.sync_bn, self.overlap = device, sync_bn, overlap
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        if self.world > MAX_RANKS:
+            raise ValueError(f"at most {MAX_RANKS} ranks per NVLink domain")
+        self.group = dist.group.WORLD
+        self.handles: Dict[str, object] = {}
+        self.tensors: Dict[str, torch.Tensor] = {}
+        self.use_multicast = use_multicast
+        self.blocks = blocks
+        self.stream = torch.cuda.Stream(device)
+        self._fork_event = torch.cuda.Event()
+        self._join_event = torch.cuda.Event()
+        self._forked = False
+        # control block: signal pads + batch-norm staging, symmetric
+        self.sig = self._symmetric("signals", N_SLOTS * 2 * MAX_RANKS, torch.int32)
+        self.bn_staging = self._symmetric("bn_staging", 2 * BN_STAGING, torch.float32)
+        self.state = torch.zeros(N_SLOTS, 2, dtype=torch.int32, device=device)
+        self._sig_ptrs = _ptr_array(self.handles["signals"].signal_ptrs if False else self.handles["signals"].buffer_ptrs)
+        self._bn_ptrs = _ptr_array(self.handles["bn_staging"].buffer_ptrs)
+
+    # ---- symmetric allocation -----------------------------------------------------------------------------------
+    def _symmetric(self, name: str, numel: int, dtype) -> torch.Tensor:
+        t = self.symm_mem.empty(numel, dtype=dtype, device=self.device)
+        t.zero_()
+        torch.cuda.synchronize(self.device)
+        self.handles[name] = self.symm_mem.rendezvous(t, self.group.group_name)
+        self.tensors[name] = t
+        return t
+
+    def alloc(self, name: str, numel: int, dtype) -> torch.Tensor:
+        """Engine allocation hook: buffers that peers read or write live in symmetric memory."""
+        if name in ("zero_region", "bf16"):
+            return self._symmetric(name, numel, dtype)
+        return torch.zeros(numel, dtype=dtype, device=self.device)
+
+    def attach(self, engine) -> None:
+        A = engine.arena
+        dist.broadcast(A.master, src=0)  # one-time: the chief's initialisation (image_train.py:117,125)
+        engine.refresh_compute_weights()
+        self._grad_ptrs = _ptr_array(self.handles["zero_region"].buffer_ptrs)
+        self._bf16_ptrs = _ptr_array(self.handles["bf16"].buffer_ptrs)
+        hg, hb = self.handles["zero_region"], self.handles["bf16"]
+        mc_ok = self.use_multicast and getattr(hg, "has_multicast_support", False) and hg.multicast_ptr and hb.multicast_ptr
+        self.mc_grad = int(hg.multicast_ptr) if mc_ok else None
+        self.mc_bf16 = int(hb.multicast_ptr) if mc_ok else None
+        self.buckets = {"g": (0, A.g_end), "d": (A.g_end, A.padded), "both": None}
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+
+    # ---- the fused optimizer step ---------------------------------------------------------------------------------
+    def _launch(self, engine, which: str) -> None:
+        A = engine.arena
+        lo, hi = self.buckets[which]
+        slot = SLOT_G if which == "g" else SLOT_D
+        _lib.call("dcgan_comm_rs_adam_ag", self._grad_ptrs, self._bf16_ptrs, self._sig_ptrs, A.master.data_ptr(),
+                  A.m.data_ptr(), A.v.data_ptr(), engine.counters.data_ptr(), self.state[slot].data_ptr(), self.rank,
+                  self.world, lo, hi, engine.lr, engine.beta1, engine.beta2, engine.eps, slot, self.mc_grad,
+                  self.mc_bf16, self.blocks)
+
+    def launch_bucket(self, engine, which: str, side_stream: bool) -> None:
+        if side_stream:
+            cur = torch.cuda.current_stream(self.device)
+            self._fork_event.record(cur)
+            self.stream.wait_event(self._fork_event)
+            with torch.cuda.stream(self.stream):
+                self._launch(engine, which)
+                self._join_event.record(self.stream)
+            self._forked = True
+        else:
+            self._launch(engine, which)
+
+    def join(self) -> None:
+        if self._forked:
+            torch.cuda.current_stream(self.device).wait_event(self._join_event)
+            self._forked = False
+
+    def optimizer_step(self, engine, which: str = "both") -> None:
+        for w in (("d", "g") if which == "both" else (which,)):
+            self._launch(engine, w)
+
+    # ---- cross-replica batch norm -----------------------------------------------------------------------------------
+    def allreduce_bn(self, buf: torch.Tensor) -> None:
+        n = buf.numel()
+        assert n <= BN_STAGING
+        _lib.call("dcgan_comm_allreduce_small", self._bn_ptrs, self._sig_ptrs, buf.data_ptr(), n, BN_STAGING,
+                  self.state[SLOT_BN].data_ptr(), self.rank, self.world, SLOT_BN)
+
+    # ---- sharded state -> full state (checkpoints) ---------------------------------------------------------------------
+    def owned_mask(self, engine) -> torch.Tensor:
+        A = engine.arena
+        mask = torch.zeros(A.padded, dtype=torch.bool, device=self.device)
+        for lo, hi in (self.buckets["g"], self.buckets["d"]):
+            total4 = (hi - lo) // 4
+            per4 = (total4 + self.world - 1) // self.world
+            s0 = lo + min(self.rank * per4, total4) * 4
+            s1 = lo + min((self.rank + 1) * per4, total4) * 4
+            mask[s0:s1] = True
+        return mask
+
+    def gather_state(self, engine) -> None:
+        """Collective: fills every rank's master / Adam slots with the owners' values."""
+        A = engine.arena
+        mask = self.owned_mask(engine)
+        for t in (A.master, A.m, A.v):
+            tmp = torch.where(mask, t, torch.zeros_like(t))
+            dist.all_reduce(tmp)
+            t.copy_(tmp)
+
+    def close(self) -> None:
+        torch.cuda.synchronize(self.device)

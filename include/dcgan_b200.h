@@ -126,6 +126,28 @@ int dcgan_f32_to_bf16(const float* src, void* dst, size_t n, float scale, float 
 int dcgan_grid_merge(const void* img, float* out, int N, int H, int W, int C, int cols, cudaStream_t stream);
 int dcgan_count_zeros(const void* x, unsigned long long* count, size_t n, cudaStream_t stream);
 
+/* ---- in-kernel collectives over NVLink peer memory (csrc/comm_sm100.cu) --------------------------------
+ * Replace the reference's gRPC parameter push/pull.  *_ptrs are host arrays of `world`
+ * device pointers (one per rank, peer-mapped symmetric buffers); `state` is 2 local uint32 per slot. */
+
+/* Sync replicas: reduce-scatter of f32 gradients + average + TF-form Adam on this rank's shard of
+ * [lo,hi) + all-gather of the updated bf16 parameters, in one kernel.  mc_* = NVLS multicast addresses
+ * of the gradient / bf16 buffers or NULL for plain P2P loads and stores. */
+int dcgan_comm_rs_adam_ag(const void* const* grad_ptrs, const void* const* bf16_ptrs, const void* const* sig_ptrs,
+                          float* master, float* m, float* v, const long long* counters, unsigned* state, int rank,
+                          int world, size_t lo, size_t hi, float lr, float b1, float b2, float eps, int slot,
+                          const float* mc_grad, void* mc_bf16, int blocks, cudaStream_t stream);
+/* Mean all-reduce of a small f32 vector (cross-GPU batch-norm statistics). */
+int dcgan_comm_allreduce_small(const void* const* staging_ptrs, const void* const* sig_ptrs, float* data, int n,
+                               int staging_stride, unsigned* state, int rank, int world, int slot,
+                               cudaStream_t stream);
+/* Async parameter-server mode: apply this worker's gradients to the owners' shards through peer memory
+ * (unlocked, stale -- reference image_train.py:109-112 with use_locking=False) and refresh the local copy. */
+int dcgan_comm_async_apply(const void* const* master_ptrs, const void* const* bf16_ptrs, const void* const* m_ptrs,
+                           const void* const* v_ptrs, const float* grad, void* local_bf16,
+                           long long* const* peer_counters_dev, int rank, int world, size_t n, float lr, float b1,
+                           float b2, float eps, int blocks, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
