@@ -156,6 +156,7 @@ def main():
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
 
     launches_per_step = 0
+    use_graph = False
     if args.impl == "ours":
         from distributed_tensorflow_for_dcgan_b200.engine import DCGANEngine
         from distributed_tensorflow_for_dcgan_b200.ops import _lib, kernels as Kn
@@ -171,7 +172,8 @@ def main():
         eng.step_body()
         launches_per_step = _lib.launch_count - c0
         torch.cuda.synchronize()
-        if not args.no_graph:
+        use_graph = not args.no_graph and not (world > 1 and args.comm == "nccl")
+        if use_graph:  # (NCCL collectives are launched eagerly: the baseline path is not graph-captured)
             eng.capture()
 
         def device_step(i):
@@ -277,7 +279,7 @@ def main():
             "impl": args.impl,
             "config": {"model": f"DCGAN {S}x{S} ngf={cfg.gf_dim} ndf={cfg.df_dim} z={cfg.z_dim}",
                        "global_batch": gb, "batch_per_gpu": B, "seq_len": None, "parallelism": parallelism,
-                       "update_mode": "simultaneous", "cuda_graph": (args.impl == "ours" and not args.no_graph),
+                       "update_mode": "simultaneous", "cuda_graph": (args.impl == "ours" and use_graph),
                        "l2": "flushed between timed steps (256 MiB write outside the event pairs)",
                        "step_ms_min_med_max": [round(min(per_step), 4), round(statistics.median(per_step), 4),
                                                round(max(per_step), 4)]},
