@@ -83,12 +83,13 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 // k-blocks whose gather copies are in flight per producer thread before the oldest is published
-constexpr int kGatherDepth = 3;
+// (kGatherDepth is min(3, STAGES - 1), a kernel-local constant)
 
 template <int MODE, int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads, 1)
+__global__ void __launch_bounds__(kNumThreads, (SmemLayout<BLOCK_N, STAGES>::kTotal <= 110 * 1024) ? 2 : 1)
 igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
   using L = SmemLayout<BLOCK_N, STAGES>;
+  constexpr int kGatherDepth = (STAGES - 1 < 3) ? STAGES - 1 : 3;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
@@ -450,11 +451,15 @@ static int launch(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cuda
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 
+// tuning knob (bring-up / profiling): bit 0 = two CTAs per SM with shallower stage rings
+static int g_igemm_tuning = 1;
+
 template <int MODE>
 static int dispatch_n(int block_n, const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cudaStream_t st) {
+  const bool occ2 = (g_igemm_tuning & 1) != 0;
   switch (block_n) {
-    case 64: return launch<MODE, 64, 6>(tmap, p, grid, st);
-    case 128: return launch<MODE, 128, 5>(tmap, p, grid, st);
+    case 64: return occ2 ? launch<MODE, 64, 4>(tmap, p, grid, st) : launch<MODE, 64, 6>(tmap, p, grid, st);
+    case 128: return occ2 ? launch<MODE, 128, 3>(tmap, p, grid, st) : launch<MODE, 128, 5>(tmap, p, grid, st);
     case 256: return launch<MODE, 256, 4>(tmap, p, grid, st);
     default: return DCGAN_ERR_SHAPE;
   }
@@ -477,6 +482,8 @@ static int pick_block_n(int Cn, int rows_tiles, int extra_parallel) {
 using namespace dcgan;
 
 extern "C" {
+
+void dcgan_set_igemm_tuning(int v) { g_igemm_tuning = v; }
 
 int dcgan_conv_fprop(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                      int Cin, int Cout, int act, int block_n, cudaStream_t stream) {

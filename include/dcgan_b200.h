@@ -37,6 +37,9 @@ int dcgan_last_device_error(void);
 /* Bring-up switch for the MN-major UMMA descriptor convention (0 = CuTe convention). */
 void dcgan_set_mn_desc_variant(int v);
 
+/* Profiling switch for the implicit-GEMM kernels: bit 0 = two CTAs per SM (default on). */
+void dcgan_set_igemm_tuning(int v);
+
 /* ---- implicit-GEMM convolutions on tcgen05 / TMEM / TMA (csrc/igemm_sm100.cu) ------------------ */
 
 /* Strided forward conv 5x5 s2 SAME: out[NB,H/2,W/2,Cout] = act(conv(x[NB,H,W,Cin]) + bias).
