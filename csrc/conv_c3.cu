@@ -83,8 +83,9 @@ c3_fprop_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kC3Threads)
 c3_tconv_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                const __nv_bfloat16* __restrict__ aux, __nv_bfloat16* __restrict__ out, int H, int W, int C,
-                int act, int mode) {
+                const __nv_bfloat16* __restrict__ aux, __nv_bfloat16* __restrict__ out,
+                float* __restrict__ colsum /* optional [3]: += per-channel sum of the f32 results */, int H, int W,
+                int C, int act, int mode) {
   extern __shared__ float ws[];  // [25][3][C]
   for (int i = threadIdx.x; i < 75 * C; i += kC3Threads) ws[i] = w[i];
   __syncthreads();
@@ -135,6 +136,7 @@ c3_tconv_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w
     }
   }
   const int oH = 2 * H, oW = 2 * W;
+  float csum[3] = {0.f, 0.f, 0.f};
 #pragma unroll
   for (int ph = 0; ph < 2; ++ph) {
     const size_t o = (((size_t)n * oH + 2 * qy + ph) * oW + 2 * qx) * 3;  // 6 contiguous bf16
@@ -155,9 +157,23 @@ c3_tconv_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w
         v[2 * j + 1] *= (1.f - a.y * a.y);
       }
     }
+#pragma unroll
+    for (int j = 0; j < 6; ++j) csum[j % 3] += v[j];
     uint32_t* op = reinterpret_cast<uint32_t*>(out + o);
 #pragma unroll
     for (int j = 0; j < 3; ++j) op[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+  }
+  if (colsum != nullptr) {  // bias gradient of the 3-channel layer, reduced in f32 before the bf16 rounding
+    __shared__ float cred[3];
+    if (threadIdx.x < 3) cred[threadIdx.x] = 0.f;
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float s = warp_sum(csum[c]);
+      if ((threadIdx.x & 31) == 0) atomicAdd(&cred[c], s);
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) atomicAdd(&colsum[threadIdx.x], cred[threadIdx.x]);
   }
 }
 
@@ -257,8 +273,8 @@ int dcgan_c3_fprop(const void* x, const float* w, const float* bias, void* out, 
   return LAUNCH_OK();
 }
 
-int dcgan_c3_tconv(const void* x, const float* w, const float* bias, const void* aux, void* out, int N, int H,
-                   int W, int C, int act, int mode, cudaStream_t st) {
+int dcgan_c3_tconv(const void* x, const float* w, const float* bias, const void* aux, void* out, float* colsum,
+                   int N, int H, int W, int C, int act, int mode, cudaStream_t st) {
   if (C % 8 || H % kTH || W % kTW) return DCGAN_ERR_SHAPE;
   const size_t smem = (size_t)75 * C * sizeof(float);
   if (smem > 48 * 1024) {
@@ -274,7 +290,7 @@ int dcgan_c3_tconv(const void* x, const float* w, const float* bias, const void*
   dim3 grid((H / kTH) * (W / kTW), N);
   c3_tconv_kernel<<<grid, kC3Threads, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), w, bias,
                                                   reinterpret_cast<const __nv_bfloat16*>(aux),
-                                                  reinterpret_cast<__nv_bfloat16*>(out), H, W, C, act, mode);
+                                                  reinterpret_cast<__nv_bfloat16*>(out), colsum, H, W, C, act, mode);
   return LAUNCH_OK();
 }
 

@@ -48,6 +48,7 @@ struct IgemmParams {
   const float* bias;       // F/T optional, per out channel
   int act;                 // F/T activation
   int oH, oW;              // F/T output spatial dims
+  int b_mn;                // F/T: weights are [25][Ck][Cn] (Cn contiguous) -> MN-major B operand
   int* err_flag;           // sticky device error flag (csrc/runtime.cu)
   const int* mn_variant;   // MN-major descriptor convention switch (bring-up harness only)
 };
@@ -166,7 +167,13 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
             tap = kh * 5 + kw;
           }
           mbar_arrive_expect_tx(&full_bar[s], L::kBTileBytes);
-          tma_load_2d(sB, &tmap, &full_bar[s], c0, tap * p.Cn + n0);
+          if (p.b_mn) {  // native [tap][Ck][Cn] layout: 64(k) x 64(n) boxes, one per 64 output channels
+#pragma unroll
+            for (int j = 0; j < BLOCK_N / 64; ++j)
+              tma_load_2d(sB + j * 8192, &tmap, &full_bar[s], n0 + 64 * j, tap * p.gC + c0);
+          } else {
+            tma_load_2d(sB, &tmap, &full_bar[s], c0, tap * p.Cn + n0);
+          }
         }
       }
     }
@@ -174,11 +181,15 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
     // =================================== MMA issuer ============================================
     if (lane == 0) {
       constexpr bool kMN = (MODE == MODE_W);
-      constexpr uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, kMN, kMN);
+      const bool b_mn = kMN || (p.b_mn != 0);
+      const uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, kMN, b_mn);
       const bool swap = kMN && (*p.mn_variant != 0);
       const uint32_t lbo = kMN ? (swap ? 1024u : 8192u) : 16u;
       const uint32_t sbo = kMN ? (swap ? 8192u : 1024u) : 1024u;
       const uint32_t kstep = kMN ? 2048u : 32u;  // bytes per UMMA_K=16 step
+      const uint32_t lbo_b = b_mn ? (swap ? 1024u : 8192u) : 16u;
+      const uint32_t sbo_b = b_mn ? (swap ? 8192u : 1024u) : 1024u;
+      const uint32_t kstep_b = b_mn ? 2048u : 32u;
       bool ok = true;
       for (int kb = 0; kb < num_kb && ok; ++kb) {
         const int s = kb % STAGES;
@@ -191,7 +202,7 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
 #pragma unroll
         for (int k = 0; k < kBlockK / 16; ++k) {
           const uint64_t da = make_smem_desc_sw128(a_addr + k * kstep, lbo, sbo);
-          const uint64_t db = make_smem_desc_sw128(b_addr + k * kstep, lbo, sbo);
+          const uint64_t db = make_smem_desc_sw128(b_addr + k * kstep_b, lbo_b, sbo_b);
           umma_bf16(tmem_base, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
         }
         umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs retire
@@ -485,8 +496,8 @@ extern "C" {
 
 void dcgan_set_igemm_tuning(int v) { g_igemm_tuning = v; }
 
-int dcgan_conv_fprop(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
-                     int Cin, int Cout, int act, int block_n, cudaStream_t stream) {
+static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
+                           int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream) {
   if ((H & 1) || (W & 1) || Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
   const int oH = H / 2, oW = W / 2;
   const int lh = ilog2_exact(oH), lw = ilog2_exact(oW);
@@ -501,15 +512,27 @@ int dcgan_conv_fprop(const void* x, const void* w_nk, const float* bias, void* o
   p.rows_total = NB * oH * oW;
   p.Cn = Cout; p.Cd = 0;
   p.num_kb = 25 * (Cin / 64);
+  p.b_mn = b_mn;
   p.out = out; p.bias = bias; p.act = act; p.oH = oH; p.oW = oW;
   const int mt = (p.rows_total + kBlockM - 1) / kBlockM;
   if (block_n <= 0) block_n = pick_block_n(Cout, mt, 1);
   if (block_n < 0 || Cout % block_n) return DCGAN_ERR_SHAPE;
   CUtensorMap tmap;
-  int rc = get_tmap_2d(w_nk, (uint64_t)25 * Cout, Cin, block_n, 64, &tmap);
+  int rc = b_mn ? get_tmap_2d(w_nk, (uint64_t)25 * Cin, Cout, 64, 64, &tmap)
+                : get_tmap_2d(w_nk, (uint64_t)25 * Cout, Cin, block_n, 64, &tmap);
   if (rc) return rc;
   dim3 grid(mt, Cout / block_n, 1);
   return dispatch_n<MODE_F>(block_n, tmap, p, grid, stream);
+}
+
+int dcgan_conv_fprop(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
+                     int Cin, int Cout, int act, int block_n, cudaStream_t stream) {
+  return conv_fprop_impl(x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n, 0, stream);
+}
+
+int dcgan_conv_fprop_kn(const void* x, const void* w_kn, const float* bias, void* out, int NB, int H, int W,
+                        int Cin, int Cout, int act, int block_n, cudaStream_t stream) {
+  return conv_fprop_impl(x, w_kn, bias, out, NB, H, W, Cin, Cout, act, block_n, 1, stream);
 }
 
 int dcgan_conv_tconv(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,

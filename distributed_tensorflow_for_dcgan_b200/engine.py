@@ -133,13 +133,9 @@ class DCGANEngine:
                                        ema_var=torch.zeros(2, C, **f32), act="lrelu")
 
         # ---- bf16 compute copies of the weights -------------------------------------------------------
+        # one flat bf16 shadow in the TF layouts serves every use: K-major B for the transposed-conv mode,
+        # MN-major B for the strided mode -- no per-use transposed copies
         self.w_native = A.named(A.bf16)
-        self.w_t: Dict[str, torch.Tensor] = {}
-        for i in (1, 2, 3):
-            co, ci = self.g_ch[i], self.g_ch[i - 1]
-            self.w_t[f"g_h{i}/w"] = torch.zeros(25, ci, co, **bf)      # [25][Cin_d][Cout_d]: deconv data-grad
-            ci, co = self.d_ch[i], self.d_ch[i + 1]
-            self.w_t[f"d_h{i}_conv/w"] = torch.zeros(25, co, ci, **bf)  # [25][Cout][Cin]: conv forward
 
         # ---- activations ------------------------------------------------------------------------------
         self.z = torch.zeros(B, cfg.z_dim, **f32)
@@ -175,15 +171,10 @@ class DCGANEngine:
     # weights
     # ------------------------------------------------------------------------------------------------
     def refresh_compute_weights(self, cast: bool = True) -> None:
-        """bf16 copies of the master weights: the flat native cast plus the per-tap transposes."""
+        """bf16 shadow of the master weights (flat cast; the optimizer kernels keep it current)."""
         A = self.arena
         if cast:
             K.cast_bf16(A.master, A.bf16)
-        for i in (1, 2, 3):
-            co, ci = self.g_ch[i], self.g_ch[i - 1]
-            K.transpose_taps(self.w_native[f"g_h{i}/w"], self.w_t[f"g_h{i}/w"], 25, co, ci)
-            ci, co = self.d_ch[i], self.d_ch[i + 1]
-            K.transpose_taps(self.w_native[f"d_h{i}_conv/w"], self.w_t[f"d_h{i}_conv/w"], 25, ci, co)
 
     # ------------------------------------------------------------------------------------------------
     # forward
@@ -222,7 +213,8 @@ class DCGANEngine:
         p = self.params
         K.c3_fprop(self.d_in, p["d_h0_conv/w"], p["d_h0_conv/biases"], act="lrelu", out=self.d_act[0])
         for i in (1, 2, 3):
-            K.conv_fprop(self.d_act[i - 1], self.w_t[f"d_h{i}_conv/w"], p[f"d_h{i}_conv/biases"], out=self.d_pre[i])
+            w = self.w_native[f"d_h{i}_conv/w"].view(25, self.d_ch[i], self.d_ch[i + 1])
+            K.conv_fprop_kn(self.d_act[i - 1], w, p[f"d_h{i}_conv/biases"], out=self.d_pre[i])
             self._bn_fwd(f"d_bn{i}", self.d_pre[i], self.d_act[i])
         K.head_fwd(self.d_act[3].view(2 * self.B, -1), p["d_h3_lin/Matrix"], p["d_h3_lin/bias"], self.logits)
 
@@ -258,18 +250,18 @@ class DCGANEngine:
                   g["d_h0_conv/biases"], "lrelu", bias_rows=2 * B * self.d_sz[1] * self.d_sz[1])
         K.c3_wgrad(self.d_in, self.dd_pre[0][:2 * B], g["d_h0_conv/w"])
         # g_loss slab only: gradient w.r.t. the generator's pre-tanh output
-        K.c3_tconv(self.dd_pre[0][2 * B:], p["d_h0_conv/w"], None, aux=self.d_in[B:], out=self.dimg)
+        K.c3_tconv(self.dd_pre[0][2 * B:], p["d_h0_conv/w"], None, aux=self.d_in[B:], out=self.dimg,
+                   colsum=g["g_h4/biases"])  # g_h4's bias gradient falls out of the same pass, in f32
 
     def generator_backward(self) -> None:
         p, g, B = self.params, self.grad_views, self.B
-        K.colsum(self.dimg.view(-1, 3), g["g_h4/biases"])
         K.c3_wgrad(self.dimg, self.g_act[3], g["g_h4/w"])
         K.c3_fprop(self.dimg, p["g_h4/w"], None, out=self.dg_act[3])
         for i in (3, 2, 1):
             self._bn_bwd(f"g_bn{i}", self.dg_act[i], self.g_pre[i], self.dg_pre[i])
             co, ci = self.g_ch[i], self.g_ch[i - 1]
             K.conv_wgrad(self.dg_pre[i], self.g_act[i - 1], g[f"g_h{i}/w"].view(25, co, ci))
-            K.conv_fprop(self.dg_pre[i], self.w_t[f"g_h{i}/w"], None, out=self.dg_act[i - 1])
+            K.conv_fprop_kn(self.dg_pre[i], self.w_native[f"g_h{i}/w"].view(25, co, ci), None, out=self.dg_act[i - 1])
         self._bn_bwd("g_bn0", self.dg_act[0], self.g_pre[0], self.dg_pre[0])
         K.lin_wgrad(self.z, self.dg_pre[0].view(B, -1), g["g_h0_lin/Matrix"], g["g_h0_lin/bias"])
 

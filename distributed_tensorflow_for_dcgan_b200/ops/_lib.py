@@ -19,10 +19,11 @@ c_int, c_float, c_void_p, c_size_t = ctypes.c_int, ctypes.c_float, ctypes.c_void
 # name -> argument kinds: p = device pointer, i = int, f = float, z = size_t, s = stream
 _SIGNATURES = {
     "dcgan_conv_fprop": "ppppiiiiiiis",
+    "dcgan_conv_fprop_kn": "ppppiiiiiiis",
     "dcgan_conv_tconv": "ppppiiiiiiis",
     "dcgan_conv_wgrad": "pppiiiiiiis",
     "dcgan_c3_fprop": "ppppiiiiis",
-    "dcgan_c3_tconv": "pppppiiiiiis",
+    "dcgan_c3_tconv": "ppppppiiiiiis",
     "dcgan_c3_wgrad": "pppiiiis",
     "dcgan_bn_stats": "ppiiis",
     "dcgan_bn_apply": "ppppppppiiiffiis",

@@ -29,6 +29,16 @@ def conv_fprop(x, w_nk, bias=None, act="none", out=None, block_n=0):
     return out
 
 
+def conv_fprop_kn(x, w_kn, bias=None, act="none", out=None, block_n=0):
+    """5x5 s2 SAME conv with the filter in TF layout: w_kn [25,Cin,Cout] bf16 (no transposed copy)."""
+    N, H, W, Cin = x.shape
+    Cout = w_kn.shape[2]
+    if out is None:
+        out = _bf16((N, H // 2, W // 2, Cout), x)
+    call("dcgan_conv_fprop_kn", ptr(x), ptr(w_kn), ptr(bias), ptr(out), N, H, W, Cin, Cout, ACT[act], block_n)
+    return out
+
+
 def conv_tconv(x, w_nk, bias=None, act="none", out=None, block_n=0):
     """5x5 s2 transposed conv (TF crop).  x [N,H,W,Cin], w_nk [25,Cout,Cin] -> [N,2H,2W,Cout]."""
     N, H, W, Cin = x.shape
@@ -56,12 +66,12 @@ def c3_fprop(x, w, bias=None, act="none", out=None):
     return out
 
 
-def c3_tconv(x, w, bias=None, act="none", aux=None, out=None):
-    """mode 0: act(v + bias); with ``aux``: v * (1 - aux^2)."""
+def c3_tconv(x, w, bias=None, act="none", aux=None, out=None, colsum=None):
+    """mode 0: act(v + bias); with ``aux``: v * (1 - aux^2).  ``colsum`` (f32[3]) += channel sums."""
     N, H, W, C = x.shape
     if out is None:
         out = _bf16((N, 2 * H, 2 * W, 3), x)
-    call("dcgan_c3_tconv", ptr(x), ptr(w), ptr(bias), ptr(aux), ptr(out), N, H, W, C, ACT[act],
+    call("dcgan_c3_tconv", ptr(x), ptr(w), ptr(bias), ptr(aux), ptr(out), ptr(colsum), N, H, W, C, ACT[act],
          0 if aux is None else 1)
     return out
 

@@ -49,6 +49,12 @@ void dcgan_set_igemm_tuning(int v);
 int dcgan_conv_fprop(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                      int Cin, int Cout, int act, int block_n, cudaStream_t stream);
 
+/* Same, with the filter in its TensorFlow layout [25][Cin][Cout] (HWIO; also the deconv layout
+ * [kh,kw,Cout_d,Cin_d] read as a data-gradient filter): fed to the MMA as an MN-major operand, so no
+ * transposed weight copy is needed. */
+int dcgan_conv_fprop_kn(const void* x, const void* w_kn, const float* bias, void* out, int NB, int H, int W,
+                        int Cin, int Cout, int act, int block_n, cudaStream_t stream);
+
 /* Transposed conv 5x5 s2 (TF crop 1 before / 2 after): out[NB,2H,2W,Cout] = act(deconv(x) + bias).
  * w_nk is bf16 [25][Cout][Cin].  Same math as tf.nn.conv2d_transpose at reference
  * distriubted_model.py:200 and as the data gradient of conv2d at :183. */
@@ -71,9 +77,10 @@ int dcgan_conv_wgrad(const void* big, const void* small, float* dw, int NB, int 
 int dcgan_c3_fprop(const void* x, const float* w, const float* bias, void* out, int N, int H, int W, int C,
                    int act, cudaStream_t stream);
 /* out[N,2H,2W,3] from x[N,H,W,C]: g_h4 forward (distriubted_model.py:109; mode 0: act(v+bias)) and the
- * d_h0 data gradient (mode 1: v * (1 - aux^2), the tanh backward against aux = generator output). */
-int dcgan_c3_tconv(const void* x, const float* w, const float* bias, const void* aux, void* out, int N, int H,
-                   int W, int C, int act, int mode, cudaStream_t stream);
+ * d_h0 data gradient (mode 1: v * (1 - aux^2), the tanh backward against aux = generator output).
+ * colsum (optional, f32[3], zeroed by the caller) += per-channel sum of the results = g_h4's bias gradient. */
+int dcgan_c3_tconv(const void* x, const float* w, const float* bias, const void* aux, void* out, float* colsum,
+                   int N, int H, int W, int C, int act, int mode, cudaStream_t stream);
 /* dw[25][3][C] += sum x3[N,2Hs,2Ws,3] (gathered) * y[N,Hs,Ws,C]   (f32 atomics; zero first). */
 int dcgan_c3_wgrad(const void* x3, const void* y, float* dw, int N, int Hs, int Ws, int C, cudaStream_t stream);
 

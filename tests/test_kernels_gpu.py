@@ -38,6 +38,19 @@ def test_conv_fprop(cuda_lib, N, H, Cin, Cout):
     _close(out, ref, name="conv_fprop")
 
 
+@pytest.mark.parametrize("N,H,Cin,Cout", [(2, 16, 64, 128), (4, 8, 128, 64), (1, 8, 64, 256), (2, 8, 256, 512)])
+def test_conv_fprop_tf_layout(cuda_lib, N, H, Cin, Cout):
+    """Filter consumed in its HWIO layout through an MN-major B operand (no transposed copy)."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    x = _rand((N, H, H, Cin))
+    w = _rand((5, 5, Cin, Cout), 0.05)
+    b = torch.randn(Cout, device="cuda") * 0.1
+    out = K.conv_fprop_kn(x, w.view(25, Cin, Cout), b, act="lrelu")
+    ref = Fn.lrelu(Fn.conv2d_same(x.float(), w.float(), b))
+    K.check_device_error()
+    _close(out, ref, name="conv_fprop_kn")
+
+
 @pytest.mark.parametrize("N,H,Cin,Cout", [(2, 8, 64, 64), (2, 4, 128, 128), (1, 8, 256, 128)])
 def test_conv_tconv(cuda_lib, N, H, Cin, Cout):
     from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
@@ -99,9 +112,11 @@ def test_c3_tconv_fwd_and_tanh_bwd(cuda_lib):
     ref = torch.tanh(Fn.deconv2d(x.float(), w, b))
     _close(out, ref, name="c3_tconv")
     aux = out
-    out2 = K.c3_tconv(x, w, None, aux=aux)
+    cs = torch.zeros(3, device="cuda")
+    out2 = K.c3_tconv(x, w, None, aux=aux, colsum=cs)
     ref2 = Fn.deconv2d(x.float(), w) * (1 - aux.float() ** 2)
     _close(out2, ref2, name="c3_tconv_tanh_bwd")
+    _close(cs, ref2.sum((0, 1, 2)), rel=2e-3, name="c3_tconv colsum")
 
 
 def test_c3_wgrad(cuda_lib):
