@@ -203,6 +203,23 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// Column sums across the 32 lanes of a warp: lane L ends up with sum over lanes of their v[L].
+// Butterfly transpose-reduce: 31 shuffles instead of 32 x 5.
+__device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32]) {
+  const unsigned lane = threadIdx.x & 31;
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = upper ? v[i] : v[i + off];
+      const float keep = upper ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
 enum Act : int { kActNone = 0, kActRelu = 1, kActLrelu = 2, kActTanh = 3, kActSigmoid = 4 };
 
 __device__ __forceinline__ float apply_act(float x, int act) {

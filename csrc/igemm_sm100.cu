@@ -48,6 +48,9 @@ struct IgemmParams {
   const float* bias;       // F/T optional, per out channel
   int act;                 // F/T activation
   int oH, oW;              // F/T output spatial dims
+  float* stats;            // F/T optional: [groups][2][Cn] += per-channel (sum, sum of squares) of the
+                           // pre-activation output -- the batch-norm moments (distriubted_model.py:37)
+  int stat_group_rows;     // rows per statistics group (multiple of 128)
   int b_mn;                // F/T: weights are [25][Ck][Cn] (Cn contiguous) -> MN-major B operand
   int* err_flag;           // sticky device error flag (csrc/runtime.cu)
   const int* mn_variant;   // MN-major descriptor convention switch (bring-up harness only)
@@ -64,7 +67,8 @@ struct SmemLayout {
   static constexpr int kBTileBytes = BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kATileBytes + kBTileBytes;
   static constexpr int kBarOffset = STAGES * kStageBytes;
-  static constexpr int kTotal = kBarOffset + 256 + 1024;  // + barriers + alignment slack
+  static constexpr int kStatOffset = kBarOffset + 256;     // [2][BLOCK_N] f32 epilogue column sums
+  static constexpr int kTotal = kStatOffset + 2 * BLOCK_N * 4 + 1024;  // + alignment slack
 };
 
 // 16-byte chunk (row, chunk) of a [rows][128 B] tile in the SWIZZLE_128B pattern
@@ -98,6 +102,7 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
   uint64_t* tmem_full_bar = empty_bar + STAGES;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+  float* stat_smem = reinterpret_cast<float*>(smem + L::kStatOffset);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -316,6 +321,11 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
     }
 
     // ------------------------------------ epilogue ----------------------------------------------
+    const bool do_stats = (MODE != MODE_W) && p.stats != nullptr;
+    if (do_stats) {
+      for (int i = gt; i < 2 * BLOCK_N; i += kNumGatherThreads) stat_smem[i] = 0.f;
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+    }
     if (ok) ok = mbar_wait(tmem_full_bar, 0, abort_flag, p.err_flag);
     tc_fence_after();
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
@@ -338,23 +348,39 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
         uint32_t v[32];
         tmem_ld_32x32(taddr + c, v);
         tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float a = __uint_as_float(v[j]);
+          if (p.bias != nullptr) a += __ldg(p.bias + n0 + c + j);
+          f[j] = valid ? a : 0.f;
+        }
         if (valid) {
           uint32_t packed[16];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            float a = __uint_as_float(v[2 * j]), b = __uint_as_float(v[2 * j + 1]);
-            if (p.bias != nullptr) {
-              a += __ldg(p.bias + n0 + c + 2 * j);
-              b += __ldg(p.bias + n0 + c + 2 * j + 1);
-            }
-            a = apply_act(a, p.act);
-            b = apply_act(b, p.act);
-            packed[j] = pack_bf16x2(a, b);
-          }
+          for (int j = 0; j < 16; ++j)
+            packed[j] = pack_bf16x2(apply_act(f[2 * j], p.act), apply_act(f[2 * j + 1], p.act));
           uint4* dst = reinterpret_cast<uint4*>(orow + c);
 #pragma unroll
           for (int j = 0; j < 4; ++j)
             dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+        }
+        if (do_stats) {  // batch-norm moments of this tile, reduced over the warp's 32 rows
+          float sq[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) sq[j] = f[j] * f[j];
+          const float s1 = warp_transpose_reduce32(f);
+          const float s2 = warp_transpose_reduce32(sq);
+          atomicAdd(&stat_smem[c + lane], s1);
+          atomicAdd(&stat_smem[BLOCK_N + c + lane], s2);
+        }
+      }
+      if (do_stats) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        float* gs = p.stats + (size_t)(m0 / p.stat_group_rows) * 2 * p.Cn + n0;
+        for (int i = gt; i < BLOCK_N; i += kNumGatherThreads) {
+          atomicAdd(gs + i, stat_smem[i]);
+          atomicAdd(gs + p.Cn + i, stat_smem[BLOCK_N + i]);
         }
       }
     } else {
@@ -497,7 +523,8 @@ extern "C" {
 void dcgan_set_igemm_tuning(int v) { g_igemm_tuning = v; }
 
 static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
-                           int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream) {
+                           int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream,
+                           float* stats = nullptr, int stat_groups = 1) {
   if ((H & 1) || (W & 1) || Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
   const int oH = H / 2, oW = W / 2;
   const int lh = ilog2_exact(oH), lw = ilog2_exact(oW);
@@ -513,6 +540,11 @@ static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, v
   p.Cn = Cout; p.Cd = 0;
   p.num_kb = 25 * (Cin / 64);
   p.b_mn = b_mn;
+  if (stats != nullptr) {
+    if (stat_groups < 1 || p.rows_total % stat_groups || (p.rows_total / stat_groups) % kBlockM) return DCGAN_ERR_SHAPE;
+    p.stats = stats;
+    p.stat_group_rows = p.rows_total / stat_groups;
+  }
   p.out = out; p.bias = bias; p.act = act; p.oH = oH; p.oW = oW;
   const int mt = (p.rows_total + kBlockM - 1) / kBlockM;
   if (block_n <= 0) block_n = pick_block_n(Cout, mt, 1);
@@ -535,8 +567,15 @@ int dcgan_conv_fprop_kn(const void* x, const void* w_kn, const float* bias, void
   return conv_fprop_impl(x, w_kn, bias, out, NB, H, W, Cin, Cout, act, block_n, 1, stream);
 }
 
-int dcgan_conv_tconv(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
-                     int Cin, int Cout, int act, int block_n, cudaStream_t stream) {
+int dcgan_conv_fprop_kn_stats(const void* x, const void* w_kn, const float* bias, void* out, float* stats,
+                              int stat_groups, int NB, int H, int W, int Cin, int Cout, int block_n,
+                              cudaStream_t stream) {
+  return conv_fprop_impl(x, w_kn, bias, out, NB, H, W, Cin, Cout, 0, block_n, 1, stream, stats, stat_groups);
+}
+
+static int conv_tconv_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
+                           int Cin, int Cout, int act, int block_n, cudaStream_t stream, float* stats,
+                           int stat_groups) {
   if (Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
   const int lh = ilog2_exact(H), lw = ilog2_exact(W);
   if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;
@@ -550,6 +589,11 @@ int dcgan_conv_tconv(const void* x, const void* w_nk, const float* bias, void* o
   p.rows_total = NB * H * W;
   p.Cn = Cout; p.Cd = 0;
   p.num_kb = 0;  // per parity class, derived in-kernel
+  if (stats != nullptr) {
+    if (stat_groups < 1 || p.rows_total % stat_groups || (p.rows_total / stat_groups) % kBlockM) return DCGAN_ERR_SHAPE;
+    p.stats = stats;
+    p.stat_group_rows = p.rows_total / stat_groups;
+  }
   p.out = out; p.bias = bias; p.act = act; p.oH = 2 * H; p.oW = 2 * W;
   const int mt = (p.rows_total + kBlockM - 1) / kBlockM;
   if (block_n <= 0) block_n = pick_block_n(Cout, mt, 4);
@@ -559,6 +603,17 @@ int dcgan_conv_tconv(const void* x, const void* w_nk, const float* bias, void* o
   if (rc) return rc;
   dim3 grid(mt, Cout / block_n, 4);
   return dispatch_n<MODE_T>(block_n, tmap, p, grid, stream);
+}
+
+int dcgan_conv_tconv(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
+                     int Cin, int Cout, int act, int block_n, cudaStream_t stream) {
+  return conv_tconv_impl(x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n, stream, nullptr, 1);
+}
+
+int dcgan_conv_tconv_stats(const void* x, const void* w_nk, const float* bias, void* out, float* stats,
+                           int stat_groups, int NB, int H, int W, int Cin, int Cout, int block_n,
+                           cudaStream_t stream) {
+  return conv_tconv_impl(x, w_nk, bias, out, NB, H, W, Cin, Cout, 0, block_n, stream, stats, stat_groups);
 }
 
 int dcgan_conv_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd,

@@ -179,13 +179,20 @@ class DCGANEngine:
     # ------------------------------------------------------------------------------------------------
     # forward
     # ------------------------------------------------------------------------------------------------
-    def _bn_fwd(self, name, pre, act_out, train=True):
+    def _stats_fusable(self, name, pre) -> bool:
+        """The conv epilogue can accumulate the moments when every 128-row tile lies in one statistics group."""
+        st = self.bn[name]
+        rows = pre.numel() // st["C"]
+        return (rows // st["groups"]) % 128 == 0
+
+    def _bn_fwd(self, name, pre, act_out, train=True, stats_done=False):
         st = self.bn[name]
         C, G = st["C"], st["groups"]
         x2, y2 = pre.view(-1, C), act_out.view(-1, C)
         p = self.params
         if train:
-            K.bn_stats(x2, st["sums"], G)
+            if not stats_done:
+                K.bn_stats(x2, st["sums"], G)
             if self.comm is not None and getattr(self.comm, "sync_bn", False):
                 self.comm.allreduce_bn(st["sums"])
             K.bn_apply(x2, y2, st["sums"], p[f"{name}/gamma"], p[f"{name}/beta"], st["saved"], st["ema_mean"],
@@ -203,8 +210,12 @@ class DCGANEngine:
         self._bn_fwd("g_bn0", pre[0], act[0], train)
         for i in (1, 2, 3):
             w = self.w_native[f"g_h{i}/w"].view(25, self.g_ch[i], self.g_ch[i - 1])
-            K.conv_tconv(act[i - 1], w, p[f"g_h{i}/biases"], out=pre[i])
-            self._bn_fwd(f"g_bn{i}", pre[i], act[i], train)
+            fused = train and self._stats_fusable(f"g_bn{i}", pre[i])
+            if fused:  # batch-norm moments fall out of the conv epilogue
+                K.conv_tconv_stats(act[i - 1], w, p[f"g_h{i}/biases"], pre[i], self.bn[f"g_bn{i}"]["sums"], 1)
+            else:
+                K.conv_tconv(act[i - 1], w, p[f"g_h{i}/biases"], out=pre[i])
+            self._bn_fwd(f"g_bn{i}", pre[i], act[i], train, stats_done=fused)
         out = self.d_in[B:] if train else self.s_img
         K.c3_tconv(act[3], p["g_h4/w"], p["g_h4/biases"], act="tanh", out=out)
         return out
@@ -214,8 +225,13 @@ class DCGANEngine:
         K.c3_fprop(self.d_in, p["d_h0_conv/w"], p["d_h0_conv/biases"], act="lrelu", out=self.d_act[0])
         for i in (1, 2, 3):
             w = self.w_native[f"d_h{i}_conv/w"].view(25, self.d_ch[i], self.d_ch[i + 1])
-            K.conv_fprop_kn(self.d_act[i - 1], w, p[f"d_h{i}_conv/biases"], out=self.d_pre[i])
-            self._bn_fwd(f"d_bn{i}", self.d_pre[i], self.d_act[i])
+            fused = self._stats_fusable(f"d_bn{i}", self.d_pre[i])
+            if fused:
+                K.conv_fprop_kn_stats(self.d_act[i - 1], w, p[f"d_h{i}_conv/biases"], self.d_pre[i],
+                                      self.bn[f"d_bn{i}"]["sums"], 2)
+            else:
+                K.conv_fprop_kn(self.d_act[i - 1], w, p[f"d_h{i}_conv/biases"], out=self.d_pre[i])
+            self._bn_fwd(f"d_bn{i}", self.d_pre[i], self.d_act[i], stats_done=fused)
         K.head_fwd(self.d_act[3].view(2 * self.B, -1), p["d_h3_lin/Matrix"], p["d_h3_lin/bias"], self.logits)
 
     # ------------------------------------------------------------------------------------------------

@@ -21,6 +21,8 @@ _SIGNATURES = {
     "dcgan_conv_fprop": "ppppiiiiiiis",
     "dcgan_conv_fprop_kn": "ppppiiiiiiis",
     "dcgan_conv_tconv": "ppppiiiiiiis",
+    "dcgan_conv_fprop_kn_stats": "pppppiiiiiiis",
+    "dcgan_conv_tconv_stats": "pppppiiiiiiis",
     "dcgan_conv_wgrad": "pppiiiiiiis",
     "dcgan_c3_fprop": "ppppiiiiis",
     "dcgan_c3_tconv": "ppppppiiiiiis",

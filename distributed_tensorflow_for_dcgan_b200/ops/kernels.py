@@ -49,6 +49,21 @@ def conv_tconv(x, w_nk, bias=None, act="none", out=None, block_n=0):
     return out
 
 
+def conv_fprop_kn_stats(x, w_kn, bias, out, stats, groups, block_n=0):
+    """conv_fprop_kn + batch-norm moments of the output accumulated into stats [groups,2,Cout]."""
+    N, H, W, Cin = x.shape
+    call("dcgan_conv_fprop_kn_stats", ptr(x), ptr(w_kn), ptr(bias), ptr(out), ptr(stats), groups, N, H, W, Cin,
+         w_kn.shape[2], block_n)
+    return out
+
+
+def conv_tconv_stats(x, w_nk, bias, out, stats, groups, block_n=0):
+    N, H, W, Cin = x.shape
+    call("dcgan_conv_tconv_stats", ptr(x), ptr(w_nk), ptr(bias), ptr(out), ptr(stats), groups, N, H, W, Cin,
+         w_nk.shape[1], block_n)
+    return out
+
+
 def conv_wgrad(big, small, dw, splits=0, block_n=0):
     """dw[25,Cg,Cd] (f32, +=) from big [N,2Hs,2Ws,Cg] and small [N,Hs,Ws,Cd]."""
     N, Hs, Ws, Cd = small.shape

@@ -61,6 +61,16 @@ int dcgan_conv_fprop_kn(const void* x, const void* w_kn, const float* bias, void
 int dcgan_conv_tconv(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                      int Cin, int Cout, int act, int block_n, cudaStream_t stream);
 
+/* Variants that also accumulate the batch-norm moments of their (pre-activation) output in the epilogue:
+ * stats[stat_groups][2][Cout] (f32, zeroed by the caller) += per-channel (sum, sum of squares); rows of each
+ * group must be a multiple of 128.  Replaces a separate dcgan_bn_stats pass (distriubted_model.py:37). */
+int dcgan_conv_fprop_kn_stats(const void* x, const void* w_kn, const float* bias, void* out, float* stats,
+                              int stat_groups, int NB, int H, int W, int Cin, int Cout, int block_n,
+                              cudaStream_t stream);
+int dcgan_conv_tconv_stats(const void* x, const void* w_nk, const float* bias, void* out, float* stats,
+                           int stat_groups, int NB, int H, int W, int Cin, int Cout, int block_n,
+                           cudaStream_t stream);
+
 /* Weight gradient of either layer kind: dw[25][Cg][Cd] (f32, accumulated with atomics -- zero it
  * first) += sum over pixels of big[NB,2Hs,2Ws,Cg] (gathered at 2q+k-1) * small[NB,Hs,Ws,Cd].
  * conv2d:  big = layer input, small = output gradient  -> dw is HWIO.

@@ -51,6 +51,33 @@ def test_conv_fprop_tf_layout(cuda_lib, N, H, Cin, Cout):
     _close(out, ref, name="conv_fprop_kn")
 
 
+def test_conv_epilogue_batchnorm_moments(cuda_lib):
+    """The conv epilogue's fused (sum, sum-of-squares) equal the moments of the conv output, per group."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    N, H, Cin, Cout, G = 8, 16, 64, 128, 2
+    x = _rand((N, H, H, Cin))
+    w = _rand((5, 5, Cin, Cout), 0.05)
+    b = torch.randn(Cout, device="cuda") * 0.1
+    out = torch.empty(N, H // 2, H // 2, Cout, dtype=torch.bfloat16, device="cuda")
+    stats = torch.zeros(G, 2, Cout, device="cuda")
+    K.conv_fprop_kn_stats(x, w.view(25, Cin, Cout), b, out, stats, G)
+    ref = Fn.conv2d_same(x.float(), w.float(), b).view(G, -1, Cout)
+    _close(out.view(G, -1, Cout), ref, name="fprop_stats out")
+    _close(stats[:, 0], ref.sum(1), rel=5e-3, name="fused sum")
+    _close(stats[:, 1], (ref * ref).sum(1), rel=5e-3, name="fused sumsq")
+    # transposed mode, one group
+    xt = _rand((4, 8, 8, 128))
+    wt = _rand((5, 5, 64, 128), 0.05)
+    outt = torch.empty(4, 16, 16, 64, dtype=torch.bfloat16, device="cuda")
+    st = torch.zeros(1, 2, 64, device="cuda")
+    K.conv_tconv_stats(xt, wt.view(25, 64, 128), None, outt, st, 1)
+    reft = Fn.deconv2d(xt.float(), wt.float()).reshape(-1, 64)
+    _close(outt.view(-1, 64), reft, name="tconv_stats out")
+    _close(st[0, 0], reft.sum(0), rel=5e-3, name="tconv fused sum")
+    _close(st[0, 1], (reft * reft).sum(0), rel=5e-3, name="tconv fused sumsq")
+    K.check_device_error()
+
+
 @pytest.mark.parametrize("N,H,Cin,Cout", [(2, 8, 64, 64), (2, 4, 128, 128), (1, 8, 256, 128)])
 def test_conv_tconv(cuda_lib, N, H, Cin, Cout):
     from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
