@@ -99,23 +99,31 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__
     }
   }
   __syncthreads();
+  // thread -> fixed 8-channel vector, rows strided: the per-channel scale/shift stay in registers
   const int cvec = C >> 3;
-  const size_t r0 = (size_t)blockIdx.x * rows_per_block;
-  const size_t r1 = min(r0 + (size_t)rows_per_block, (size_t)rows_per_group);
-  const size_t base = (size_t)g * rows_per_group * cvec;
-  for (size_t i = r0 * cvec + threadIdx.x; i < r1 * cvec; i += kBnThreads) {
-    const int c0 = (int)(i % cvec) * 8;
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(x) + base + i);
+  const int lanes = kBnThreads / cvec;
+  const int cv = threadIdx.x % cvec;
+  const int rl = threadIdx.x / cvec;
+  if (rl >= lanes) return;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { sc[j] = ss[cv * 8 + j]; sh[j] = ss[C + cv * 8 + j]; }
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(r0 + rows_per_block, rows_per_group);
+  const uint4* xb = reinterpret_cast<const uint4*>(x) + (size_t)g * rows_per_group * cvec + cv;
+  uint4* yb = reinterpret_cast<uint4*>(y) + (size_t)g * rows_per_group * cvec + cv;
+#pragma unroll 2
+  for (int r = r0 + rl; r < r1; r += lanes) {
+    const uint4 v = __ldg(xb + (size_t)r * cvec);
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
     uint32_t o[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const float2 f = unpack_bf16x2(w[j]);
-      const float a = apply_act(f.x * ss[c0 + 2 * j] + ss[C + c0 + 2 * j], act);
-      const float b = apply_act(f.y * ss[c0 + 2 * j + 1] + ss[C + c0 + 2 * j + 1], act);
-      o[j] = pack_bf16x2(a, b);
+      o[j] = pack_bf16x2(apply_act(f.x * sc[2 * j] + sh[2 * j], act),
+                         apply_act(f.y * sc[2 * j + 1] + sh[2 * j + 1], act));
     }
-    reinterpret_cast<uint4*>(y)[base + i] = make_uint4(o[0], o[1], o[2], o[3]);
+    yb[(size_t)r * cvec] = make_uint4(o[0], o[1], o[2], o[3]);
   }
 }
 
@@ -219,14 +227,25 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* _
   }
   __syncthreads();
   const int cvec = C >> 3;
-  const size_t r0 = (size_t)blockIdx.x * rows_per_block;
-  const size_t r1 = min(r0 + (size_t)rows_per_block, (size_t)rows_per_group);
-  const size_t dbase = (size_t)g * rows_per_group * cvec;
-  const size_t pbase = (size_t)sg * rows_per_group * cvec;
-  for (size_t i = r0 * cvec + threadIdx.x; i < r1 * cvec; i += kBnThreads) {
-    const int c0 = (int)(i % cvec) * 8;
-    const uint4 dv = __ldg(reinterpret_cast<const uint4*>(da) + dbase + i);
-    const uint4 pv = __ldg(reinterpret_cast<const uint4*>(pre) + pbase + i);
+  const int lanes = kBnThreads / cvec;
+  const int cv = threadIdx.x % cvec;
+  const int rl = threadIdx.x / cvec;
+  if (rl >= lanes) return;
+  float mean[8], rstd[8], gm[8], bt[8], m1[8], m2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = cv * 8 + j;
+    mean[j] = s_mean[c]; rstd[j] = s_rstd[c]; gm[j] = s_g[c]; bt[j] = s_b[c]; m1[j] = s_m1[c]; m2[j] = s_m2[c];
+  }
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(r0 + rows_per_block, rows_per_group);
+  const uint4* dab = reinterpret_cast<const uint4*>(da) + (size_t)g * rows_per_group * cvec + cv;
+  const uint4* prb = reinterpret_cast<const uint4*>(pre) + (size_t)sg * rows_per_group * cvec + cv;
+  uint4* dpb = reinterpret_cast<uint4*>(dpre) + (size_t)g * rows_per_group * cvec + cv;
+#pragma unroll 2
+  for (int r = r0 + rl; r < r1; r += lanes) {
+    const uint4 dv = __ldg(dab + (size_t)r * cvec);
+    const uint4 pv = __ldg(prb + (size_t)r * cvec);
     const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
     const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
     uint32_t o[4];
@@ -234,17 +253,14 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* _
     for (int j = 0; j < 4; ++j) {
       const float2 d = unpack_bf16x2(dw[j]);
       const float2 p = unpack_bf16x2(pw[j]);
-      float r[2];
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int c = c0 + 2 * j + h;
-        const float xh = ((h ? p.y : p.x) - s_mean[c]) * s_rstd[c];
-        const float dy = (h ? d.y : d.x) * act_grad(s_g[c] * xh + s_b[c], act);
-        r[h] = s_g[c] * s_rstd[c] * (dy - s_m1[c] - xh * s_m2[c]);
-      }
-      o[j] = pack_bf16x2(r[0], r[1]);
+      const float xh0 = (p.x - mean[2 * j]) * rstd[2 * j];
+      const float xh1 = (p.y - mean[2 * j + 1]) * rstd[2 * j + 1];
+      const float dy0 = d.x * act_grad(gm[2 * j] * xh0 + bt[2 * j], act);
+      const float dy1 = d.y * act_grad(gm[2 * j + 1] * xh1 + bt[2 * j + 1], act);
+      o[j] = pack_bf16x2(gm[2 * j] * rstd[2 * j] * (dy0 - m1[2 * j] - xh0 * m2[2 * j]),
+                         gm[2 * j + 1] * rstd[2 * j + 1] * (dy1 - m1[2 * j + 1] - xh1 * m2[2 * j + 1]));
     }
-    reinterpret_cast<uint4*>(dpre)[dbase + i] = make_uint4(o[0], o[1], o[2], o[3]);
+    dpb[(size_t)r * cvec] = make_uint4(o[0], o[1], o[2], o[3]);
   }
 }
 
@@ -326,7 +342,7 @@ int dcgan_bn_stats(const void* x, float* sums, int groups, int rows_per_group, i
 int dcgan_bn_apply(const void* x, void* y, const float* sums, const float* gamma, const float* beta, float* saved,
                    float* ema_mean, float* ema_var, int groups, int rows_per_group, int C, float eps, float decay,
                    int act, int use_ema, cudaStream_t st) {
-  if (C % 8) return DCGAN_ERR_SHAPE;
+  if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
   bn_apply_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(
@@ -350,7 +366,7 @@ int dcgan_bn_bwd_reduce(const void* da, const void* pre, const float* saved, con
 int dcgan_bn_bwd_apply(const void* da, const void* pre, void* dpre, const float* saved, const float* gamma,
                        const float* beta, const float* red, float* dgamma, float* dbeta, int groups,
                        int stat_groups, int param_groups, int rows_per_group, int C, int act, cudaStream_t st) {
-  if (C % 8) return DCGAN_ERR_SHAPE;
+  if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
   bn_bwd_apply_kernel<<<grid, kBnThreads, 6 * C * sizeof(float), st>>>(
