@@ -81,40 +81,56 @@ c3_fprop_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w
 // epilogue: mode 0: act(v + bias); mode 1: v * (1 - aux^2)   (tanh backward against aux = tanh output)
 // grid = (tiles per image, N)
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kC3Threads)
+constexpr int kTQ = 2;             // input locations per thread (rows qy and qy + kTH/2 of the tile): the
+                                   // broadcast filter reads from shared memory are the bottleneck, so each
+                                   // filter value fetched feeds kTQ pixels
+constexpr int kTconvThreads = kC3Threads / kTQ;
+__global__ void __launch_bounds__(kTconvThreads)
 c3_tconv_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                 const __nv_bfloat16* __restrict__ aux, __nv_bfloat16* __restrict__ out,
                 float* __restrict__ colsum /* optional [3]: += per-channel sum of the f32 results */, int H, int W,
                 int C, int act, int mode) {
   extern __shared__ float ws[];  // [25][3][C]
-  for (int i = threadIdx.x; i < 75 * C; i += kC3Threads) ws[i] = w[i];
+  for (int i = threadIdx.x; i < 75 * C; i += kTconvThreads) ws[i] = w[i];
   __syncthreads();
   const int tiles_x = W / kTW;
-  const int qy = (blockIdx.x / tiles_x) * kTH + threadIdx.x / kTW;
+  const int qy0 = (blockIdx.x / tiles_x) * kTH + threadIdx.x / kTW;  // + q * (kTH / kTQ)
   const int qx = (blockIdx.x % tiles_x) * kTW + threadIdx.x % kTW;
   const int n = blockIdx.y;
-  float acc[2][2][3];
+  float acc[kTQ][2][2][3];
 #pragma unroll
-  for (int a = 0; a < 2; ++a)
+  for (int q = 0; q < kTQ; ++q)
 #pragma unroll
-    for (int b = 0; b < 2; ++b)
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
-      for (int c = 0; c < 3; ++c) acc[a][b][c] = 0.f;
+      for (int b = 0; b < 2; ++b)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) acc[q][a][b][c] = 0.f;
 
 #pragma unroll
   for (int dy = -1; dy <= 1; ++dy) {
 #pragma unroll
     for (int dx = -1; dx <= 1; ++dx) {
-      const int iy = qy + dy, ix = qx + dx;
-      if ((unsigned)iy >= (unsigned)H || (unsigned)ix >= (unsigned)W) continue;
-      const uint4* xp = reinterpret_cast<const uint4*>(x + (((size_t)n * H + iy) * W + ix) * C);
+      const int ix = qx + dx;
+      const uint4* xp[kTQ];
+      bool valid[kTQ];
+#pragma unroll
+      for (int q = 0; q < kTQ; ++q) {
+        const int iy = qy0 + q * (kTH / kTQ) + dy;
+        valid[q] = (unsigned)iy < (unsigned)H && (unsigned)ix < (unsigned)W;
+        xp[q] = reinterpret_cast<const uint4*>(x + (((size_t)n * H + (valid[q] ? iy : 0)) * W + (valid[q] ? ix : 0)) * C);
+      }
 #pragma unroll 1
       for (int cb = 0; cb < C / 8; ++cb) {
-        const uint4 v = __ldg(xp + cb);
-        float xf[8];
-        { float2 f;
-          f = unpack_bf16x2(v.x); xf[0] = f.x; xf[1] = f.y; f = unpack_bf16x2(v.y); xf[2] = f.x; xf[3] = f.y;
-          f = unpack_bf16x2(v.z); xf[4] = f.x; xf[5] = f.y; f = unpack_bf16x2(v.w); xf[6] = f.x; xf[7] = f.y; }
+        float xf[kTQ][8];
+#pragma unroll
+        for (int q = 0; q < kTQ; ++q) {
+          uint4 v = make_uint4(0, 0, 0, 0);
+          if (valid[q]) v = __ldg(xp[q] + cb);
+          float2 f;
+          f = unpack_bf16x2(v.x); xf[q][0] = f.x; xf[q][1] = f.y; f = unpack_bf16x2(v.y); xf[q][2] = f.x; xf[q][3] = f.y;
+          f = unpack_bf16x2(v.z); xf[q][4] = f.x; xf[q][5] = f.y; f = unpack_bf16x2(v.w); xf[q][6] = f.x; xf[q][7] = f.y;
+        }
 #pragma unroll
         for (int ph = 0; ph < 2; ++ph) {
           const int kh = ph + 1 - 2 * dy;
@@ -127,8 +143,10 @@ c3_tconv_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w
             for (int co = 0; co < 3; ++co) {
               const float4* wp = reinterpret_cast<const float4*>(ws + ((kh * 5 + kw) * 3 + co) * C + cb * 8);
               const float4 w0 = wp[0], w1 = wp[1];
-              acc[ph][pw][co] += xf[0] * w0.x + xf[1] * w0.y + xf[2] * w0.z + xf[3] * w0.w + xf[4] * w1.x +
-                                 xf[5] * w1.y + xf[6] * w1.z + xf[7] * w1.w;
+#pragma unroll
+              for (int q = 0; q < kTQ; ++q)
+                acc[q][ph][pw][co] += xf[q][0] * w0.x + xf[q][1] * w0.y + xf[q][2] * w0.z + xf[q][3] * w0.w +
+                                      xf[q][4] * w1.x + xf[q][5] * w1.y + xf[q][6] * w1.z + xf[q][7] * w1.w;
             }
           }
         }
@@ -138,30 +156,34 @@ c3_tconv_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w
   const int oH = 2 * H, oW = 2 * W;
   float csum[3] = {0.f, 0.f, 0.f};
 #pragma unroll
-  for (int ph = 0; ph < 2; ++ph) {
-    const size_t o = (((size_t)n * oH + 2 * qy + ph) * oW + 2 * qx) * 3;  // 6 contiguous bf16
-    float v[6];
+  for (int q = 0; q < kTQ; ++q) {
+    const int qy = qy0 + q * (kTH / kTQ);
 #pragma unroll
-    for (int pw = 0; pw < 2; ++pw)
+    for (int ph = 0; ph < 2; ++ph) {
+      const size_t o = (((size_t)n * oH + 2 * qy + ph) * oW + 2 * qx) * 3;  // 6 contiguous bf16
+      float v[6];
 #pragma unroll
-      for (int co = 0; co < 3; ++co) v[pw * 3 + co] = acc[ph][pw][co];
-    if (mode == 0) {
+      for (int pw = 0; pw < 2; ++pw)
 #pragma unroll
-      for (int j = 0; j < 6; ++j) v[j] = apply_act(v[j] + (bias ? bias[j % 3] : 0.f), act);
-    } else {
-      const uint32_t* ap = reinterpret_cast<const uint32_t*>(aux + o);
+        for (int co = 0; co < 3; ++co) v[pw * 3 + co] = acc[q][ph][pw][co];
+      if (mode == 0) {
 #pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        const float2 a = unpack_bf16x2(ap[j]);
-        v[2 * j] *= (1.f - a.x * a.x);
-        v[2 * j + 1] *= (1.f - a.y * a.y);
+        for (int j = 0; j < 6; ++j) v[j] = apply_act(v[j] + (bias ? bias[j % 3] : 0.f), act);
+      } else {
+        const uint32_t* ap = reinterpret_cast<const uint32_t*>(aux + o);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const float2 a = unpack_bf16x2(ap[j]);
+          v[2 * j] *= (1.f - a.x * a.x);
+          v[2 * j + 1] *= (1.f - a.y * a.y);
+        }
       }
+#pragma unroll
+      for (int j = 0; j < 6; ++j) csum[j % 3] += v[j];
+      uint32_t* op = reinterpret_cast<uint32_t*>(out + o);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) op[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
     }
-#pragma unroll
-    for (int j = 0; j < 6; ++j) csum[j % 3] += v[j];
-    uint32_t* op = reinterpret_cast<uint32_t*>(out + o);
-#pragma unroll
-    for (int j = 0; j < 3; ++j) op[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
   }
   if (colsum != nullptr) {  // bias gradient of the 3-channel layer, reduced in f32 before the bf16 rounding
     __shared__ float cred[3];
@@ -288,7 +310,7 @@ int dcgan_c3_tconv(const void* x, const float* w, const float* bias, const void*
     if (smem > 100 * 1024) return DCGAN_ERR_SHAPE;
   }
   dim3 grid((H / kTH) * (W / kTW), N);
-  c3_tconv_kernel<<<grid, kC3Threads, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), w, bias,
+  c3_tconv_kernel<<<grid, kTconvThreads, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), w, bias,
                                                   reinterpret_cast<const __nv_bfloat16*>(aux),
                                                   reinterpret_cast<__nv_bfloat16*>(out), colsum, H, W, C, act, mode);
   return LAUNCH_OK();

@@ -1,0 +1,382 @@
+// Tensor-core versions of the 3-channel strided layer and its filter gradient.
+//
+// d_h0_conv (64x64x3 -> 32x32x64, distriubted_model.py:118) and the data gradient of g_h4 have
+// K = 5*5*3 = 75, far too skinny for the generic implicit-GEMM pipeline, and on the CUDA cores they
+// are bound by FP32 issue rate (profiles/launches_step_v1.csv: 75 us and 77 us).  Here the im2col
+// operand is built in shared memory, once per 128-pixel tile, straight into the 128B-swizzled UMMA
+// layout with K padded to 5 x 16 (each filter row kh = 15 taps*channels + 1 zero), and fed to
+// tcgen05.mma with the accumulator in TMEM:
+//
+//   c3_fprop_tc : out[128 px][64 co] = im2col[128 px][80] . W[64 co][80]^T      (K-major A and B)
+//   c3_wgrad_tc : dW[80][64 co]     += im2col[px][80]^T   . dy[px][64 co]      (MN-major A and B, K = pixels,
+//                 accumulated in TMEM over all tiles of the CTA, one f32 atomic pass at the end)
+//
+// Both then run at memory speed.  Filter layout is the shared [25][3][C] of csrc/conv_c3.cu.
+#include "common.cuh"
+#include "../include/dcgan_b200.h"
+
+namespace dcgan {
+
+constexpr int kTcThreads = 128;
+constexpr int kPatchMaxElems = 4096;       // bf16; covers tiles of 4x32 (2288), 2x64 (2800), 1x128 (3920) pixels
+
+// 16-byte chunk (row, chunk) of a [rows][128 B] tile in the SWIZZLE_128B pattern
+__device__ __forceinline__ uint32_t swz(uint32_t row, uint32_t chunk) {
+  return row * 128u + ((chunk ^ (row & 7u)) << 4);
+}
+
+struct TileGeom {
+  int W_out, rows_per_tile, patch_h, patch_w3, patch_pitch;  // patch_w3 = patch width * 3, pitch in bf16
+};
+__device__ __forceinline__ TileGeom make_geom(int W_out) {
+  TileGeom g;
+  g.W_out = W_out;
+  g.rows_per_tile = 128 / W_out;
+  g.patch_h = 2 * g.rows_per_tile + 3;
+  g.patch_w3 = (2 * W_out + 3) * 3;
+  g.patch_pitch = (g.patch_w3 + 7) & ~7;
+  return g;
+}
+
+// input patch (3 channels) of one tile -> smem bf16.  A tile spans full image rows, so the patch columns of
+// pixel -1 and of pixels >= W are always padding (TF SAME: 1 before, 2 after): they are zeroed once per
+// kernel by zero_patch(); per tile only the in-image part of each row is copied, as 32-bit words with all
+// loads of a thread in flight before the first store.
+__device__ __forceinline__ void zero_patch(__nv_bfloat16* patch) {
+  for (int i = threadIdx.x; i < kPatchMaxElems / 8; i += kTcThreads)
+    reinterpret_cast<uint4*>(patch)[i] = make_uint4(0, 0, 0, 0);
+}
+
+constexpr int kPatchWordsPerThread = 15;  // 5 rows * 384 words / 128 threads (the 1x128 tile)
+
+__device__ __forceinline__ void fetch_patch(const __nv_bfloat16* __restrict__ x, uint32_t (&v)[kPatchWordsPerThread],
+                                            int n, int oy0, int H, int W, const TileGeom& g) {
+  const int iy0 = 2 * oy0 - 1;
+  const int words_per_row = (3 * W) >> 1;       // 32-bit words of one image row (W even)
+  const int total = g.patch_h * words_per_row;  // <= 11 * 96 = 1056, 7 * 192 = 1344, 5 * 384 = 1920
+#pragma unroll
+  for (int k = 0; k < kPatchWordsPerThread; ++k) {
+    const int i = threadIdx.x + k * kTcThreads;
+    v[k] = 0u;
+    if (i < total) {
+      const int r = i / words_per_row, wcol = i - r * words_per_row;
+      const int iy = iy0 + r;
+      if ((unsigned)iy < (unsigned)H)
+        v[k] = __ldg(reinterpret_cast<const uint32_t*>(x + ((size_t)n * H + iy) * W * 3) + wcol);
+    }
+  }
+}
+
+__device__ __forceinline__ void commit_patch(__nv_bfloat16* patch, const uint32_t (&v)[kPatchWordsPerThread], int W,
+                                             const TileGeom& g) {
+  const int words_per_row = (3 * W) >> 1;
+  const int total = g.patch_h * words_per_row;
+#pragma unroll
+  for (int k = 0; k < kPatchWordsPerThread; ++k) {
+    const int i = threadIdx.x + k * kTcThreads;
+    if (i < total) {
+      const int r = i / words_per_row, wcol = i - r * words_per_row;
+      // pixel 0 sits at element 3 of the patch row (element 0..2 = pixel -1): odd offset -> two 16-bit stores
+      unsigned short* dst = reinterpret_cast<unsigned short*>(patch) + r * g.patch_pitch + 3 + 2 * wcol;
+      dst[0] = (unsigned short)(v[k] & 0xffffu);
+      dst[1] = (unsigned short)(v[k] >> 16);
+    }
+  }
+}
+
+// im2col row of pixel `t` of the tile: chunks 0..9 (k = kh*16 + kw*3 + ci) of its 256-byte row, split over the
+// two k-block sub-tiles.  Chunks 10..15 stay zero (written once at kernel start).
+__device__ __forceinline__ void build_im2col_row(uint8_t* a_tiles, const __nv_bfloat16* patch, int t, const TileGeom& g) {
+  const int ty = t / g.W_out, tx = t - ty * g.W_out;
+#pragma unroll
+  for (int kh = 0; kh < 5; ++kh) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(patch + (2 * ty + kh) * g.patch_pitch + 6 * tx);
+    uint32_t w[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) w[j] = src[j];  // 16 bf16: 15 taps*channels + 1 neighbour element
+    w[7] &= 0x0000ffffu;                        // k = kh*16 + 15 is padding
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int c = kh * 2 + half;              // chunk index 0..9 within the 16-chunk row
+      uint8_t* dst = a_tiles + (c >> 3) * (128 * 128) + swz(t, c & 7);
+      *reinterpret_cast<uint4*>(dst) = make_uint4(w[4 * half], w[4 * half + 1], w[4 * half + 2], w[4 * half + 3]);
+    }
+  }
+}
+
+__device__ __forceinline__ void zero_im2col_padding(uint8_t* a_tiles, int t) {
+#pragma unroll
+  for (int c = 10; c < 16; ++c)
+    *reinterpret_cast<uint4*>(a_tiles + (c >> 3) * (128 * 128) + swz(t, c & 7)) = make_uint4(0, 0, 0, 0);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// forward: grid = (CTAs, C/64).  smem: A 32 KiB | B 16 KiB | patch | barrier
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTcThreads)
+c3_fprop_tc_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                   __nv_bfloat16* __restrict__ out, int N, int H, int W, int C, int act, int* err_flag) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_tiles = smem;                       // 2 x [128][128 B]
+  uint8_t* b_tiles = smem + 32768;               // 2 x [64][128 B]
+  __nv_bfloat16* patch = reinterpret_cast<__nv_bfloat16*>(smem + 32768 + 16384);
+  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(smem + 32768 + 16384 + kPatchMaxElems * 2);
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(mma_bar + 1);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+
+  const int t = threadIdx.x, warp = t >> 5;
+  const int oH = H / 2, oW = W / 2;
+  const TileGeom g = make_geom(oW);
+  const int c0 = blockIdx.y * 64;
+
+  if (t == 0) { mbar_init(mma_bar, 1); *abort_flag = 0; fence_mbar_init(); }
+  if (warp == 0) { tmem_alloc(tmem_ptr_smem, 64); tmem_relinquish(); }
+  // B operand: W[co][k] with k = kh*16 + kw*3 + ci, bf16, K-major SW128, zero padded
+  for (int i = t; i < 16384 / 16; i += kTcThreads) reinterpret_cast<uint4*>(b_tiles)[i] = make_uint4(0, 0, 0, 0);
+  zero_im2col_padding(a_tiles, t);
+  zero_patch(patch);
+  {
+    // thread -> output channel co = t & 63 and every other filter row; all 38 loads in flight first
+    const int co = t & 63, r0 = t >> 6;
+    float wv[38];
+#pragma unroll
+    for (int j = 0; j < 38; ++j) {
+      const int row = r0 + 2 * j;                   // row = (kh*5+kw)*3+ci = kh*15 + kk
+      wv[j] = row < 75 ? __ldg(w + (size_t)row * C + c0 + co) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 38; ++j) {
+      const int row = r0 + 2 * j;
+      if (row < 75) {
+        const int kh = row / 15, kk = row - kh * 15;
+        const int k = kh * 16 + kk;
+        uint8_t* dst = b_tiles + (k >> 6) * (64 * 128) + swz(co, (k & 63) >> 3) + (k & 7) * 2;
+        *reinterpret_cast<__nv_bfloat16*>(dst) = __float2bfloat16(wv[j]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t a_addr = smem_u32(a_tiles), b_addr = smem_u32(b_tiles);
+  constexpr uint32_t idesc = make_idesc_bf16(128, 64, 0, 0);
+
+  const int tiles_per_img = oH * oW / 128;
+  const int tiles = N * tiles_per_img;
+  uint32_t phase = 0;
+  uint32_t pv[kPatchWordsPerThread];  // the next tile's patch, in flight while this tile computes
+  if ((int)blockIdx.x < tiles) {
+    const int n = blockIdx.x / tiles_per_img;
+    fetch_patch(x, pv, n, (blockIdx.x - n * tiles_per_img) * g.rows_per_tile, H, W, g);
+  }
+  // per-channel bias of this thread's epilogue columns is loop invariant: keep it in shared memory
+  float* bias_s = reinterpret_cast<float*>(smem + 32768 + 16384 + kPatchMaxElems * 2 + 64);
+  if (t < 64) bias_s[t] = bias != nullptr ? bias[c0 + t] : 0.f;
+  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int n = tile / tiles_per_img;
+    const int oy0 = (tile - n * tiles_per_img) * g.rows_per_tile;
+    commit_patch(patch, pv, W, g);
+    __syncthreads();
+    {
+      const int nt = tile + gridDim.x;
+      if (nt < tiles) {
+        const int nn = nt / tiles_per_img;
+        fetch_patch(x, pv, nn, (nt - nn * tiles_per_img) * g.rows_per_tile, H, W, g);
+      }
+    }
+    build_im2col_row(a_tiles, patch, t, g);
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (t == 0) {
+      tc_fence_after();
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {  // K = 80 = 4 steps in k-block 0 + 1 step in k-block 1
+        const uint32_t off = (k < 4) ? k * 32u : 0u;
+        const uint64_t da = make_smem_desc_sw128(a_addr + (k >> 2) * 16384 + off, 16, 1024);
+        const uint64_t db = make_smem_desc_sw128(b_addr + (k >> 2) * 8192 + off, 16, 1024);
+        umma_bf16(tmem_base, da, db, idesc, k != 0 ? 1u : 0u);
+      }
+      umma_commit(mma_bar);
+    }
+    const bool ok = mbar_wait(mma_bar, phase, abort_flag, err_flag);
+    phase ^= 1;
+    tc_fence_after();
+    // epilogue: thread t = pixel t of the tile = TMEM lane t
+    const int ty = t / oW, tx = t - ty * oW;
+    __nv_bfloat16* orow = out + (((size_t)n * oH + oy0 + ty) * oW + tx) * C + c0;
+#pragma unroll
+    for (int c = 0; c < 64; c += 32) {
+      uint32_t v[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16) + c, v);
+      tmem_ld_wait();
+      if (ok) {
+        uint32_t packed[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float a = __uint_as_float(v[2 * j]) + bias_s[c + 2 * j];
+          const float b = __uint_as_float(v[2 * j + 1]) + bias_s[c + 2 * j + 1];
+          packed[j] = pack_bf16x2(apply_act(a, act), apply_act(b, act));
+        }
+        uint4* dst = reinterpret_cast<uint4*>(orow + c);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+      }
+    }
+    tc_fence_before();
+    __syncthreads();  // TMEM drained and the A tile consumed before the next tile overwrites them
+  }
+  if (warp == 0) tmem_dealloc(tmem_base, 64);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// filter gradient: grid = (CTAs, C/64).  smem: A 32 KiB | B 16 KiB (dy tile) | patch | barrier
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTcThreads)
+c3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ x3, const __nv_bfloat16* __restrict__ y, float* __restrict__ dw,
+                   int N, int Hs, int Ws, int C, int* err_flag) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_tiles = smem;                       // 2 x [128 px][128 B]  (MN-major A: M = k index)
+  uint8_t* b_tile = smem + 32768;                // [128 px][128 B]      (MN-major B: N = 64 channels)
+  __nv_bfloat16* patch = reinterpret_cast<__nv_bfloat16*>(smem + 32768 + 16384);
+  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(smem + 32768 + 16384 + kPatchMaxElems * 2);
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(mma_bar + 1);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+
+  const int t = threadIdx.x, warp = t >> 5;
+  const int H = 2 * Hs, W = 2 * Ws;
+  const TileGeom g = make_geom(Ws);
+  const int c0 = blockIdx.y * 64;
+
+  if (t == 0) { mbar_init(mma_bar, 1); *abort_flag = 0; fence_mbar_init(); }
+  if (warp == 0) { tmem_alloc(tmem_ptr_smem, 64); tmem_relinquish(); }
+  zero_im2col_padding(a_tiles, t);
+  zero_patch(patch);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t a_addr = smem_u32(a_tiles), b_addr = smem_u32(b_tile);
+  constexpr uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);
+
+  const int tiles_per_img = Hs * Ws / 128;
+  const int tiles = N * tiles_per_img;
+  uint32_t phase = 0;
+  bool any = false, ok = true;
+  uint32_t pv[kPatchWordsPerThread];  // next tile's patch and dy row, fetched while this tile's MMAs run
+  uint4 yv[8];
+  auto fetch = [&](int tile) {
+    const int n = tile / tiles_per_img;
+    const int qy0 = (tile - n * tiles_per_img) * g.rows_per_tile;
+    const uint4* src = reinterpret_cast<const uint4*>(y + ((size_t)(n * Hs + qy0) * Ws + t) * C + c0);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) yv[j] = __ldg(src + j);
+    fetch_patch(x3, pv, n, qy0, H, W, g);
+  };
+  if ((int)blockIdx.x < tiles) fetch(blockIdx.x);
+  for (int tile = blockIdx.x; tile < tiles && ok; tile += gridDim.x) {
+    if (any) {  // the previous tile's MMAs must retire before its operands are overwritten
+      ok = mbar_wait(mma_bar, phase, abort_flag, err_flag);
+      phase ^= 1;
+    }
+    // dy rows of this tile: pixel t -> 128 contiguous bytes, swizzled into the B tile
+#pragma unroll
+    for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(b_tile + swz(t, j)) = yv[j];
+    commit_patch(patch, pv, W, g);
+    __syncthreads();
+    if (tile + (int)gridDim.x < tiles) fetch(tile + gridDim.x);
+    build_im2col_row(a_tiles, patch, t, g);
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (t == 0) {
+      tc_fence_after();
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {  // K = 128 pixels of the tile, 16 per instruction
+        const uint64_t da = make_smem_desc_sw128(a_addr + k * 2048, 16384, 1024);  // 2 chunks of 64 k-indices
+        const uint64_t db = make_smem_desc_sw128(b_addr + k * 2048, 16384, 1024);  // one chunk of 64 channels
+        umma_bf16(tmem_base, da, db, idesc, (any || k != 0) ? 1u : 0u);
+      }
+      umma_commit(mma_bar);
+    }
+    any = true;
+  }
+  if (any && ok) ok = mbar_wait(mma_bar, phase, abort_flag, err_flag);
+  tc_fence_after();
+  // epilogue: TMEM lane m = padded k index kh*16 + kk; rows with kk == 15 or m >= 80 are padding
+  const int m = t;
+  const int kh = m >> 4, kk = m & 15;
+  const bool real = any && ok && m < 80 && kk < 15;
+  float* orow = dw + (size_t)(kh * 15 + kk) * C + c0;
+#pragma unroll
+  for (int c = 0; c < 64; c += 32) {
+    uint32_t v[32];
+    tmem_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16) + c, v);
+    tmem_ld_wait();
+    if (real) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) atomicAdd(orow + c + j, __uint_as_float(v[j]));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 64);
+}
+
+constexpr int kTcSmem = 32768 + 16384 + kPatchMaxElems * 2 + 64 + 256 + 1024;
+
+}  // namespace dcgan
+
+using namespace dcgan;
+
+static int g_c3_blocks_fprop = 0, g_c3_blocks_wgrad = 0;  // 0 = default; profiling overrides
+
+extern "C" {
+
+void dcgan_set_c3_tuning(int fprop_blocks, int wgrad_blocks) {
+  g_c3_blocks_fprop = fprop_blocks;
+  g_c3_blocks_wgrad = wgrad_blocks;
+}
+
+int dcgan_c3_fprop_tc(const void* x, const float* w, const float* bias, void* out, int N, int H, int W, int C,
+                      int act, cudaStream_t st) {
+  const int oH = H / 2, oW = W / 2;
+  if (C % 64 || (H & 1) || (W & 1) || (oW != 32 && oW != 64 && oW != 128) || (oH * oW) % 128) return DCGAN_ERR_SHAPE;
+  static bool attr = false;
+  if (!attr) {
+    if (cudaFuncSetAttribute(c3_fprop_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem) != cudaSuccess)
+      return DCGAN_ERR_LAUNCH;
+    attr = true;
+  }
+  int* err = error_flag_ptr();
+  if (!err) return DCGAN_ERR_DRIVER;
+  const int tiles = N * oH * oW / 128;
+  const int cap_f = g_c3_blocks_fprop > 0 ? g_c3_blocks_fprop : 148 * 3;
+  dim3 grid(tiles < cap_f ? tiles : cap_f, C / 64);
+  c3_fprop_tc_kernel<<<grid, kTcThreads, kTcSmem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), w, bias,
+                                                        reinterpret_cast<__nv_bfloat16*>(out), N, H, W, C, act, err);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_c3_wgrad_tc(const void* x3, const void* y, float* dw, int N, int Hs, int Ws, int C, cudaStream_t st) {
+  if (C % 64 || (Ws != 32 && Ws != 64 && Ws != 128) || (Hs * Ws) % 128) return DCGAN_ERR_SHAPE;
+  static bool attr = false;
+  if (!attr) {
+    if (cudaFuncSetAttribute(c3_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem) != cudaSuccess)
+      return DCGAN_ERR_LAUNCH;
+    attr = true;
+  }
+  int* err = error_flag_ptr();
+  if (!err) return DCGAN_ERR_DRIVER;
+  const int tiles = N * Hs * Ws / 128;
+  const int cap_w = g_c3_blocks_wgrad > 0 ? g_c3_blocks_wgrad : 148;  // few CTAs: the final f32 atomics contend per address
+  dim3 grid(tiles < cap_w ? tiles : cap_w, C / 64);
+  c3_wgrad_tc_kernel<<<grid, kTcThreads, kTcSmem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x3),
+                                                        reinterpret_cast<const __nv_bfloat16*>(y), dw, N, Hs, Ws, C, err);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+}  // extern "C"

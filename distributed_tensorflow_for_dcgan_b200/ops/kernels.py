@@ -72,12 +72,20 @@ def conv_wgrad(big, small, dw, splits=0, block_n=0):
     return dw
 
 
-def c3_fprop(x, w, bias=None, act="none", out=None):
+def _tc_width_ok(w_out: int, h_out: int) -> bool:
+    return w_out in (32, 64, 128) and (h_out * w_out) % 128 == 0
+
+
+def c3_fprop(x, w, bias=None, act="none", out=None, tensor_cores=True):
+    """3 -> C strided conv; tensor-core kernel when the output width allows, CUDA-core kernel otherwise."""
     N, H, W, _ = x.shape
     C = w.shape[-1]
     if out is None:
         out = _bf16((N, H // 2, W // 2, C), x)
-    call("dcgan_c3_fprop", ptr(x), ptr(w), ptr(bias), ptr(out), N, H, W, C, ACT[act])
+    if tensor_cores and _tc_width_ok(W // 2, H // 2):
+        call("dcgan_c3_fprop_tc", ptr(x), ptr(w), ptr(bias), ptr(out), N, H, W, C, ACT[act])
+    else:
+        call("dcgan_c3_fprop", ptr(x), ptr(w), ptr(bias), ptr(out), N, H, W, C, ACT[act])
     return out
 
 
@@ -91,9 +99,12 @@ def c3_tconv(x, w, bias=None, act="none", aux=None, out=None, colsum=None):
     return out
 
 
-def c3_wgrad(x3, y, dw):
+def c3_wgrad(x3, y, dw, tensor_cores=True):
     N, Hs, Ws, C = y.shape
-    call("dcgan_c3_wgrad", ptr(x3), ptr(y), ptr(dw), N, Hs, Ws, C)
+    if tensor_cores and _tc_width_ok(Ws, Hs):
+        call("dcgan_c3_wgrad_tc", ptr(x3), ptr(y), ptr(dw), N, Hs, Ws, C)
+    else:
+        call("dcgan_c3_wgrad", ptr(x3), ptr(y), ptr(dw), N, Hs, Ws, C)
     return dw
 
 

@@ -94,6 +94,12 @@ int dcgan_c3_tconv(const void* x, const float* w, const float* bias, const void*
 /* dw[25][3][C] += sum x3[N,2Hs,2Ws,3] (gathered) * y[N,Hs,Ws,C]   (f32 atomics; zero first). */
 int dcgan_c3_wgrad(const void* x3, const void* y, float* dw, int N, int Hs, int Ws, int C, cudaStream_t stream);
 
+/* Tensor-core versions (csrc/conv_c3_tc.cu): im2col built in shared memory in the UMMA layout (K padded to
+ * 5x16), tcgen05.mma with TMEM accumulators.  Output width (W/2, resp. Ws) must be 32, 64 or 128. */
+int dcgan_c3_fprop_tc(const void* x, const float* w, const float* bias, void* out, int N, int H, int W, int C,
+                      int act, cudaStream_t stream);
+int dcgan_c3_wgrad_tc(const void* x3, const void* y, float* dw, int N, int Hs, int Ws, int C, cudaStream_t stream);
+
 /* ---- batch norm fused with its activation (csrc/bn_act.cu; reference distriubted_model.py:15-52) --
  * x/y/da/dpre are bf16 [groups*rows_per_group][C]; sums/saved/red are f32 [groups][2][C]. */
 int dcgan_bn_stats(const void* x, float* sums, int groups, int rows_per_group, int C, cudaStream_t stream);

@@ -13,7 +13,8 @@ eng = DCGANEngine(cfg, seed=3)
 torch.manual_seed(0)
 real = torch.rand(B, 64, 64, 3, device="cuda") * 2 - 1
 z = torch.rand(B, cfg.z_dim, device="cuda") * 2 - 1
-p0 = {k: v.detach().clone() for k, v in eng.params.items()}
+p0 = {k: (v.detach().to(torch.bfloat16).float() if (k.endswith("/w") or k == "g_h0_lin/Matrix") else v.detach().clone())
+      for k, v in eng.params.items()}
 eng.real_f32.copy_(real); eng.z.copy_(z)
 eng.step_body(); torch.cuda.synchronize()
 losses, grads, G = _oracle_step(p0, cfg, real.to(torch.bfloat16).float(), z)

@@ -31,8 +31,11 @@ def test_engine_step_matches_oracle(cuda_lib):
     B = cfg.batch_size
     real = (torch.rand(B, 64, 64, 3, device="cuda") * 2 - 1)
     z = torch.rand(B, cfg.z_dim, device="cuda") * 2 - 1
-    # the oracle consumes the same bf16-rounded weights / inputs the kernels see
-    p0 = {k: v.detach().clone() for k, v in eng.params.items()}
+    # the oracle consumes the same bf16-rounded weights / inputs the tensor-core kernels see (filters and
+    # g_h0_lin/Matrix are used through the bf16 shadow; biases, batch-norm parameters and d_h3_lin stay f32)
+    p_master = {k: v.detach().clone() for k, v in eng.params.items()}
+    p0 = {k: (v.to(torch.bfloat16).float() if (k.endswith("/w") or k == "g_h0_lin/Matrix") else v.clone())
+          for k, v in p_master.items()}
     eng.real_f32.copy_(real)
     eng.z.copy_(z)
     eng.step_body()
@@ -60,14 +63,14 @@ def test_engine_step_matches_oracle(cuda_lib):
         # bf16 activations / activation gradients through up to nine layers: direction within ~1%
         # (the 3-element g_h4 bias gradient is a heavily cancelling sum over 262k pixels: judge its
         # direction only)
-        ok = cos > 0.975 and (err <= 0.35 * den or ref.numel() < 16)
+        ok = (cos > 0.975 and err <= 0.35 * den) if ref.numel() >= 16 else cos > 0.9
         assert ok, f"{name}: cos {cos} err {err} max {den}"
     assert skipped == 6
     assert eng.counters.tolist() == [1, 1]
     # Adam applied to the engine's own gradients equals the TF-form reference update
     from distributed_tensorflow_for_dcgan_b200.optim.adam_tf import adam_tf_step_
     for name in ("d_h2_conv/w", "g_h1/w", "g_bn2/gamma", "d_h3_lin/Matrix"):
-        pr = p0[name].clone()
+        pr = p_master[name].clone()
         g = eng.grad_views[name].clone()
         adam_tf_step_(pr, g, torch.zeros_like(pr), torch.zeros_like(pr), 1)
         assert torch.allclose(eng.params[name], pr, rtol=1e-5, atol=1e-7), name

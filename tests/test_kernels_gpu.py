@@ -120,13 +120,16 @@ def test_conv_wgrad_deconv_layer(cuda_lib):
     _close(dw.view(5, 5, Cout, Cin), ref, rel=2e-3, name="deconv_wgrad")
 
 
-def test_c3_fprop(cuda_lib):
+@pytest.mark.parametrize("tc", [True, False])
+@pytest.mark.parametrize("S,C", [(64, 64), (128, 128)])
+def test_c3_fprop(cuda_lib, tc, S, C):
     from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
-    x = _rand((3, 64, 64, 3))
-    w = torch.randn(5, 5, 3, 64, device="cuda") * 0.05
-    b = torch.randn(64, device="cuda") * 0.1
-    out = K.c3_fprop(x, w, b, act="lrelu")
-    ref = Fn.lrelu(Fn.conv2d_same(x.float(), w, b))
+    x = _rand((3, S, S, 3))
+    w = torch.randn(5, 5, 3, C, device="cuda") * 0.05
+    b = torch.randn(C, device="cuda") * 0.1
+    out = K.c3_fprop(x, w, b, act="lrelu", tensor_cores=tc)
+    ref = Fn.lrelu(Fn.conv2d_same(x.float(), w.to(torch.bfloat16).float() if tc else w, b))
+    K.check_device_error()
     _close(out, ref, name="c3_fprop")
 
 
@@ -146,14 +149,17 @@ def test_c3_tconv_fwd_and_tanh_bwd(cuda_lib):
     _close(cs, ref2.sum((0, 1, 2)), rel=2e-3, name="c3_tconv colsum")
 
 
-def test_c3_wgrad(cuda_lib):
+@pytest.mark.parametrize("tc", [True, False])
+@pytest.mark.parametrize("S,C", [(64, 64), (128, 128)])
+def test_c3_wgrad(cuda_lib, tc, S, C):
     from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
-    x3 = _rand((4, 64, 64, 3))
-    y = _rand((4, 32, 32, 64))
-    dw = torch.zeros(5, 5, 3, 64, device="cuda")
-    K.c3_wgrad(x3, y, dw)
-    w = torch.zeros(5, 5, 3, 64, device="cuda", requires_grad=True)
+    x3 = _rand((4, S, S, 3))
+    y = _rand((4, S // 2, S // 2, C))
+    dw = torch.zeros(5, 5, 3, C, device="cuda")
+    K.c3_wgrad(x3, y, dw, tensor_cores=tc)
+    w = torch.zeros(5, 5, 3, C, device="cuda", requires_grad=True)
     ref, = torch.autograd.grad(Fn.conv2d_same(x3.float(), w), w, y.float())
+    K.check_device_error()
     _close(dw, ref, rel=2e-3, name="c3_wgrad")
 
 
