@@ -67,25 +67,30 @@ class AsyncPSComm:
                   engine.beta1, engine.beta2, engine.eps, self.blocks)
 
     def global_step(self) -> int:
-        """Applies of all workers so far (rank 0's counter, read through peer memory)."""
+        """Applies of all workers so far: rank 0's counter, read through peer memory from any rank."""
         torch.cuda.synchronize(self.device)
         if self.rank == 0:
             return int(self.shard_counters[1].item())
-        return -1
+        return int(self.handles["shard_counters"].get_buffer(0, (2,), torch.int64)[1].item())
 
     def gather_state(self, engine) -> None:
-        """Collective: every rank copies the owners' shards (call at a quiescent point)."""
+        """Copies the owners' shards into this rank's arrays through peer memory (not a collective; other
+        workers may keep pushing, so the snapshot is as loosely consistent as the mode itself)."""
         A = engine.arena
         total4 = A.padded // 4
         per4 = (total4 + self.world - 1) // self.world
-        mask = torch.zeros(A.padded, dtype=torch.bool, device=self.device)
-        mask[min(self.rank * per4, total4) * 4:min((self.rank + 1) * per4, total4) * 4] = True
-        dist.barrier()
-        for t in (A.master, A.m, A.v):
-            tmp = torch.where(mask, t, torch.zeros_like(t))
-            dist.all_reduce(tmp)
-            t.copy_(tmp)
+        torch.cuda.synchronize(self.device)
+        for name, local in (("master", A.master), ("adam_m", A.m), ("adam_v", A.v)):
+            hdl = self.handles[name]
+            for r in range(self.world):
+                if r == self.rank:
+                    continue
+                s0, s1 = min(r * per4, total4) * 4, min((r + 1) * per4, total4) * 4
+                if s1 > s0:
+                    local[s0:s1].copy_(hdl.get_buffer(r, (A.padded,), torch.float32)[s0:s1])
+        torch.cuda.synchronize(self.device)
 
     def close(self) -> None:
+        # a worker may only release its shard once nobody pushes to it any more
         torch.cuda.synchronize(self.device)
         dist.barrier()

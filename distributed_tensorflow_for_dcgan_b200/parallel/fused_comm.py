@@ -72,7 +72,9 @@ class FusedComm:
 
     def alloc(self, name: str, numel: int, dtype) -> torch.Tensor:
         """Engine allocation hook: buffers that peers read or write live in symmetric memory."""
-        if name in ("zero_region", "bf16"):
+        if name in ("zero_region", "bf16", "master", "adam_m", "adam_v"):
+            # gradients / bf16 parameters are exchanged every step; the sharded f32 state is peer-mapped too so
+            # that a checkpoint can read the owners' shards without their participation
             return self._symmetric(name, numel, dtype)
         return torch.zeros(numel, dtype=dtype, device=self.device)
 
@@ -129,25 +131,29 @@ class FusedComm:
                   self.state[SLOT_BN].data_ptr(), self.rank, self.world, SLOT_BN)
 
     # ---- sharded state -> full state (checkpoints) ---------------------------------------------------------------------
-    def owned_mask(self, engine) -> torch.Tensor:
-        A = engine.arena
-        mask = torch.zeros(A.padded, dtype=torch.bool, device=self.device)
-        for lo, hi in (self.buckets["g"], self.buckets["d"]):
-            total4 = (hi - lo) // 4
-            per4 = (total4 + self.world - 1) // self.world
-            s0 = lo + min(self.rank * per4, total4) * 4
-            s1 = lo + min((self.rank + 1) * per4, total4) * 4
-            mask[s0:s1] = True
-        return mask
+    def shard_range(self, bucket: str, rank: int):
+        lo, hi = self.buckets[bucket]
+        total4 = (hi - lo) // 4
+        per4 = (total4 + self.world - 1) // self.world
+        return lo + min(rank * per4, total4) * 4, lo + min((rank + 1) * per4, total4) * 4
 
     def gather_state(self, engine) -> None:
-        """Collective: fills every rank's master / Adam slots with the owners' values."""
+        """Fills this rank's master / Adam slots with the owners' shards, read through peer memory.  Not a
+        collective: only the caller (the chief, at a step boundary) takes part.  In sync mode the owners cannot
+        touch their shards until the caller joins the next step's exchange, so the copy is consistent."""
         A = engine.arena
-        mask = self.owned_mask(engine)
-        for t in (A.master, A.m, A.v):
-            tmp = torch.where(mask, t, torch.zeros_like(t))
-            dist.all_reduce(tmp)
-            t.copy_(tmp)
+        torch.cuda.synchronize(self.device)
+        for name, local in (("master", A.master), ("adam_m", A.m), ("adam_v", A.v)):
+            hdl = self.handles[name]
+            for r in range(self.world):
+                if r == self.rank:
+                    continue
+                peer = hdl.get_buffer(r, (A.padded,), torch.float32)
+                for bucket in ("g", "d"):
+                    s0, s1 = self.shard_range(bucket, r)
+                    if s1 > s0:
+                        local[s0:s1].copy_(peer[s0:s1])
+        torch.cuda.synchronize(self.device)
 
     def close(self) -> None:
         torch.cuda.synchronize(self.device)

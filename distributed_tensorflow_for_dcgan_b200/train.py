@@ -124,14 +124,13 @@ def run_worker(FLAGS, role, cfg) -> int:
         elif not use_cuda:
             for t in trainer.params.values():
                 dist.broadcast(t, src=role.cluster.worker_rank(0))
-        elif restored or True:
-            # GPU sync path: comm.attach() already broadcast rank 0's arena; re-broadcast after a restore
-            if comm is not None and restored is not None:
-                dist.broadcast(trainer.engine.arena.master, src=0)
-                dist.broadcast(trainer.engine.arena.m, src=0)
-                dist.broadcast(trainer.engine.arena.v, src=0)
-                dist.broadcast(trainer.engine.counters, src=0)
-                trainer.engine.refresh_compute_weights()
+        elif comm is not None:
+            # GPU path: every worker adopts the chief's (fresh or restored) variables, slots and counters -- the
+            # "wait for the chief to initialise" of managed_session (image_train.py:141)
+            eng = trainer.engine
+            for t in (eng.arena.master, eng.arena.m, eng.arena.v, eng.counters):
+                dist.broadcast(t, src=0)
+            eng.refresh_compute_weights()
 
     replica = 0 if FLAGS.identical_replicas else role.task_index
     images = _make_reader(FLAGS, FLAGS.data_dir, batch, cfg, FLAGS.seed + 17 * replica)

@@ -194,6 +194,9 @@ class EngineTrainer:
 
     @property
     def global_step(self) -> int:
+        comm = self.engine.comm
+        if comm is not None and hasattr(comm, "global_step"):   # async PS: applies of *all* workers
+            return comm.global_step()
         return int(self.engine.counters[1].item())
 
     @property
@@ -206,7 +209,10 @@ class EngineTrainer:
             e.capture()
         real = torch.as_tensor(real)
         z = torch.as_tensor(z)
-        return e.train_step(real, z)
+        d_real, d_fake, g_loss, step = e.train_step(real, z)
+        if e.comm is not None and hasattr(e.comm, "global_step"):
+            step = e.comm.global_step()
+        return d_real, d_fake, g_loss, step
 
     def evaluate_losses(self, real, z):
         """Training-mode forward only (EMA side effect included), no parameter update."""

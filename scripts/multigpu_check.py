@@ -66,8 +66,10 @@ for mc in (False, True):
         fus.optimizer_step("both")
         torch.cuda.synchronize(); dist.barrier()
     K.check_device_error()
-    fus_state = fus.state_dict()   # collective (gathers the sharded master / slots)
+    dist.barrier()
+    fus_state = fus.state_dict()   # reads the owners' shards of master / slots through peer memory
     ref_state = ref.state_dict()
+    dist.barrier()
     worst = 0.0
     for k in ("g_h1/w", "d_h2_conv/w", "g_bn2/gamma", "d_h3_lin/Matrix", "g_h0_lin/Matrix", "d_h1_conv/w/Adam",
               "g_h3/w/Adam_1"):
@@ -132,8 +134,10 @@ log(f"[async ps] pushes total={int(total)} global_step(rank0)={gs} shard_t={int(
 if rank == 0:
     assert gs == int(total), "lost global_step increments"
 assert int(ac.shard_counters[0]) == int(total)
-ac.gather_state(aeng)
-assert torch.isfinite(aeng.arena.master).all()
+if rank == 0:
+    ac.gather_state(aeng)   # one-sided: only the chief takes part
+    assert torch.isfinite(aeng.arena.master).all()
+dist.barrier()
 results["async_total_pushes"] = int(total)
 del aeng, ac
 torch.cuda.synchronize(); dist.barrier()

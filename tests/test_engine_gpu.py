@@ -109,3 +109,23 @@ def test_engine_alternating_mode(cuda_lib):
     for it in range(3):
         out = eng.train_step(real, torch.rand(16, cfg.z_dim, device="cuda") * 2 - 1)
         assert all(v == v for v in out[:3]) and out[3] == it + 1
+
+
+def test_training_driver_on_gpu(cuda_lib, tmp_path):
+    """The launch script end to end on one GPU: step log, chief sample grid, TF-named checkpoint, events."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, os.path.join(root, "image_train.py"), "--device=cuda", "--synthetic_data", "--max_steps=12",
+           "--save_summaries_secs=0", f"--checkpoint_dir={tmp_path}/ckpt", f"--sample_dir={tmp_path}/samples"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=str(tmp_path),
+                       env=dict(os.environ, PYTHONPATH=root))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.startswith("Epoch:")]
+    assert len(lines) == 12 and "step: [12]" in lines[-1]
+    assert "[Sample] d_loss:" in r.stdout and os.path.exists(tmp_path / "samples" / "train_00_0001.png")
+    from distributed_tensorflow_for_dcgan_b200.utils import checkpoint
+    sd = checkpoint.load_latest(str(tmp_path / "ckpt"))
+    assert int(sd["Variable"]) == 12 and sd["d_h3_conv/w"].shape == (5, 5, 256, 512)
+    assert any(f.startswith("events.out.tfevents") for f in os.listdir(tmp_path / "ckpt"))
