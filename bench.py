@@ -45,6 +45,8 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--wide", action="store_true", help="128x128, ngf=ndf=128 (BASELINE.json config 3)")
     ap.add_argument("--sync-bn", action="store_true")
+    ap.add_argument("--mode", default="sync", choices=["sync", "async"],
+                    help="async = parameter-server mode over peer memory (BASELINE.json config 4)")
     return ap.parse_args()
 
 
@@ -163,7 +165,11 @@ def main():
         comm = None
         if world > 1:
             from distributed_tensorflow_for_dcgan_b200.parallel.sync_dp import make_comm
-            comm = make_comm(args.comm, dev, sync_bn=args.sync_bn)
+            if args.mode == "async":
+                from distributed_tensorflow_for_dcgan_b200.parallel.async_ps import AsyncPSComm
+                comm = AsyncPSComm(dev)
+            else:
+                comm = make_comm(args.comm, dev, sync_bn=args.sync_bn)
         eng = DCGANEngine(cfg, device=dev, seed=0, comm=comm)
         if comm is not None:
             comm.attach(eng)
@@ -185,7 +191,9 @@ def main():
         def stage_inputs(i):
             eng.real_f32.copy_(host_real[i % n_host], non_blocking=True)
             eng.z.copy_(host_z[i % n_host], non_blocking=True)
-        parallelism = f"dp{world}" + ("" if world == 1 else f"-{args.comm}")
+        parallelism = f"dp{world}" + ("" if world == 1 else (f"-{args.comm}" if args.mode == "sync" else "-async-ps"))
+        if args.sync_bn:
+            parallelism += "-syncbn"
     else:
         from baseline.ddp_dcgan import BaselineTrainer
         tr = BaselineTrainer(dev, world=world, batch=B, s=S, gf=cfg.gf_dim, df=cfg.df_dim, z_dim=cfg.z_dim,
@@ -263,6 +271,7 @@ def main():
         value = gb * K_steps / (dev_ms / 1e3)
         e2e_value = gb * K_steps / (e2e_ms / 1e3)
         base = None
+        headline = not args.wide and args.mode == "sync" and B == 64 and not args.sync_bn
         try:
             with open(os.path.join(ROOT, "baseline", "measured.json")) as f:
                 base = json.load(f).get("images_per_sec", {}).get(str(world))
@@ -274,12 +283,12 @@ def main():
             "metric": METRIC, "value": round(value, 1), "unit": "images/s", "n_gpus": world,
             "steps": K_steps, "warmup": W, "ms_per_step": round(dev_ms / K_steps, 4),
             "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": (round(value / base, 3) if base else None),
+            "vs_baseline": (round(value / base, 3) if (base and headline) else None),
             "dtype": "bf16", "data": "synthetic (uniform [-1,1] images, random-init weights)",
             "impl": args.impl,
             "config": {"model": f"DCGAN {S}x{S} ngf={cfg.gf_dim} ndf={cfg.df_dim} z={cfg.z_dim}",
                        "global_batch": gb, "batch_per_gpu": B, "seq_len": None, "parallelism": parallelism,
-                       "update_mode": "simultaneous", "cuda_graph": (args.impl == "ours" and use_graph),
+                       "update_mode": "simultaneous", "replica_mode": args.mode, "cuda_graph": (args.impl == "ours" and use_graph),
                        "l2": "flushed between timed steps (256 MiB write outside the event pairs)",
                        "step_ms_min_med_max": [round(min(per_step), 4), round(statistics.median(per_step), 4),
                                                round(max(per_step), 4)]},

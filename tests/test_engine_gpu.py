@@ -129,3 +129,31 @@ def test_training_driver_on_gpu(cuda_lib, tmp_path):
     sd = checkpoint.load_latest(str(tmp_path / "ckpt"))
     assert int(sd["Variable"]) == 12 and sd["d_h3_conv/w"].shape == (5, 5, 256, 512)
     assert any(f.startswith("events.out.tfevents") for f in os.listdir(tmp_path / "ckpt"))
+
+
+def test_wide_128_config_matches_oracle(cuda_lib):
+    """BASELINE.json config 3 geometry: 128x128, ngf=ndf=128 (single GPU; the cross-GPU statistics are
+    covered by scripts/multigpu_check.py)."""
+    from distributed_tensorflow_for_dcgan_b200.config import ModelConfig
+    from distributed_tensorflow_for_dcgan_b200.engine import DCGANEngine
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    torch.manual_seed(0)
+    cfg = ModelConfig(output_size=128, gf_dim=128, df_dim=128, batch_size=8)
+    eng = DCGANEngine(cfg, seed=2)
+    B = cfg.batch_size
+    real = torch.rand(B, 128, 128, 3, device="cuda") * 2 - 1
+    z = torch.rand(B, cfg.z_dim, device="cuda") * 2 - 1
+    p0 = {k: (v.detach().to(torch.bfloat16).float() if (k.endswith("/w") or k == "g_h0_lin/Matrix") else v.detach().clone())
+          for k, v in eng.params.items()}
+    eng.real_f32.copy_(real); eng.z.copy_(z)
+    eng.step_body()
+    torch.cuda.synchronize()
+    K.check_device_error()
+    losses, grads, G = _oracle_step(p0, cfg, real.to(torch.bfloat16).float(), z)
+    for a, b in zip(eng.losses.tolist(), losses):
+        assert abs(a - b) < 3e-2 * max(1.0, abs(b)), (eng.losses.tolist(), losses)
+    assert (eng.d_in[B:].float() - G).abs().max().item() < 5e-2
+    for name in ("d_h1_conv/w", "d_h3_conv/w", "g_h2/w", "g_h4/w", "d_h0_conv/w", "g_bn1/gamma", "g_h0_lin/Matrix"):
+        gv, ref = eng.grad_views[name], grads[name]
+        cos = torch.nn.functional.cosine_similarity(gv.flatten(), ref.flatten(), dim=0).item()
+        assert cos > 0.97, f"{name}: cos {cos}"
