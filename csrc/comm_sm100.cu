@@ -82,6 +82,12 @@ __device__ __forceinline__ bool wait_all(const unsigned* mine, int world, unsign
   return __syncthreads_and((int)ok) != 0;
 }
 
+// Shard size in units of 4 elements, rounded up to an even count so that shard boundaries fall on multiples of
+// 8 elements (= one 16-byte chunk of the bf16 shadow).  Every kernel and the Python side use this split.
+__host__ __device__ inline size_t shard_quads(size_t total4, int world) {
+  return (((total4 + world - 1) / world) + 1) & ~(size_t)1;
+}
+
 // signal layout inside a pad: [slot][phase 0/1][src rank], kMaxRanks entries per row
 __device__ __forceinline__ unsigned* sig_row(unsigned* pad, int slot, int phase) {
   return pad + ((size_t)slot * 2 + phase) * kMaxRanks;
@@ -95,7 +101,11 @@ __global__ void __launch_bounds__(kCommThreads)
 rs_adam_ag_kernel(PeerTable peers, float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
                   const long long* __restrict__ counters, unsigned* __restrict__ state, int rank, int world,
                   size_t lo, size_t hi, float lr, float b1, float b2, float eps, int slot, int* err_flag,
-                  const float* mc_grad, __nv_bfloat16* mc_bf16) {
+                  const float* mc_grad, __nv_bfloat16* mc_bf16, float* mc_master, size_t f32_from, size_t pull_lo,
+                  size_t pull_hi) {
+  // f32_from : elements >= f32_from are read in f32 by their consumers -> their master value is gathered too
+  //            (peers.buf_c = every rank's master array)
+  // [pull_lo, pull_hi) : not pushed at all; the consumer kernel pulls this range from the owners itself
   const unsigned epoch = state[0] + 1;
   // ---- phase A: every rank's gradients are complete -------------------------------------------------------
   if (blockIdx.x == 0 && (int)threadIdx.x < world) {
@@ -109,7 +119,7 @@ rs_adam_ag_kernel(PeerTable peers, float* __restrict__ master, float* __restrict
   const float inv_world = 1.f / (float)world;
   // shard of [lo, hi) owned by this rank (multiples of 4 elements)
   const size_t total4 = (hi - lo) / 4;
-  const size_t per4 = (total4 + world - 1) / world;
+  const size_t per4 = shard_quads(total4, world);
   const size_t s0 = lo + min((size_t)rank * per4, total4) * 4;
   const size_t s1 = lo + min((size_t)(rank + 1) * per4, total4) * 4;
   if (ok) {
@@ -141,12 +151,25 @@ rs_adam_ag_kernel(PeerTable peers, float* __restrict__ master, float* __restrict
       *reinterpret_cast<float4*>(m + i) = mv;
       *reinterpret_cast<float4*>(v + i) = vv;
       const uint2 packed = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
-      if (mc_bf16 != nullptr) {
+      if (i >= pull_lo && i < pull_hi) {
+        // gathered by its first consumer (lin_fwd_gather): only the owner's own shadow is written here
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[rank]) + i) = packed;
+      } else if (mc_bf16 != nullptr) {
         multimem_st_b64(mc_bf16 + i, packed);  // one store, every rank's copy
       } else {
 #pragma unroll 4
         for (int r = 0; r < world; ++r)
           *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[(rank + r) % world]) + i) = packed;
+      }
+      if (i >= f32_from) {
+        if (mc_master != nullptr) {
+          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_master + i), "f"(pv.x),
+                       "f"(pv.y), "f"(pv.z), "f"(pv.w)
+                       : "memory");
+        } else {
+          for (int r = 1; r < world; ++r)
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(peers.buf_c[(rank + r) % world]) + i) = pv;
+        }
       }
     }
   }
@@ -212,10 +235,10 @@ allreduce_small_kernel(PeerTable peers /* buf_a = staging */, float* __restrict_
 // ---------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kCommThreads)
 async_apply_kernel(PeerTable peers, const float* __restrict__ grad, __nv_bfloat16* __restrict__ local_bf16,
-                   long long* const* __restrict__ peer_counters, int rank, int world, size_t n, float lr, float b1,
-                   float b2, float eps) {
+                   float* __restrict__ local_master, long long* const* __restrict__ peer_counters, int rank,
+                   int world, size_t n, float lr, float b1, float b2, float eps) {
   const size_t total4 = n / 4;
-  const size_t per4 = (total4 + world - 1) / world;
+  const size_t per4 = shard_quads(total4, world);
   __shared__ float s_lr_t[kMaxRanks];
   if ((int)threadIdx.x < world) {
     // every pusher advances the owner's step count (beta powers advance per apply, like TF's shared
@@ -254,8 +277,62 @@ async_apply_kernel(PeerTable peers, const float* __restrict__ grad, __nv_bfloat1
     *reinterpret_cast<float4*>(V) = vv;
     const uint2 packed = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
     *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[owner]) + i) = packed;
-    if (owner != rank) *reinterpret_cast<uint2*>(local_bf16 + i) = packed;  // what we just read is our fresh pull
+    if (owner != rank) {  // what we just read and updated is our fresh pull (bf16 shadow + f32 for the f32 readers)
+      *reinterpret_cast<uint2*>(local_bf16 + i) = packed;
+      *reinterpret_cast<float4*>(local_master + i) = pv;
+    }
   }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// g_h0_lin with its parameter all-gather fused in: out[n, j] = sum_k z[n,k] * W[k,j] + b[j], where every
+// element of W is loaded from the bf16 shadow of the rank that owns (and just updated) it -- P2P loads over
+// NVLink from inside the consumer -- and mirrored into the local shadow on the way.  W occupies
+// [w_off, w_off + K*F) of the flat arena; ownership follows the optimizer kernel's shard split of [lo, hi).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kGatherLinTile = 16;
+__global__ void __launch_bounds__(128)
+lin_fwd_gather_kernel(PeerTable peers /* buf_b = bf16 shadows */, const float* __restrict__ z,
+                      const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, int NB, int K, int F,
+                      size_t w_off, size_t lo, size_t hi, int rank, int world) {
+  extern __shared__ uint8_t gsm[];
+  float* zs = reinterpret_cast<float*>(gsm);                                       // [kGatherLinTile][K]
+  uint4* wsm = reinterpret_cast<uint4*>(gsm + (size_t)kGatherLinTile * K * 4);     // [K][16] x 16 B = W[:, j0:j0+128]
+  const int n0 = blockIdx.y * kGatherLinTile;
+  const int j0 = blockIdx.x * 128;
+  // ---- gather: this block's 128 columns of W, 16-byte peer loads from whichever rank owns each chunk --------
+  const size_t total4 = (hi - lo) / 4;
+  const size_t per4 = shard_quads(total4, world);
+  uint4* local = reinterpret_cast<uint4*>(peers.buf_b[rank]);
+  for (int c = threadIdx.x; c < K * 16; c += 128) {
+    const int k = c >> 4, ch = c & 15;
+    const size_t idx = w_off + (size_t)k * F + j0 + ch * 8;   // first of 8 bf16; a chunk never straddles shards
+    const int owner = (int)min((idx - lo) / 4 / per4, (size_t)(world - 1));
+    const uint4 v = __ldcg(reinterpret_cast<const uint4*>(peers.buf_b[owner]) + idx / 8);
+    wsm[c] = v;
+    if (blockIdx.y == 0 && owner != rank) local[idx / 8] = v;  // mirror into the local shadow
+  }
+  for (int i = threadIdx.x; i < kGatherLinTile * K; i += 128) {
+    const int n = n0 + i / K;
+    zs[i] = n < NB ? z[(size_t)n * K + (i % K)] : 0.f;
+  }
+  __syncthreads();
+  // ---- GEMM slice from shared memory ------------------------------------------------------------------------
+  const int j = j0 + threadIdx.x;
+  if (j >= F) return;
+  float acc[kGatherLinTile];
+  const float b = bias ? bias[j] : 0.f;
+#pragma unroll
+  for (int i = 0; i < kGatherLinTile; ++i) acc[i] = b;
+  const unsigned short* wcol = reinterpret_cast<const unsigned short*>(wsm) + threadIdx.x;
+  for (int k = 0; k < K; ++k) {
+    const float w = __uint_as_float((unsigned)wcol[k * 128] << 16);
+#pragma unroll
+    for (int i = 0; i < kGatherLinTile; ++i) acc[i] += zs[i * K + k] * w;
+  }
+#pragma unroll
+  for (int i = 0; i < kGatherLinTile; ++i)
+    if (n0 + i < NB) out[(size_t)(n0 + i) * F + j] = __float2bfloat16(acc[i]);
 }
 
 static void fill(void** dst, const void* const* src, int world) {
@@ -269,20 +346,40 @@ using namespace dcgan;
 extern "C" {
 
 int dcgan_comm_rs_adam_ag(const void* const* grad_ptrs, const void* const* bf16_ptrs, const void* const* sig_ptrs,
-                          float* master, float* m, float* v, const long long* counters, unsigned* state, int rank,
-                          int world, size_t lo, size_t hi, float lr, float b1, float b2, float eps, int slot,
-                          const float* mc_grad, void* mc_bf16, int blocks, cudaStream_t st) {
-  if (world < 1 || world > kMaxRanks || (lo % 4) || (hi % 4) || hi < lo) return DCGAN_ERR_SHAPE;
+                          const void* const* master_ptrs, float* master, float* m, float* v,
+                          const long long* counters, unsigned* state, int rank, int world, size_t lo, size_t hi,
+                          float lr, float b1, float b2, float eps, int slot, const float* mc_grad, void* mc_bf16,
+                          float* mc_master, size_t f32_from, size_t pull_lo, size_t pull_hi, int blocks,
+                          cudaStream_t st) {
+  if (world < 1 || world > kMaxRanks || (lo % 4) || (hi % 4) || hi < lo || (f32_from % 4) || (pull_lo % 4) ||
+      (pull_hi % 4))
+    return DCGAN_ERR_SHAPE;
   PeerTable t{};
   fill(t.buf_a, grad_ptrs, world);
   fill(t.buf_b, bf16_ptrs, world);
+  if (master_ptrs != nullptr) fill(t.buf_c, master_ptrs, world);
+  else if (f32_from < hi) return DCGAN_ERR_SHAPE;
   fill(reinterpret_cast<void**>(t.sig), sig_ptrs, world);
   int* err = error_flag_ptr();
   if (!err) return DCGAN_ERR_DRIVER;
   if (blocks <= 0) blocks = 32;
   rs_adam_ag_kernel<<<blocks, kCommThreads, 0, st>>>(t, master, m, v, counters, state, rank, world, lo, hi, lr, b1,
                                                      b2, eps, slot, err, mc_grad,
-                                                     reinterpret_cast<__nv_bfloat16*>(mc_bf16));
+                                                     reinterpret_cast<__nv_bfloat16*>(mc_bf16), mc_master, f32_from,
+                                                     pull_lo, pull_hi);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_comm_lin_fwd_gather(const void* const* bf16_ptrs, const float* z, const float* bias, void* out, int NB,
+                              int K, int F, size_t w_off, size_t lo, size_t hi, int rank, int world,
+                              cudaStream_t st) {
+  if (world < 1 || world > kMaxRanks) return DCGAN_ERR_SHAPE;
+  PeerTable t{};
+  fill(t.buf_b, bf16_ptrs, world);
+  dim3 grid((F + 127) / 128, (NB + kGatherLinTile - 1) / kGatherLinTile);
+  if (F % 128 || (w_off % 8)) return DCGAN_ERR_SHAPE;
+  lin_fwd_gather_kernel<<<grid, 128, kGatherLinTile * K * sizeof(float) + (size_t)K * 256, st>>>(
+      t, z, bias, reinterpret_cast<__nv_bfloat16*>(out), NB, K, F, w_off, lo, hi, rank, world);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 
@@ -300,7 +397,7 @@ int dcgan_comm_allreduce_small(const void* const* staging_ptrs, const void* cons
 }
 
 int dcgan_comm_async_apply(const void* const* master_ptrs, const void* const* bf16_ptrs, const void* const* m_ptrs,
-                           const void* const* v_ptrs, const float* grad, void* local_bf16,
+                           const void* const* v_ptrs, const float* grad, void* local_bf16, float* local_master,
                            long long* const* peer_counters_dev, int rank, int world, size_t n, float lr, float b1,
                            float b2, float eps, int blocks, cudaStream_t st) {
   if (world < 1 || world > kMaxRanks || (n % 4)) return DCGAN_ERR_SHAPE;
@@ -311,7 +408,8 @@ int dcgan_comm_async_apply(const void* const* master_ptrs, const void* const* bf
   fill(t.buf_d, v_ptrs, world);
   if (blocks <= 0) blocks = 148;
   async_apply_kernel<<<blocks, kCommThreads, 0, st>>>(t, grad, reinterpret_cast<__nv_bfloat16*>(local_bf16),
-                                                      peer_counters_dev, rank, world, n, lr, b1, b2, eps);
+                                                      local_master, peer_counters_dev, rank, world, n, lr, b1, b2,
+                                                      eps);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 

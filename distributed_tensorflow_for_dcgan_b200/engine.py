@@ -34,19 +34,39 @@ class ParamArena:
     def __init__(self, cfg: ModelConfig, device, pad_to: int = 1024, alloc=None):
         self.specs = manifest.trainable_specs(cfg)
         self.offsets: Dict[str, Tuple[int, Tuple[int, ...]]] = {}
+        # Arena order (independent of the checkpoint order): [G | D]; inside each, the big filters that the
+        # tensor-core kernels read through the bf16 shadow come first, then everything the kernels read in
+        # f32 (biases, batch-norm parameters, the 3-channel filters, d_h3_lin).  The multi-GPU optimizer
+        # kernel all-gathers bf16 for the whole range and additionally f32 for the second part only.
+        def group(pred):
+            return [s for s in self.specs if pred(s.name)]
+        g_all = group(manifest.is_g_var)
+        d_all = group(manifest.is_d_var)
         off = 0
-        for s in self.specs:
-            self.offsets[s.name] = (off, s.shape)
-            off += (s.numel + 7) // 8 * 8  # keep every tensor 32-byte aligned (vector loads, TMA)
+        self.f32_start = {}
+        for key, specs in (("g", g_all), ("d", d_all)):
+            if key == "d":
+                self.g_end = off
+            for part in (True, False):
+                if not part:
+                    self.f32_start[key] = off
+                for s in specs:
+                    if self.reads_bf16(s.name) == part:
+                        self.offsets[s.name] = (off, s.shape)
+                        off += (s.numel + 7) // 8 * 8  # every tensor 32-byte aligned (vector loads, TMA)
         self.numel = off
         self.padded = (off + pad_to - 1) // pad_to * pad_to
-        self.g_end = self.offsets["d_h0_conv/w"][0]  # generator variables come first
         if alloc is None:
             alloc = lambda name, numel, dtype: torch.zeros(numel, dtype=dtype, device=device)
         self.master = alloc("master", self.padded, torch.float32)
         self.m = alloc("adam_m", self.padded, torch.float32)
         self.v = alloc("adam_v", self.padded, torch.float32)
         self.bf16 = alloc("bf16", self.padded, torch.bfloat16)
+
+    @staticmethod
+    def reads_bf16(name: str) -> bool:
+        """Variables consumed only through the bf16 shadow (the implicit-GEMM filters and g_h0_lin/Matrix)."""
+        return name == "g_h0_lin/Matrix" or (name.endswith("/w") and name not in ("g_h4/w", "d_h0_conv/w"))
 
     def view(self, flat: torch.Tensor, name: str) -> torch.Tensor:
         off, shape = self.offsets[name]
@@ -206,7 +226,12 @@ class DCGANEngine:
         p, B = self.params, self.B
         pre = self.g_pre if train else self.s_pre
         act = self.g_act if train else self.s_act
-        K.lin_fwd(self.z, self.w_native["g_h0_lin/Matrix"], p["g_h0_lin/bias"], pre[0].view(B, -1))
+        if train and self.comm is not None and hasattr(self.comm, "lin_fwd_gather"):
+            # the parameter all-gather of the first generator layer happens inside its consumer: the kernel
+            # pulls each slice of g_h0_lin/Matrix from the rank that owns (and just updated) it
+            self.comm.lin_fwd_gather(self, pre[0].view(B, -1))
+        else:
+            K.lin_fwd(self.z, self.w_native["g_h0_lin/Matrix"], p["g_h0_lin/bias"], pre[0].view(B, -1))
         self._bn_fwd("g_bn0", pre[0], act[0], train)
         for i in (1, 2, 3):
             w = self.w_native[f"g_h{i}/w"].view(25, self.g_ch[i], self.g_ch[i - 1])

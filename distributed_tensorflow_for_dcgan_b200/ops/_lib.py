@@ -47,9 +47,10 @@ _SIGNATURES = {
     "dcgan_f32_to_bf16": "ppzffs",
     "dcgan_grid_merge": "ppiiiiis",
     "dcgan_count_zeros": "ppzs",
-    "dcgan_comm_rs_adam_ag": "ppppppppiizzffffippis",
+    "dcgan_comm_rs_adam_ag": "pppppppppiizzffffipppzzzis",
+    "dcgan_comm_lin_fwd_gather": "ppppiiizzziis",
     "dcgan_comm_allreduce_small": "pppiipiiis",
-    "dcgan_comm_async_apply": "pppppppiizffffis",
+    "dcgan_comm_async_apply": "ppppppppiizffffis",
     "dcgan_bn_forward_static": "pppppppiiiffis",
 }
 _KIND = {"p": c_void_p, "i": c_int, "f": c_float, "z": c_size_t, "s": c_void_p}

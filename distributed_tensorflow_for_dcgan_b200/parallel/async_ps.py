@@ -63,7 +63,7 @@ class AsyncPSComm:
     def optimizer_step(self, engine, which: str = "both") -> None:
         A = engine.arena
         _lib.call("dcgan_comm_async_apply", self._p, self._b, self._m, self._v, engine.grads.data_ptr(),
-                  A.bf16.data_ptr(), self._counter_ptrs.data_ptr(), self.rank, self.world, A.padded, engine.lr,
+                  A.bf16.data_ptr(), A.master.data_ptr(), self._counter_ptrs.data_ptr(), self.rank, self.world, A.padded, engine.lr,
                   engine.beta1, engine.beta2, engine.eps, self.blocks)
 
     def global_step(self) -> int:
@@ -78,7 +78,7 @@ class AsyncPSComm:
         workers may keep pushing, so the snapshot is as loosely consistent as the mode itself)."""
         A = engine.arena
         total4 = A.padded // 4
-        per4 = (total4 + self.world - 1) // self.world
+        per4 = (((total4 + self.world - 1) // self.world) + 1) & ~1  # even: shard_quads() in comm_sm100.cu
         torch.cuda.synchronize(self.device)
         for name, local in (("master", A.master), ("adam_m", A.m), ("adam_v", A.v)):
             hdl = self.handles[name]

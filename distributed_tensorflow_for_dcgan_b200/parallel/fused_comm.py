@@ -18,6 +18,7 @@
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict
 
 import torch
@@ -38,7 +39,7 @@ def _ptr_array(ptrs):
 
 class FusedComm:
     def __init__(self, device, sync_bn: bool = False, overlap: bool = True, use_multicast: bool = True,
-                 blocks: int = 32):
+                 blocks: int = 32, gather_in_consumer: bool = True):
         import torch.distributed._symmetric_memory as symm_mem
         self.symm_mem = symm_mem
         self.device, self.sync_bn, self.overlap = device, sync_bn, overlap
@@ -50,6 +51,8 @@ class FusedComm:
         self.tensors: Dict[str, torch.Tensor] = {}
         self.use_multicast = use_multicast
         self.blocks = blocks
+        self.gather_in_consumer = gather_in_consumer and os.environ.get("DCGAN_GATHER_IN_CONSUMER", "1") != "0"
+        self.overlap = overlap and os.environ.get("DCGAN_COMM_OVERLAP", "1") != "0"
         self.stream = torch.cuda.Stream(device)
         self._fork_event = torch.cuda.Event()
         self._join_event = torch.cuda.Event()
@@ -84,23 +87,47 @@ class FusedComm:
         engine.refresh_compute_weights()
         self._grad_ptrs = _ptr_array(self.handles["zero_region"].buffer_ptrs)
         self._bf16_ptrs = _ptr_array(self.handles["bf16"].buffer_ptrs)
-        hg, hb = self.handles["zero_region"], self.handles["bf16"]
-        mc_ok = self.use_multicast and getattr(hg, "has_multicast_support", False) and hg.multicast_ptr and hb.multicast_ptr
+        self._master_ptrs = _ptr_array(self.handles["master"].buffer_ptrs)
+        hg, hb, hm = self.handles["zero_region"], self.handles["bf16"], self.handles["master"]
+        mc_ok = (self.use_multicast and getattr(hg, "has_multicast_support", False) and hg.multicast_ptr
+                 and hb.multicast_ptr and hm.multicast_ptr)
         self.mc_grad = int(hg.multicast_ptr) if mc_ok else None
         self.mc_bf16 = int(hb.multicast_ptr) if mc_ok else None
+        self.mc_master = int(hm.multicast_ptr) if mc_ok else None
         self.buckets = {"g": (0, A.g_end), "d": (A.g_end, A.padded), "both": None}
+        # f32-consumed variables start here inside each bucket (their master value is gathered too)
+        self.f32_from = {"g": A.f32_start["g"], "d": A.f32_start["d"]}
+        # g_h0_lin/Matrix is gathered by its consumer (lin_fwd_gather), not pushed by the optimizer kernel
+        off, shape = A.offsets["g_h0_lin/Matrix"]
+        self.pull_range = (off, off + shape[0] * shape[1]) if self.gather_in_consumer else (0, 0)
         torch.cuda.synchronize(self.device)
         dist.barrier()
 
     # ---- the fused optimizer step ---------------------------------------------------------------------------------
-    def _launch(self, engine, which: str) -> None:
+    def _launch(self, engine, which: str, blocks: int = 0) -> None:
         A = engine.arena
         lo, hi = self.buckets[which]
         slot = SLOT_G if which == "g" else SLOT_D
-        _lib.call("dcgan_comm_rs_adam_ag", self._grad_ptrs, self._bf16_ptrs, self._sig_ptrs, A.master.data_ptr(),
-                  A.m.data_ptr(), A.v.data_ptr(), engine.counters.data_ptr(), self.state[slot].data_ptr(), self.rank,
-                  self.world, lo, hi, engine.lr, engine.beta1, engine.beta2, engine.eps, slot, self.mc_grad,
-                  self.mc_bf16, self.blocks)
+        pull_lo, pull_hi = self.pull_range if which == "g" else (0, 0)
+        _lib.call("dcgan_comm_rs_adam_ag", self._grad_ptrs, self._bf16_ptrs, self._sig_ptrs, self._master_ptrs,
+                  A.master.data_ptr(), A.m.data_ptr(), A.v.data_ptr(), engine.counters.data_ptr(),
+                  self.state[slot].data_ptr(), self.rank, self.world, lo, hi, engine.lr, engine.beta1, engine.beta2,
+                  engine.eps, slot, self.mc_grad, self.mc_bf16, self.mc_master, self.f32_from[which], pull_lo,
+                  pull_hi, blocks or self.blocks)
+
+    def lin_fwd_gather(self, engine, out2d: torch.Tensor) -> None:
+        """g_h0_lin forward that pulls its weight slices from the owning ranks (parameter all-gather fused into
+        the first consumer).  Falls back to the local shadow when the feature is off."""
+        from ..ops import kernels as K
+        A = engine.arena
+        if not self.gather_in_consumer:
+            K.lin_fwd(engine.z, engine.w_native["g_h0_lin/Matrix"], engine.params["g_h0_lin/bias"], out2d)
+            return
+        off, shape = A.offsets["g_h0_lin/Matrix"]
+        lo, hi = self.buckets["g"]
+        _lib.call("dcgan_comm_lin_fwd_gather", self._bf16_ptrs, engine.z.data_ptr(),
+                  engine.params["g_h0_lin/bias"].data_ptr(), out2d.data_ptr(), engine.B, shape[0], shape[1], off, lo,
+                  hi, self.rank, self.world)
 
     def launch_bucket(self, engine, which: str, side_stream: bool) -> None:
         if side_stream:
@@ -112,7 +139,8 @@ class FusedComm:
                 self._join_event.record(self.stream)
             self._forked = True
         else:
-            self._launch(engine, which)
+            # nothing left to overlap with: give the exchange the whole GPU
+            self._launch(engine, which, blocks=148)
 
     def join(self) -> None:
         if self._forked:
@@ -134,7 +162,7 @@ class FusedComm:
     def shard_range(self, bucket: str, rank: int):
         lo, hi = self.buckets[bucket]
         total4 = (hi - lo) // 4
-        per4 = (total4 + self.world - 1) // self.world
+        per4 = (((total4 + self.world - 1) // self.world) + 1) & ~1  # even: shard_quads() in comm_sm100.cu
         return lo + min(rank * per4, total4) * 4, lo + min((rank + 1) * per4, total4) * 4
 
     def gather_state(self, engine) -> None:

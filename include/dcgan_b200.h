@@ -158,11 +158,20 @@ int dcgan_count_zeros(const void* x, unsigned long long* count, size_t n, cudaSt
 
 /* Sync replicas: reduce-scatter of f32 gradients + average + TF-form Adam on this rank's shard of
  * [lo,hi) + all-gather of the updated bf16 parameters, in one kernel.  mc_* = NVLS multicast addresses
- * of the gradient / bf16 buffers or NULL for plain P2P loads and stores. */
+ * (gradients / bf16 shadow / f32 master) or NULL for plain P2P loads and stores.  Elements >= f32_from are
+ * read in f32 by their consumers, so their master value is gathered as well (master_ptrs); elements in
+ * [pull_lo,pull_hi) are not pushed because their first consumer pulls them (dcgan_comm_lin_fwd_gather). */
 int dcgan_comm_rs_adam_ag(const void* const* grad_ptrs, const void* const* bf16_ptrs, const void* const* sig_ptrs,
-                          float* master, float* m, float* v, const long long* counters, unsigned* state, int rank,
-                          int world, size_t lo, size_t hi, float lr, float b1, float b2, float eps, int slot,
-                          const float* mc_grad, void* mc_bf16, int blocks, cudaStream_t stream);
+                          const void* const* master_ptrs, float* master, float* m, float* v,
+                          const long long* counters, unsigned* state, int rank, int world, size_t lo, size_t hi,
+                          float lr, float b1, float b2, float eps, int slot, const float* mc_grad, void* mc_bf16,
+                          float* mc_master, size_t f32_from, size_t pull_lo, size_t pull_hi, int blocks,
+                          cudaStream_t stream);
+/* g_h0_lin (distriubted_model.py:88) with the parameter all-gather fused into the consumer: every slice of
+ * Matrix is loaded over NVLink from the bf16 shadow of the rank that owns it. */
+int dcgan_comm_lin_fwd_gather(const void* const* bf16_ptrs, const float* z, const float* bias, void* out, int NB,
+                              int K, int F, size_t w_off, size_t lo, size_t hi, int rank, int world,
+                              cudaStream_t stream);
 /* Mean all-reduce of a small f32 vector (cross-GPU batch-norm statistics). */
 int dcgan_comm_allreduce_small(const void* const* staging_ptrs, const void* const* sig_ptrs, float* data, int n,
                                int staging_stride, unsigned* state, int rank, int world, int slot,
@@ -170,7 +179,7 @@ int dcgan_comm_allreduce_small(const void* const* staging_ptrs, const void* cons
 /* Async parameter-server mode: apply this worker's gradients to the owners' shards through peer memory
  * (unlocked, stale -- reference image_train.py:109-112 with use_locking=False) and refresh the local copy. */
 int dcgan_comm_async_apply(const void* const* master_ptrs, const void* const* bf16_ptrs, const void* const* m_ptrs,
-                           const void* const* v_ptrs, const float* grad, void* local_bf16,
+                           const void* const* v_ptrs, const float* grad, void* local_bf16, float* local_master,
                            long long* const* peer_counters_dev, int rank, int world, size_t n, float lr, float b1,
                            float b2, float eps, int blocks, cudaStream_t stream);
 

@@ -76,6 +76,15 @@ for mc in (False, True):
         a, b = fus_state[k].float(), ref_state[k].float()
         err = (a - b).abs().max().item() / max(b.abs().max().item(), 1e-12)
         worst = max(worst, err)
+    # parameters that kernels read in f32 must be current on EVERY rank (not only on their owner); and the
+    # consumer-side gather of g_h0_lin/Matrix must have delivered the owners' values into the local shadow
+    f32_ok = True
+    for key, end in (("g", A.g_end), ("d", A.padded)):
+        a0 = A.f32_start[key]
+        f32_ok &= bool(torch.allclose(fus.arena.master[a0:end], ref.arena.master[a0:end], rtol=1e-5, atol=1e-8))
+    fus.z.uniform_(-1, 1)
+    fus.generator_forward(train=True)
+    torch.cuda.synchronize(); dist.barrier()
     bf_diff = (fus.arena.bf16[:A.numel].float() - ref.arena.bf16[:A.numel].float()).abs().max().item()
     # every rank must hold identical bf16 parameters
     mine = fus.arena.bf16.float().sum().item()
@@ -85,6 +94,7 @@ for mc in (False, True):
         f"bf16_maxdiff={bf_diff:.3e} ranks_identical={len(set(allv)) == 1}")
     results[f"fused_mc{int(mc)}"] = dict(multicast_used=has_mc, worst_rel_err=worst, bf16_maxdiff=bf_diff,
                                          ranks_identical=len(set(allv)) == 1)
+    assert f32_ok, "f32-consumed parameters are stale on a non-owner rank"
     assert worst < 1e-5 and bf_diff < 1e-2 and len(set(allv)) == 1, "fused comm mismatch"
     # and a few real training steps stay finite and in lock-step
     l_fus = run_steps(fus, 3, B)
@@ -163,9 +173,9 @@ if "--sweep" in sys.argv:
                 continue
             for blocks in (16, 32, 64, 148):
                 def once():
-                    _lib.call("dcgan_comm_rs_adam_ag", gp, bp, fc._sig_ptrs, p.data_ptr(), m.data_ptr(), v.data_ptr(),
-                              counters.data_ptr(), fc.state[3].data_ptr(), rank, world, 0, n, 2e-4, 0.5, 0.999, 1e-8, 3,
-                              mcg, mcb, blocks)
+                    _lib.call("dcgan_comm_rs_adam_ag", gp, bp, fc._sig_ptrs, None, p.data_ptr(), m.data_ptr(),
+                              v.data_ptr(), counters.data_ptr(), fc.state[3].data_ptr(), rank, world, 0, n, 2e-4, 0.5,
+                              0.999, 1e-8, 3, mcg, mcb, None, n, 0, 0, blocks)
                 for _ in range(3): once()
                 torch.cuda.synchronize(); dist.barrier()
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
