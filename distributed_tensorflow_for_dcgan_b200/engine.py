@@ -326,15 +326,25 @@ class DCGANEngine:
     # ------------------------------------------------------------------------------------------------
     # the step
     # ------------------------------------------------------------------------------------------------
+    def _range(self, name: str):
+        """NVTX range around a phase of the step when profiling is on (``engine.nvtx = True``, --profile)."""
+        if getattr(self, "nvtx", False):
+            return torch.cuda.nvtx.range(name)
+        import contextlib
+        return contextlib.nullcontext()
+
     def step_body(self) -> None:
         """Everything of one training iteration that runs on the device, in stream order."""
         B = self.B
         self.zero_region.zero_()
         K.f32_to_bf16(self.real_f32, self.d_in[:B])
-        self.generator_forward(train=True)
-        self.discriminator_forward()
-        K.gan_loss(self.logits, self.losses, self.dlogit, self.probs, self.counters, B, 1.0, True)
-        self.discriminator_backward()
+        with self._range("G_forward"):
+            self.generator_forward(train=True)
+        with self._range("D_forward"):
+            self.discriminator_forward()
+            K.gan_loss(self.logits, self.losses, self.dlogit, self.probs, self.counters, B, 1.0, True)
+        with self._range("D_backward"):
+            self.discriminator_backward()
         if self.update_mode == "simultaneous":
             if self.comm is not None and getattr(self.comm, "overlap", False):
                 # D's gradient exchange + Adam runs on the communication stream under G's backward pass

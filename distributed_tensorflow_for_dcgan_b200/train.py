@@ -93,6 +93,7 @@ def run_worker(FLAGS, role, cfg) -> int:
         from .trainer import EngineTrainer
         trainer = EngineTrainer(cfg, FLAGS.learning_rate, FLAGS.beta1, FLAGS.seed, FLAGS.update_mode, device, comm,
                                 FLAGS.cuda_graph)
+        trainer.engine.nvtx = bool(FLAGS.profile)   # NVTX ranges per phase for nsys / ncu range filters
     else:
         from .trainer import CPUTrainer
         allreduce_world = 1
