@@ -312,3 +312,47 @@ def test_helpers(cuda_lib):
     assert torch.allclose(grid, ref)
     zf = K.zero_fraction(torch.relu(_rand((4096,))))
     assert 0.3 < zf.item() < 0.7
+
+
+def test_no_out_of_bounds_writes(cuda_lib):
+    """compute-sanitizer is closed on the GPU pool, so out-of-bounds stores are caught with guard bands: every
+    output lives inside a larger buffer pre-filled with a sentinel that must survive the kernel."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+
+    def guarded(shape, dtype):
+        n = 1
+        for s in shape:
+            n *= s
+        pad = 4096
+        buf = torch.full((n + 2 * pad,), 7.0 if dtype != torch.bfloat16 else 7.0, dtype=dtype, device="cuda")
+        return buf, buf[pad:pad + n].view(shape), pad
+
+    def intact(buf, pad):
+        return bool((buf[:pad] == 7).all() and (buf[-pad:] == 7).all())
+
+    x = _rand((3, 8, 8, 64))                       # 3*4*4 = 48 output rows: a partial 128-row tile
+    w = _rand((25, 64, 64), 0.05)
+    buf, out, pad = guarded((3, 4, 4, 64), torch.bfloat16)
+    K.conv_fprop_kn(x, w, None, out=out)
+    assert intact(buf, pad)
+    buf, out, pad = guarded((3, 16, 16, 64), torch.bfloat16)
+    K.conv_tconv(x, w, None, out=out)
+    assert intact(buf, pad)
+    buf, dw, pad = guarded((25, 64, 128), torch.float32)
+    dw.zero_()
+    K.conv_wgrad(_rand((4, 16, 16, 64)), _rand((4, 8, 8, 128)), dw)
+    assert intact(buf, pad)
+    x3 = _rand((2, 64, 64, 3))
+    w3 = torch.randn(5, 5, 3, 64, device="cuda") * 0.05
+    buf, out, pad = guarded((2, 32, 32, 64), torch.bfloat16)
+    K.c3_fprop(x3, w3, None, out=out)
+    assert intact(buf, pad)
+    buf, out, pad = guarded((2, 64, 64, 3), torch.bfloat16)
+    K.c3_tconv(_rand((2, 32, 32, 64)), w3, None, act="tanh", out=out)
+    assert intact(buf, pad)
+    buf, dw3, pad = guarded((5, 5, 3, 64), torch.float32)
+    dw3.zero_()
+    K.c3_wgrad(x3, _rand((2, 32, 32, 64)), dw3)
+    assert intact(buf, pad)
+    torch.cuda.synchronize()
+    K.check_device_error()
