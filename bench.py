@@ -63,8 +63,9 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
                  str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.mark_lo, self.mark_hi = 0, None
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except Exception:
@@ -73,6 +74,14 @@ class ClockSampler:
     def _read(self):
         for line in self.proc.stdout:
             self.lines.append(line.strip())
+
+    def mark_begin(self):
+        """Start of the timed region: samples before this line count as idle."""
+        self.mark_lo = max(len(self.lines) - 1, 0)
+
+    def mark_end(self):
+        time.sleep(0.12)  # let the sample that covers the end of the region arrive
+        self.mark_hi = len(self.lines)
 
     def stop(self):
         if self.proc is None:
@@ -84,7 +93,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        lines = self.lines[self.mark_lo:self.mark_hi] if self.mark_hi else self.lines
+        for ln in lines:
             parts = [p.strip() for p in ln.split(",")]
             if len(parts) < 7:
                 continue
@@ -222,6 +232,11 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    # clocks / throttle reasons are sampled from before the warm-up; only the samples taken during the two
+    # timed regions are reported
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     # ---- warm-up ------------------------------------------------------------------------------------
     for i in range(W):
         stage_inputs(i)
@@ -229,9 +244,8 @@ def main():
     barrier()
 
     # ---- device-timed region: K steps, one event pair per step, L2 flushed in between -----------------
-    sampler = ClockSampler(local)
     if rank == 0:
-        sampler.start()
+        sampler.mark_begin()
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(K_steps)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(K_steps)]
     barrier()
@@ -256,6 +270,8 @@ def main():
     t1.record()
     barrier()
     e2e_ms = t0.elapsed_time(t1)
+    if rank == 0:
+        sampler.mark_end()
     clocks = sampler.stop() if rank == 0 else None
 
     t = torch.tensor([dev_ms, e2e_ms], device=dev, dtype=torch.float64)

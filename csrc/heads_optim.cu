@@ -30,10 +30,19 @@ lin_fwd_kernel(const float* __restrict__ z, const __nv_bfloat16* __restrict__ W,
   const float b = bias ? bias[j] : 0.f;
 #pragma unroll
   for (int i = 0; i < kLinTile; ++i) acc[i] = b;
-  for (int k = 0; k < K; ++k) {
-    const float w = __bfloat162float(W[(size_t)k * F + j]);
+  constexpr int kBatch = 10;  // weight loads in flight per thread
+  for (int k0 = 0; k0 < K; k0 += kBatch) {
+    __nv_bfloat16 wv[kBatch];
 #pragma unroll
-    for (int i = 0; i < kLinTile; ++i) acc[i] += zs[i * K + k] * w;
+    for (int u = 0; u < kBatch; ++u) wv[u] = (k0 + u < K) ? W[(size_t)(k0 + u) * F + j] : __float2bfloat16(0.f);
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      if (k0 + u < K) {
+        const float w = __bfloat162float(wv[u]);
+#pragma unroll
+        for (int i = 0; i < kLinTile; ++i) acc[i] += zs[i * K + k0 + u] * w;
+      }
+    }
   }
 #pragma unroll
   for (int i = 0; i < kLinTile; ++i)
@@ -58,11 +67,20 @@ lin_wgrad_kernel(const float* __restrict__ z, const __nv_bfloat16* __restrict__ 
 #pragma unroll
   for (int i = 0; i < kt; ++i) acc[i] = 0.f;
   float bsum = 0.f;
-  for (int n = 0; n < NB; ++n) {
-    const float d = __bfloat162float(dy[(size_t)n * F + j]);
-    bsum += d;
+  constexpr int kBatch = 8;  // gradient loads in flight per thread
+  for (int nb = 0; nb < NB; nb += kBatch) {
+    __nv_bfloat16 dv[kBatch];
 #pragma unroll
-    for (int i = 0; i < kt; ++i) acc[i] += zs[n * kt + i] * d;
+    for (int u = 0; u < kBatch; ++u) dv[u] = (nb + u < NB) ? dy[(size_t)(nb + u) * F + j] : __float2bfloat16(0.f);
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      if (nb + u < NB) {
+        const float d = __bfloat162float(dv[u]);
+        bsum += d;
+#pragma unroll
+        for (int i = 0; i < kt; ++i) acc[i] += zs[(nb + u) * kt + i] * d;
+      }
+    }
   }
 #pragma unroll
   for (int i = 0; i < kt; ++i)

@@ -91,10 +91,12 @@ __device__ __forceinline__ void cp_async_wait() {
 // (kGatherDepth is min(3, STAGES - 1), a kernel-local constant)
 
 template <int MODE, int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads, (SmemLayout<BLOCK_N, STAGES>::kTotal <= 110 * 1024) ? 2 : 1)
+__global__ void __launch_bounds__(kNumThreads, (SmemLayout<BLOCK_N, STAGES>::kTotal <= 74 * 1024)    ? 3
+                                              : (SmemLayout<BLOCK_N, STAGES>::kTotal <= 110 * 1024) ? 2
+                                                                                                    : 1)
 igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
   using L = SmemLayout<BLOCK_N, STAGES>;
-  constexpr int kGatherDepth = (STAGES - 1 < 3) ? STAGES - 1 : 3;
+  constexpr int kGatherDepth = (STAGES >= 8) ? 6 : ((STAGES - 1 < 3) ? STAGES - 1 : 3);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
@@ -495,7 +497,10 @@ template <int MODE>
 static int dispatch_n(int block_n, const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cudaStream_t st) {
   const bool occ2 = (g_igemm_tuning & 1) != 0;
   switch (block_n) {
-    case 64: return occ2 ? launch<MODE, 64, 4>(tmap, p, grid, st) : launch<MODE, 64, 6>(tmap, p, grid, st);
+    case 64:
+      if (g_igemm_tuning & 4) return launch<MODE, 64, 8>(tmap, p, grid, st);  // deep ring, 1 CTA/SM
+      if (g_igemm_tuning & 2) return launch<MODE, 64, 3>(tmap, p, grid, st);  // 3 CTAs/SM
+      return occ2 ? launch<MODE, 64, 4>(tmap, p, grid, st) : launch<MODE, 64, 6>(tmap, p, grid, st);
     case 128: return occ2 ? launch<MODE, 128, 3>(tmap, p, grid, st) : launch<MODE, 128, 5>(tmap, p, grid, st);
     case 256: return launch<MODE, 256, 4>(tmap, p, grid, st);
     default: return DCGAN_ERR_SHAPE;

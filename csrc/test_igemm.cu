@@ -214,7 +214,7 @@ int main(int argc, char** argv) {
   fails += test_wgrad(4, 8, 8, 128, 256, 0, 0, 0);
   printf("correctness: %d failing tests\n", fails);
   if (argc < 2) {
-    for (int tune : {0, 1}) {
+    for (int tune : {1, 5}) {
       printf("=== igemm tuning %d ===\n", tune);
       dcgan_set_igemm_tuning(tune);
       bench_layers();
