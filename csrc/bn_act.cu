@@ -17,6 +17,7 @@
 namespace dcgan {
 
 constexpr int kBnThreads = 256;
+constexpr int kRowBatch = 4;  // rows in flight per thread in the streaming loops
 
 // ---------------------------------------------------------------------------------------------
 // forward statistics: sums[g][0][c] += sum x, sums[g][1][c] += sum x^2   (zeroed by the caller)
@@ -112,18 +113,29 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__
   const int r1 = min(r0 + rows_per_block, rows_per_group);
   const uint4* xb = reinterpret_cast<const uint4*>(x) + (size_t)g * rows_per_group * cvec + cv;
   uint4* yb = reinterpret_cast<uint4*>(y) + (size_t)g * rows_per_group * cvec + cv;
-#pragma unroll 2
-  for (int r = r0 + rl; r < r1; r += lanes) {
-    const uint4 v = __ldg(xb + (size_t)r * cvec);
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-    uint32_t o[4];
+  // kRowBatch rows per trip, all loads issued before the first use: the tensors are L2 resident and the loop is
+  // latency-bound otherwise
+  for (int rb = r0 + rl; rb < r1; rb += lanes * kRowBatch) {
+    uint4 v[kRowBatch];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 f = unpack_bf16x2(w[j]);
-      o[j] = pack_bf16x2(apply_act(f.x * sc[2 * j] + sh[2 * j], act),
-                         apply_act(f.y * sc[2 * j + 1] + sh[2 * j + 1], act));
+    for (int u = 0; u < kRowBatch; ++u) {
+      const int r = rb + u * lanes;
+      v[u] = r < r1 ? __ldg(xb + (size_t)r * cvec) : make_uint4(0, 0, 0, 0);
     }
-    yb[(size_t)r * cvec] = make_uint4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+    for (int u = 0; u < kRowBatch; ++u) {
+      const int r = rb + u * lanes;
+      if (r >= r1) break;
+      const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(w[j]);
+        o[j] = pack_bf16x2(apply_act(f.x * sc[2 * j] + sh[2 * j], act),
+                           apply_act(f.y * sc[2 * j + 1] + sh[2 * j + 1], act));
+      }
+      yb[(size_t)r * cvec] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
   }
 }
 
@@ -166,21 +178,33 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* 
     const int r1 = min(r0 + rows_per_block, rows_per_group);
     const __nv_bfloat16* dab = da + ((size_t)g * rows_per_group) * C + cv * 8;
     const __nv_bfloat16* prb = pre + ((size_t)sg * rows_per_group) * C + cv * 8;
-    for (int r = r0 + rl; r < r1; r += lanes) {
-      const uint4 dv = __ldg(reinterpret_cast<const uint4*>(dab + (size_t)r * C));
-      const uint4 pv = __ldg(reinterpret_cast<const uint4*>(prb + (size_t)r * C));
-      const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
-      const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
+    for (int rb = r0 + rl; rb < r1; rb += lanes * kRowBatch) {
+      uint4 dvv[kRowBatch], pvv[kRowBatch];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 d = unpack_bf16x2(dw[j]);
-        const float2 p = unpack_bf16x2(pw[j]);
-        const float xh0 = (p.x - mean[2 * j]) * rstd[2 * j];
-        const float xh1 = (p.y - mean[2 * j + 1]) * rstd[2 * j + 1];
-        const float dy0 = d.x * act_grad(gm[2 * j] * xh0 + bt[2 * j], act);
-        const float dy1 = d.y * act_grad(gm[2 * j + 1] * xh1 + bt[2 * j + 1], act);
-        s1[2 * j] += dy0; s2[2 * j] += dy0 * xh0;
-        s1[2 * j + 1] += dy1; s2[2 * j + 1] += dy1 * xh1;
+      for (int u = 0; u < kRowBatch; ++u) {
+        const int r = rb + u * lanes;
+        dvv[u] = pvv[u] = make_uint4(0, 0, 0, 0);
+        if (r < r1) {
+          dvv[u] = __ldg(reinterpret_cast<const uint4*>(dab + (size_t)r * C));
+          pvv[u] = __ldg(reinterpret_cast<const uint4*>(prb + (size_t)r * C));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kRowBatch; ++u) {
+        if (rb + u * lanes >= r1) break;
+        const uint32_t dw[4] = {dvv[u].x, dvv[u].y, dvv[u].z, dvv[u].w};
+        const uint32_t pw[4] = {pvv[u].x, pvv[u].y, pvv[u].z, pvv[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 d = unpack_bf16x2(dw[j]);
+          const float2 p = unpack_bf16x2(pw[j]);
+          const float xh0 = (p.x - mean[2 * j]) * rstd[2 * j];
+          const float xh1 = (p.y - mean[2 * j + 1]) * rstd[2 * j + 1];
+          const float dy0 = d.x * act_grad(gm[2 * j] * xh0 + bt[2 * j], act);
+          const float dy1 = d.y * act_grad(gm[2 * j + 1] * xh1 + bt[2 * j + 1], act);
+          s1[2 * j] += dy0; s2[2 * j] += dy0 * xh0;
+          s1[2 * j + 1] += dy1; s2[2 * j + 1] += dy1 * xh1;
+        }
       }
     }
 #pragma unroll
@@ -242,25 +266,37 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* _
   const uint4* dab = reinterpret_cast<const uint4*>(da) + (size_t)g * rows_per_group * cvec + cv;
   const uint4* prb = reinterpret_cast<const uint4*>(pre) + (size_t)sg * rows_per_group * cvec + cv;
   uint4* dpb = reinterpret_cast<uint4*>(dpre) + (size_t)g * rows_per_group * cvec + cv;
-#pragma unroll 2
-  for (int r = r0 + rl; r < r1; r += lanes) {
-    const uint4 dv = __ldg(dab + (size_t)r * cvec);
-    const uint4 pv = __ldg(prb + (size_t)r * cvec);
-    const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
-    const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
-    uint32_t o[4];
+  for (int rb = r0 + rl; rb < r1; rb += lanes * kRowBatch) {
+    uint4 dvv[kRowBatch], pvv[kRowBatch];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 d = unpack_bf16x2(dw[j]);
-      const float2 p = unpack_bf16x2(pw[j]);
-      const float xh0 = (p.x - mean[2 * j]) * rstd[2 * j];
-      const float xh1 = (p.y - mean[2 * j + 1]) * rstd[2 * j + 1];
-      const float dy0 = d.x * act_grad(gm[2 * j] * xh0 + bt[2 * j], act);
-      const float dy1 = d.y * act_grad(gm[2 * j + 1] * xh1 + bt[2 * j + 1], act);
-      o[j] = pack_bf16x2(gm[2 * j] * rstd[2 * j] * (dy0 - m1[2 * j] - xh0 * m2[2 * j]),
-                         gm[2 * j + 1] * rstd[2 * j + 1] * (dy1 - m1[2 * j + 1] - xh1 * m2[2 * j + 1]));
+    for (int u = 0; u < kRowBatch; ++u) {
+      const int r = rb + u * lanes;
+      dvv[u] = pvv[u] = make_uint4(0, 0, 0, 0);
+      if (r < r1) {
+        dvv[u] = __ldg(dab + (size_t)r * cvec);
+        pvv[u] = __ldg(prb + (size_t)r * cvec);
+      }
     }
-    dpb[(size_t)r * cvec] = make_uint4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+    for (int u = 0; u < kRowBatch; ++u) {
+      const int r = rb + u * lanes;
+      if (r >= r1) break;
+      const uint32_t dw[4] = {dvv[u].x, dvv[u].y, dvv[u].z, dvv[u].w};
+      const uint32_t pw[4] = {pvv[u].x, pvv[u].y, pvv[u].z, pvv[u].w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 d = unpack_bf16x2(dw[j]);
+        const float2 p = unpack_bf16x2(pw[j]);
+        const float xh0 = (p.x - mean[2 * j]) * rstd[2 * j];
+        const float xh1 = (p.y - mean[2 * j + 1]) * rstd[2 * j + 1];
+        const float dy0 = d.x * act_grad(gm[2 * j] * xh0 + bt[2 * j], act);
+        const float dy1 = d.y * act_grad(gm[2 * j + 1] * xh1 + bt[2 * j + 1], act);
+        o[j] = pack_bf16x2(gm[2 * j] * rstd[2 * j] * (dy0 - m1[2 * j] - xh0 * m2[2 * j]),
+                           gm[2 * j + 1] * rstd[2 * j + 1] * (dy1 - m1[2 * j + 1] - xh1 * m2[2 * j + 1]));
+      }
+      dpb[(size_t)r * cvec] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
   }
 }
 
@@ -286,23 +322,36 @@ act_bwd_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __rest
     for (int j = 0; j < 8; ++j) s[j] = 0.f;
     const int r0 = blockIdx.x * rows_per_block;
     const int r1 = min(r0 + rows_per_block, rows);
-    for (int r = r0 + rl; r < r1; r += lanes) {
-      const int ar = r < a_rows ? r : r - (rows - a_rows);  // third slab re-uses the fake slab's activations
-      const uint4 dv = __ldg(reinterpret_cast<const uint4*>(da + (size_t)r * C + cv * 8));
-      const uint4 av = __ldg(reinterpret_cast<const uint4*>(a + (size_t)ar * C + cv * 8));
-      const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
-      const uint32_t aw[4] = {av.x, av.y, av.z, av.w};
-      uint32_t o[4];
+    for (int rb = r0 + rl; rb < r1; rb += lanes * kRowBatch) {
+      uint4 dvv[kRowBatch], avv[kRowBatch];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 d = unpack_bf16x2(dw[j]);
-        const float2 p = unpack_bf16x2(aw[j]);
-        const float r0v = d.x * act_grad(p.x, act);
-        const float r1v = d.y * act_grad(p.y, act);
-        if (r < bias_rows) { s[2 * j] += r0v; s[2 * j + 1] += r1v; }
-        o[j] = pack_bf16x2(r0v, r1v);
+      for (int u = 0; u < kRowBatch; ++u) {
+        const int r = rb + u * lanes;
+        dvv[u] = avv[u] = make_uint4(0, 0, 0, 0);
+        if (r < r1) {
+          const int ar = r < a_rows ? r : r - (rows - a_rows);  // third slab re-uses the fake slab's activations
+          dvv[u] = __ldg(reinterpret_cast<const uint4*>(da + (size_t)r * C + cv * 8));
+          avv[u] = __ldg(reinterpret_cast<const uint4*>(a + (size_t)ar * C + cv * 8));
+        }
       }
-      *reinterpret_cast<uint4*>(dpre + (size_t)r * C + cv * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+      for (int u = 0; u < kRowBatch; ++u) {
+        const int r = rb + u * lanes;
+        if (r >= r1) break;
+        const uint32_t dw[4] = {dvv[u].x, dvv[u].y, dvv[u].z, dvv[u].w};
+        const uint32_t aw[4] = {avv[u].x, avv[u].y, avv[u].z, avv[u].w};
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 d = unpack_bf16x2(dw[j]);
+          const float2 p = unpack_bf16x2(aw[j]);
+          const float r0v = d.x * act_grad(p.x, act);
+          const float r1v = d.y * act_grad(p.y, act);
+          if (r < bias_rows) { s[2 * j] += r0v; s[2 * j + 1] += r1v; }
+          o[j] = pack_bf16x2(r0v, r1v);
+        }
+        *reinterpret_cast<uint4*>(dpre + (size_t)r * C + cv * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
     }
     if (dbias) {
 #pragma unroll
