@@ -407,6 +407,217 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
   if (warp == 1) tmem_dealloc(tmem_base, BLOCK_N);
 }
 
+
+// =================================================================================================
+// Parity-fused transposed conv ("T4"): one CTA computes all four output parity classes of its 128
+// input locations.  The nine shifted gathers (dy, dx in {-1,0,1}) are the only distinct A tiles -- the
+// per-parity kernels above gather 25 -- and each feeds the 1, 2 or 4 parity accumulators whose filter
+// tap lands on that shift.  A tiles and filter tiles travel in separate rings (one A tile serves up to
+// four B tiles); the four f32 accumulators take 4 x BLOCK_N TMEM columns.
+// Used for the large-M layers (many CTAs), where the gather traffic from L2 is the bound
+// (profiles/README.md): d_h1/d_h2 data gradients, g_h3 forward.
+// =================================================================================================
+template <int BLOCK_N, int A_STAGES, int B_SLOTS>
+struct SmemLayoutT4 {
+  static constexpr int kBTileBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kBOffset = A_STAGES * kATileBytes;
+  static constexpr int kBarOffset = kBOffset + B_SLOTS * kBTileBytes;
+  static constexpr int kStatOffset = kBarOffset + 512;
+  static constexpr int kTotal = kStatOffset + 2 * BLOCK_N * 4 + 1024;
+};
+
+template <int BLOCK_N, int A_STAGES, int B_SLOTS>
+__global__ void __launch_bounds__(kNumThreads, (SmemLayoutT4<BLOCK_N, A_STAGES, B_SLOTS>::kTotal <= 110 * 1024 &&
+                                                BLOCK_N <= 64) ? 2 : 1)
+igemm_t4_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
+  using L = SmemLayoutT4<BLOCK_N, A_STAGES, B_SLOTS>;
+  constexpr int kGatherDepth = (A_STAGES - 1 < 3) ? A_STAGES - 1 : 3;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+  uint64_t* a_empty = a_full + A_STAGES;
+  uint64_t* b_full = a_empty + A_STAGES;
+  uint64_t* b_empty = b_full + B_SLOTS;
+  uint64_t* tmem_full_bar = b_empty + B_SLOTS;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+  float* stat_smem = reinterpret_cast<float*>(smem + L::kStatOffset);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int m0 = blockIdx.x * kBlockM, n0 = blockIdx.y * BLOCK_N;
+  const int cpt = p.gC / kBlockK;
+  const int num_a = 9 * cpt;  // (shift, channel chunk) items
+
+  if (tid == 0) {
+    for (int s = 0; s < A_STAGES; ++s) { mbar_init(&a_full[s], kNumGatherThreads); mbar_init(&a_empty[s], 1); }
+    for (int s = 0; s < B_SLOTS; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    mbar_init(tmem_full_bar, 1);
+    *abort_flag = 0;
+    fence_mbar_init();
+    tma_prefetch_desc(&tmap);
+  }
+  if (warp == 1) { tmem_alloc(tmem_ptr_smem, 4 * BLOCK_N); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ============================ TMA producer: filter tiles =======================================
+    if (lane == 0) {
+      int b = 0;
+      bool ok = true;
+      for (int a = 0; a < num_a && ok; ++a) {
+        const int sft = a / cpt, c0 = (a - sft * cpt) * kBlockK;
+        const int dy = sft / 3 - 1, dx = sft % 3 - 1;
+        for (int ph = (dy == 1) ? 1 : 0; ph < 2 && ok; ++ph)
+          for (int pw = (dx == 1) ? 1 : 0; pw < 2; ++pw) {
+            const int tap = (ph + 1 - 2 * dy) * 5 + (pw + 1 - 2 * dx);
+            const int slot = b % B_SLOTS;
+            if (!mbar_wait(&b_empty[slot], ((b / B_SLOTS) & 1) ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+            mbar_arrive_expect_tx(&b_full[slot], L::kBTileBytes);
+            tma_load_2d(smem + L::kBOffset + slot * L::kBTileBytes, &tmap, &b_full[slot], c0, tap * p.Cn + n0);
+            ++b;
+          }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================ MMA issuer ========================================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
+      int b = 0;
+      uint32_t started = 0;  // bit p: parity accumulator p already holds a partial sum
+      bool ok = true;
+      for (int a = 0; a < num_a && ok; ++a) {
+        const int st = a % A_STAGES;
+        const int sft = a / cpt;
+        const int dy = sft / 3 - 1, dx = sft % 3 - 1;
+        ok = mbar_wait(&a_full[st], (a / A_STAGES) & 1, abort_flag, p.err_flag);
+        if (!ok) break;
+        const uint32_t a_addr = smem_u32(smem + st * kATileBytes);
+        for (int ph = (dy == 1) ? 1 : 0; ph < 2 && ok; ++ph)
+          for (int pw = (dx == 1) ? 1 : 0; pw < 2; ++pw) {
+            const int slot = b % B_SLOTS;
+            if (!mbar_wait(&b_full[slot], (b / B_SLOTS) & 1, abort_flag, p.err_flag)) { ok = false; break; }
+            tc_fence_after();
+            const int par = ph * 2 + pw;
+            const uint32_t b_addr = smem_u32(smem + L::kBOffset + slot * L::kBTileBytes);
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k) {
+              const uint64_t da = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+              const uint64_t db = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+              umma_bf16(tmem_base + par * BLOCK_N, da, db, idesc, (((started >> par) & 1u) | (k != 0)) ? 1u : 0u);
+            }
+            started |= 1u << par;
+            umma_commit(&b_empty[slot]);
+            ++b;
+          }
+        umma_commit(&a_empty[st]);
+      }
+      umma_commit(tmem_full_bar);
+    }
+  } else {
+    // ============================ gather producers, then epilogue ====================================
+    const int gt = tid - 64, chunk = gt & 7, rbase = gt >> 3;
+    const int rW = 1 << p.rW_log2, rH = 1 << p.rH_log2;
+    bool ok = true;
+    int pix_base[8], yx[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int R = m0 + rbase + 16 * i;
+      if (R < p.rows_total) {
+        const int qw = R & (rW - 1), qh = (R >> p.rW_log2) & (rH - 1), n = R >> (p.rW_log2 + p.rH_log2);
+        pix_base[i] = n * p.gH * p.gW;
+        yx[i] = (qh << 16) | qw;
+      } else { pix_base[i] = -1; yx[i] = 0; }
+    }
+    for (int it = 0; it < num_a + kGatherDepth - 1; ++it) {
+      if (it < num_a) {
+        const int st = it % A_STAGES;
+        const int sft = it / cpt, c0 = (it - sft * cpt) * kBlockK;
+        const int dy = sft / 3 - 1, dx = sft % 3 - 1;
+        if (!mbar_wait(&a_empty[st], ((it / A_STAGES) & 1) ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+        const uint32_t sA = smem_u32(smem + st * kATileBytes);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int y = (yx[i] >> 16) + dy, x = (yx[i] & 0xffff) + dx;
+          const bool valid = pix_base[i] >= 0 && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW;
+          const size_t off = valid ? ((size_t)(pix_base[i] + y * p.gW + x)) * p.gC + c0 + chunk * 8 : 0;
+          cp_async_16(sA + swz128(rbase + 16 * i, chunk), p.g + off, valid ? 16u : 0u);
+        }
+      }
+      cp_async_commit();
+      if (it >= kGatherDepth - 1) {
+        cp_async_wait<kGatherDepth - 1>();
+        fence_proxy_async_smem();
+        mbar_arrive(&a_full[(it - (kGatherDepth - 1)) % A_STAGES]);
+      }
+    }
+    // ------------------------------------ epilogue: four parity accumulators ---------------------------
+    const bool do_stats = p.stats != nullptr;
+    if (do_stats) {
+      for (int i = gt; i < 2 * BLOCK_N; i += kNumGatherThreads) stat_smem[i] = 0.f;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
+    if (ok) ok = mbar_wait(tmem_full_bar, 0, abort_flag, p.err_flag);
+    tc_fence_after();
+    const int q = warp & 3;
+    const int R = m0 + q * 32 + lane;
+    const bool valid = ok && R < p.rows_total;
+    const int qw = R & (rW - 1), qh = (R >> p.rW_log2) & (rH - 1), n = R >> (p.rW_log2 + p.rH_log2);
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+    for (int par = 0; par < 4; ++par) {
+      const int oh = 2 * qh + (par >> 1), ow = 2 * qw + (par & 1);
+      __nv_bfloat16* orow =
+          reinterpret_cast<__nv_bfloat16*>(p.out) + ((size_t)((n * p.oH + oh) * p.oW + ow)) * p.Cn + n0;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + par * BLOCK_N + c, v);
+        tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float a = __uint_as_float(v[j]);
+          if (p.bias != nullptr) a += __ldg(p.bias + n0 + c + j);
+          f[j] = valid ? a : 0.f;
+        }
+        if (valid) {
+          uint32_t packed[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            packed[j] = pack_bf16x2(apply_act(f[2 * j], p.act), apply_act(f[2 * j + 1], p.act));
+          uint4* dst = reinterpret_cast<uint4*>(orow + c);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+        }
+        if (do_stats) {
+          float sq[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) sq[j] = f[j] * f[j];
+          const float s1 = warp_transpose_reduce32(f);
+          const float s2 = warp_transpose_reduce32(sq);
+          atomicAdd(&stat_smem[c + lane], s1);
+          atomicAdd(&stat_smem[BLOCK_N + c + lane], s2);
+        }
+      }
+    }
+    if (do_stats) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      float* gs = p.stats + (size_t)(m0 / p.stat_group_rows) * 2 * p.Cn + n0;
+      for (int i = gt; i < BLOCK_N; i += kNumGatherThreads) {
+        atomicAdd(gs + i, stat_smem[i]);
+        atomicAdd(gs + p.Cn + i, stat_smem[BLOCK_N + i]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 4 * BLOCK_N);
+}
+
 // =================================================================================================
 // host side
 // =================================================================================================
@@ -491,7 +702,7 @@ static int launch(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cuda
 }
 
 // tuning knob (bring-up / profiling): bit 0 = two CTAs per SM with shallower stage rings
-static int g_igemm_tuning = 1;
+static int g_igemm_tuning = 1;  // bit 3 (8): parity-fused transposed conv for large-M layers; bit 4: its N=128 tile
 
 template <int MODE>
 static int dispatch_n(int block_n, const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cudaStream_t st) {
@@ -505,6 +716,20 @@ static int dispatch_n(int block_n, const CUtensorMap& tmap, const IgemmParams& p
     case 256: return launch<MODE, 256, 4>(tmap, p, grid, st);
     default: return DCGAN_ERR_SHAPE;
   }
+}
+
+template <int BLOCK_N, int A_STAGES, int B_SLOTS>
+static int launch_t4(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cudaStream_t stream) {
+  using L = SmemLayoutT4<BLOCK_N, A_STAGES, B_SLOTS>;
+  auto kern = igemm_t4_kernel<BLOCK_N, A_STAGES, B_SLOTS>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal) != cudaSuccess)
+      return DCGAN_ERR_LAUNCH;
+    attr_done = true;
+  }
+  kern<<<grid, kNumThreads, L::kTotal, stream>>>(tmap, p);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 
 static int pick_block_n(int Cn, int rows_tiles, int extra_parallel) {
@@ -601,6 +826,18 @@ static int conv_tconv_impl(const void* x, const void* w_nk, const float* bias, v
   }
   p.out = out; p.bias = bias; p.act = act; p.oH = 2 * H; p.oW = 2 * W;
   const int mt = (p.rows_total + kBlockM - 1) / kBlockM;
+  // large-M layers: parity-fused kernel (9 gathers per channel chunk instead of 25); block_n < 0 forces the
+  // per-parity kernels (tests / profiling)
+  const bool want_t4 = (g_igemm_tuning & 8) && block_n == 0 && mt >= 90 && (Cout == 64 || Cout == 128);
+  if (want_t4) {
+    const int bn = (Cout == 128 && (g_igemm_tuning & 16)) ? 128 : 64;
+    CUtensorMap tmap4;
+    int rc4 = get_tmap_2d(w_nk, (uint64_t)25 * Cout, Cin, bn, 64, &tmap4);
+    if (rc4) return rc4;
+    dim3 grid4(mt, Cout / bn, 1);
+    return bn == 64 ? launch_t4<64, 3, 6>(tmap4, p, grid4, stream) : launch_t4<128, 3, 6>(tmap4, p, grid4, stream);
+  }
+  if (block_n < 0) block_n = 0;
   if (block_n <= 0) block_n = pick_block_n(Cout, mt, 4);
   if (block_n < 0 || Cout % block_n) return DCGAN_ERR_SHAPE;
   CUtensorMap tmap;

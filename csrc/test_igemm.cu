@@ -170,8 +170,8 @@ static void bench_layers() {
   for (auto& l : tl) {
     Buf x, w; x.init((size_t)l.NB * l.H * l.H * l.Cin, 1.f); w.init((size_t)25 * l.Cout * l.Cin, 0.05f);
     __nv_bfloat16* o; CK(cudaMalloc(&o, (size_t)l.NB * l.H * l.H * 4 * l.Cout * 2));
-    for (int bn : {64, 128, 256}) {
-      if (l.Cout % bn) continue;
+    for (int bn : {0, 64, 128, 256}) {
+      if (bn && l.Cout % bn) continue;
       float ms = time_ms([&] { dcgan_conv_tconv(x.d, w.d, nullptr, o, l.NB, l.H, l.H, l.Cin, l.Cout, 0, bn, 0); }, 20);
       double fl_ = 2.0 * l.NB * l.H * l.H * l.Cout * 25.0 * l.Cin;
       printf("[TIME] %s bn=%d %.3f ms %.1f TFLOP/s err=%d\n", l.name, bn, ms, fl_ / ms * 1e-9, dcgan_last_device_error());
@@ -205,6 +205,13 @@ int main(int argc, char** argv) {
   fails += test_tconv(2, 8, 8, 64, 64, 64);
   fails += test_tconv(2, 4, 4, 128, 128, 128);
   fails += test_tconv(1, 8, 8, 64, 256, 256);
+  // parity-fused transposed conv (needs >= 90 M tiles: 128*... rows)
+  dcgan_set_igemm_tuning(1 | 8);
+  fails += test_tconv(48, 16, 16, 64, 64, 0);     // 12288 rows = 96 tiles, N=64
+  fails += test_tconv(48, 16, 16, 128, 128, 0);   // Cout=128 as two N=64 tiles
+  dcgan_set_igemm_tuning(1 | 8 | 16);
+  fails += test_tconv(48, 16, 16, 64, 128, 0);    // N=128 tile, 512 TMEM columns
+  dcgan_set_igemm_tuning(1);
   int w0 = test_wgrad(2, 8, 8, 64, 128, 1, 64, 0);
   int w1 = 0;
   if (w0) { w1 = test_wgrad(2, 8, 8, 64, 128, 1, 64, 1); printf("MN-major variant 1 %s\n", w1 ? "also fails" : "passes"); }
@@ -214,7 +221,7 @@ int main(int argc, char** argv) {
   fails += test_wgrad(4, 8, 8, 128, 256, 0, 0, 0);
   printf("correctness: %d failing tests\n", fails);
   if (argc < 2) {
-    for (int tune : {1, 5}) {
+    for (int tune : {1, 9, 25}) {
       printf("=== igemm tuning %d ===\n", tune);
       dcgan_set_igemm_tuning(tune);
       bench_layers();
