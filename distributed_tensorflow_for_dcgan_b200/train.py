@@ -90,10 +90,18 @@ def run_worker(FLAGS, role, cfg) -> int:
             else:
                 from .parallel.async_ps import AsyncPSComm
                 comm = AsyncPSComm(device)
-        from .trainer import EngineTrainer
-        trainer = EngineTrainer(cfg, FLAGS.learning_rate, FLAGS.beta1, FLAGS.seed, FLAGS.update_mode, device, comm,
-                                FLAGS.cuda_graph)
-        trainer.engine.nvtx = bool(FLAGS.profile)   # NVTX ranges per phase for nsys / ncu range filters
+        if FLAGS.dtype == "fp32":
+            # reference-precision path: the oracle model in f32 on the GPU through PyTorch's library kernels
+            # (single process only); the hand-written engine computes in bf16
+            if role.distributed:
+                raise SystemExit("--dtype=fp32 runs the single-process oracle path; use bf16 for multi-GPU")
+            from .trainer import CPUTrainer
+            trainer = CPUTrainer(cfg, FLAGS.learning_rate, FLAGS.beta1, FLAGS.seed, FLAGS.update_mode, device=device)
+        else:
+            from .trainer import EngineTrainer
+            trainer = EngineTrainer(cfg, FLAGS.learning_rate, FLAGS.beta1, FLAGS.seed, FLAGS.update_mode, device,
+                                    comm, FLAGS.cuda_graph)
+            trainer.engine.nvtx = bool(FLAGS.profile)   # NVTX ranges per phase for nsys / ncu range filters
     else:
         from .trainer import CPUTrainer
         allreduce_world = 1

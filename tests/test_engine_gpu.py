@@ -112,12 +112,22 @@ def test_engine_alternating_mode(cuda_lib):
 
 
 def test_training_driver_on_gpu(cuda_lib, tmp_path):
-    """The launch script end to end on one GPU: step log, chief sample grid, TF-named checkpoint, events."""
+    """The launch script end to end on one GPU, fed from TFRecords through the native reader and the device
+    prefetch ring: step log, chief sample grid, TF-named checkpoint, events."""
     import os
     import subprocess
     import sys
+    import numpy as np
+    from distributed_tensorflow_for_dcgan_b200.data import tfrecord
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    cmd = [sys.executable, os.path.join(root, "image_train.py"), "--device=cuda", "--synthetic_data", "--max_steps=12",
+    rng = np.random.RandomState(0)
+    for d in ("train", "sample_data"):
+        os.makedirs(tmp_path / d)
+        for i in range(2):
+            tfrecord.write_image_tfrecord(str(tmp_path / d / f"image_{i}.tfrecords"), rng.rand(100, 64, 64, 3) * 2 - 1)
+    cmd = [sys.executable, os.path.join(root, "image_train.py"), "--device=cuda", "--max_steps=12",
+           f"--data_dir={tmp_path}/train", f"--sample_image_dir={tmp_path}/sample_data",
+           "--shuffle_min_after_dequeue=64", "--num_reader_threads=4",
            "--save_summaries_secs=0", f"--checkpoint_dir={tmp_path}/ckpt", f"--sample_dir={tmp_path}/samples"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=str(tmp_path),
                        env=dict(os.environ, PYTHONPATH=root))
