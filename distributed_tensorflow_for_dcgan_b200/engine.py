@@ -19,6 +19,8 @@ the fused reduce-scatter + Adam + all-gather kernel over NVLink peer memory (par
 """
 from __future__ import annotations
 
+import contextlib
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -184,6 +186,11 @@ class DCGANEngine:
         self.s_act = [torch.zeros_like(t) for t in self.g_pre]
         self.s_img = torch.zeros(B, s, s, 3, **bf)
 
+        # filter gradients are off the critical path (only the optimizer consumes them): they run on a side
+        # stream next to the data-gradient chain, filling the SMs that the small grids leave idle
+        self.wgrad_overlap = os.environ.get("DCGAN_WGRAD_OVERLAP", "1") != "0"
+        self.side = torch.cuda.Stream(self.device)
+        self._side_used = False
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self.refresh_compute_weights()
 
@@ -274,6 +281,34 @@ class DCGANEngine:
         K.bn_bwd_apply(da.view(-1, C), pre.view(-1, C), dpre.view(-1, C), st["saved"], p[f"{name}/gamma"],
                        p[f"{name}/beta"], st["red"], g[f"{name}/gamma"], g[f"{name}/beta"], slabs, G, G, st["act"])
 
+    @contextlib.contextmanager
+    def _off_critical_path(self):
+        """Runs the enclosed launches on the side stream, ordered after everything issued so far on the current
+        stream; ``_join_side()`` orders the current stream after them again."""
+        if not self.wgrad_overlap:
+            yield
+            return
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self.side.wait_event(ev)
+        with torch.cuda.stream(self.side):
+            yield
+        self._side_used = True
+
+    def side_event(self) -> Optional[torch.cuda.Event]:
+        """Event marking the end of the side-stream work issued so far (None when nothing is pending)."""
+        if not self._side_used:
+            return None
+        ev = torch.cuda.Event()
+        ev.record(self.side)
+        return ev
+
+    def _join_side(self) -> None:
+        ev = self.side_event()
+        if ev is not None:
+            torch.cuda.current_stream(self.device).wait_event(ev)
+            self._side_used = False
+
     def discriminator_backward(self) -> None:
         """Three slabs of data gradient ([d_loss|real, d_loss|fake, g_loss|fake]); filter gradients from
         the first two only (``var_list=d_vars`` for d_loss, image_train.py:109-110)."""
@@ -283,25 +318,29 @@ class DCGANEngine:
         for i in (3, 2, 1):
             self._bn_bwd(f"d_bn{i}", self.dd_act[i], self.d_pre[i], self.dd_pre[i])
             ci, co = self.d_ch[i], self.d_ch[i + 1]
-            K.conv_wgrad(self.d_act[i - 1], self.dd_pre[i][:2 * B], g[f"d_h{i}_conv/w"].view(25, ci, co))
+            with self._off_critical_path():
+                K.conv_wgrad(self.d_act[i - 1], self.dd_pre[i][:2 * B], g[f"d_h{i}_conv/w"].view(25, ci, co))
             K.conv_tconv(self.dd_pre[i], self.w_native[f"d_h{i}_conv/w"].view(25, ci, co), None,
                          out=self.dd_act[i - 1])
         C0 = self.d_ch[1]
         K.act_bwd(self.dd_act[0].view(-1, C0), self.d_act[0].view(-1, C0), self.dd_pre[0].view(-1, C0),
                   g["d_h0_conv/biases"], "lrelu", bias_rows=2 * B * self.d_sz[1] * self.d_sz[1])
-        K.c3_wgrad(self.d_in, self.dd_pre[0][:2 * B], g["d_h0_conv/w"])
+        with self._off_critical_path():
+            K.c3_wgrad(self.d_in, self.dd_pre[0][:2 * B], g["d_h0_conv/w"])
         # g_loss slab only: gradient w.r.t. the generator's pre-tanh output
         K.c3_tconv(self.dd_pre[0][2 * B:], p["d_h0_conv/w"], None, aux=self.d_in[B:], out=self.dimg,
                    colsum=g["g_h4/biases"])  # g_h4's bias gradient falls out of the same pass, in f32
 
     def generator_backward(self) -> None:
         p, g, B = self.params, self.grad_views, self.B
-        K.c3_wgrad(self.dimg, self.g_act[3], g["g_h4/w"])
+        with self._off_critical_path():
+            K.c3_wgrad(self.dimg, self.g_act[3], g["g_h4/w"])
         K.c3_fprop(self.dimg, p["g_h4/w"], None, out=self.dg_act[3])
         for i in (3, 2, 1):
             self._bn_bwd(f"g_bn{i}", self.dg_act[i], self.g_pre[i], self.dg_pre[i])
             co, ci = self.g_ch[i], self.g_ch[i - 1]
-            K.conv_wgrad(self.dg_pre[i], self.g_act[i - 1], g[f"g_h{i}/w"].view(25, co, ci))
+            with self._off_critical_path():
+                K.conv_wgrad(self.dg_pre[i], self.g_act[i - 1], g[f"g_h{i}/w"].view(25, co, ci))
             K.conv_fprop_kn(self.dg_pre[i], self.w_native[f"g_h{i}/w"].view(25, co, ci), None, out=self.dg_act[i - 1])
         self._bn_bwd("g_bn0", self.dg_act[0], self.g_pre[0], self.dg_pre[0])
         K.lin_wgrad(self.z, self.dg_pre[0].view(B, -1), g["g_h0_lin/Matrix"], g["g_h0_lin/bias"])
@@ -316,6 +355,7 @@ class DCGANEngine:
 
     def optimizer_step(self, which: str = "both") -> None:
         A = self.arena
+        self._join_side()  # every filter gradient must have landed
         if self.comm is not None:
             self.comm.optimizer_step(self, which)
         else:
@@ -336,23 +376,36 @@ class DCGANEngine:
     def step_body(self) -> None:
         """Everything of one training iteration that runs on the device, in stream order."""
         B = self.B
-        self.zero_region.zero_()
+        # gradients are not touched before the backward pass: their memset runs beside the forward pass
+        with self._off_critical_path():
+            self.grads.zero_()
+        self._scratch.zero_()
         K.f32_to_bf16(self.real_f32, self.d_in[:B])
         with self._range("G_forward"):
             self.generator_forward(train=True)
         with self._range("D_forward"):
             self.discriminator_forward()
             K.gan_loss(self.logits, self.losses, self.dlogit, self.probs, self.counters, B, 1.0, True)
+        self._join_side()
         with self._range("D_backward"):
             self.discriminator_backward()
         if self.update_mode == "simultaneous":
             if self.comm is not None and getattr(self.comm, "overlap", False):
                 # D's gradient exchange + Adam runs on the communication stream under G's backward pass
-                self.comm.launch_bucket(self, "d", side_stream=True)
+                self.comm.launch_bucket(self, "d", side_stream=True, also_wait=self.side_event())
                 self.generator_backward()
+                self._join_side()
                 self.comm.launch_bucket(self, "g", side_stream=False)
                 self.comm.join()
                 self.refresh_compute_weights(cast=False)
+            elif self.comm is None and self.wgrad_overlap:
+                # D's Adam (its gradients are complete) runs beside G's backward pass
+                A = self.arena
+                with self._off_critical_path():
+                    self._adam_range(A.g_end, A.padded)
+                self.generator_backward()
+                self._join_side()
+                self._adam_range(0, A.g_end)
             else:
                 self.generator_backward()
                 self.optimizer_step("both")

@@ -129,11 +129,13 @@ class FusedComm:
                   engine.params["g_h0_lin/bias"].data_ptr(), out2d.data_ptr(), engine.B, shape[0], shape[1], off, lo,
                   hi, self.rank, self.world)
 
-    def launch_bucket(self, engine, which: str, side_stream: bool) -> None:
+    def launch_bucket(self, engine, which: str, side_stream: bool, also_wait=None) -> None:
         if side_stream:
             cur = torch.cuda.current_stream(self.device)
             self._fork_event.record(cur)
             self.stream.wait_event(self._fork_event)
+            if also_wait is not None:   # e.g. the engine's side stream that carries the filter gradients
+                self.stream.wait_event(also_wait)
             with torch.cuda.stream(self.stream):
                 self._launch(engine, which)
                 self._join_event.record(self.stream)
