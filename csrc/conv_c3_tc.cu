@@ -326,6 +326,175 @@ c3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ x3, const __nv_bfloat16* __
   if (warp == 0) tmem_dealloc(tmem_base, 64);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// C -> 3 transposed conv on tensor cores (g_h4 forward, distriubted_model.py:109; d_h0 data gradient).
+//   step 1 (tcgen05): Y[q][tap*3+co] = sum_ci x[q][ci] * W[tap][co][ci]       -- a plain GEMM, no im2col:
+//           M = input locations (an 8x16 tile plus a one-pixel halo = 180 rows in two 128-row MMAs),
+//           N = 80 (75 tap/channel pairs + padding), K = 64 channels.
+//   step 2 (col2im in shared memory): out[2q+p][co] = sum over the taps of parity p of Y[q + (p+1-k)/2][tap][co],
+//           then bias+tanh, or the tanh backward against `aux`, and the optional per-channel sum.
+// grid = (tiles, 1); C must be 64.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kTH2 = 8, kTW2 = 16;                       // interior tile (input locations)
+constexpr int kHaloW = kTW2 + 2, kHaloRows = (kTH2 + 2) * (kTW2 + 2);  // 18, 180
+constexpr int kYPitch = 77;                              // f32 per Y row (75 used; odd pitch -> conflict-free)
+constexpr int kTconvTcSmem = 32768 /*A*/ + 128 * 128 /*B (80 rows used)*/ + kHaloRows * kYPitch * 4 + 64 + 1024;
+
+__global__ void __launch_bounds__(kTcThreads)
+c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w_bf16 /*[75][64]*/,
+                   const float* __restrict__ bias, const __nv_bfloat16* __restrict__ aux,
+                   __nv_bfloat16* __restrict__ out, float* __restrict__ colsum, int N, int H, int W, int act,
+                   int mode, int* err_flag) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_tiles = smem;                       // 2 x [128 rows][128 B]: halo rows 0..179 (+ zero rows)
+  uint8_t* b_tile = smem + 32768;                // [80 rows (tap*3+co)][128 B]
+  float* ysm = reinterpret_cast<float*>(smem + 32768 + 16384);
+  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(smem + 32768 + 16384 + kHaloRows * kYPitch * 4);
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(mma_bar + 1);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+  __shared__ float cred[3];
+
+  const int t = threadIdx.x, warp = t >> 5;
+  if (t == 0) { mbar_init(mma_bar, 1); *abort_flag = 0; fence_mbar_init(); }
+  if (t < 3) cred[t] = 0.f;
+  if (warp == 0) { tmem_alloc(tmem_ptr_smem, 256); tmem_relinquish(); }
+  // B: filter rows (tap*3+co) x 64 channels, K-major SW128; rows 75..79 zero
+  for (int i = t; i < 80 * 8; i += kTcThreads) {
+    const int row = i >> 3, ch = i & 7;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (row < 75) v = __ldg(reinterpret_cast<const uint4*>(w_bf16 + (size_t)row * 64) + ch);
+    *reinterpret_cast<uint4*>(b_tile + swz(row, ch)) = v;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t a_addr = smem_u32(a_tiles), b_addr = smem_u32(b_tile);
+  constexpr uint32_t idesc = make_idesc_bf16(128, 80, 0, 0);
+
+  const int tiles_x = W / kTW2, tiles_y = H / kTH2;
+  const int tiles = N * tiles_y * tiles_x;
+  const int oH = 2 * H, oW = 2 * W;
+  uint32_t phase = 0;
+  float csum[3] = {0.f, 0.f, 0.f};
+  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int n = tile / (tiles_y * tiles_x);
+    const int tr = tile - n * tiles_y * tiles_x;
+    const int qy0 = (tr / tiles_x) * kTH2, qx0 = (tr % tiles_x) * kTW2;
+    // ---- gather the halo tile: 256 rows x 8 chunks, zero outside the image / beyond row 179 -----------------
+    {
+      uint4 v[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int idx = t + k * kTcThreads;        // 0..2047 = row * 8 + chunk
+        const int row = idx >> 3, ch = idx & 7;
+        v[k] = make_uint4(0, 0, 0, 0);
+        if (row < kHaloRows) {
+          const int ly = row / kHaloW, lx = row - ly * kHaloW;
+          const int qy = qy0 - 1 + ly, qx = qx0 - 1 + lx;
+          if ((unsigned)qy < (unsigned)H && (unsigned)qx < (unsigned)W)
+            v[k] = __ldg(reinterpret_cast<const uint4*>(x + (((size_t)n * H + qy) * W + qx) * 64) + ch);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int idx = t + k * kTcThreads;
+        const int row = idx >> 3, ch = idx & 7;
+        *reinterpret_cast<uint4*>(a_tiles + (row >> 7) * 16384 + swz(row & 127, ch)) = v[k];
+      }
+    }
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (t == 0) {
+      tc_fence_after();
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t da = make_smem_desc_sw128(a_addr + j * 16384 + k * 32, 16, 1024);
+          const uint64_t db = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+          umma_bf16(tmem_base + j * 128, da, db, idesc, k != 0 ? 1u : 0u);
+        }
+      umma_commit(mma_bar);
+    }
+    const bool ok = mbar_wait(mma_bar, phase, abort_flag, err_flag);
+    phase ^= 1;
+    tc_fence_after();
+    // ---- TMEM -> Y in shared memory ----------------------------------------------------------------------------
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int row = j * 128 + t;
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + j * 128;
+      uint32_t v0[32], v1[32], v2[16];
+      tmem_ld_32x32(taddr, v0);
+      tmem_ld_32x32(taddr + 32, v1);
+      tmem_ld_32x16(taddr + 64, v2);
+      tmem_ld_wait();
+      if (row < kHaloRows) {
+        float* yr = ysm + row * kYPitch;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) { yr[c] = __uint_as_float(v0[c]); yr[32 + c] = __uint_as_float(v1[c]); }
+#pragma unroll
+        for (int c = 0; c < 11; ++c) yr[64 + c] = __uint_as_float(v2[c]);
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+    // ---- col2im: thread = interior location (ty, tx) -> its 2x2 output quad ---------------------------------
+    if (ok) {
+      const int ty = t / kTW2, tx = t - ty * kTW2;
+      const int qy = qy0 + ty, qx = qx0 + tx;
+#pragma unroll
+      for (int ph = 0; ph < 2; ++ph) {
+        float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int pw = 0; pw < 2; ++pw)
+#pragma unroll
+          for (int kh = 1 - ph; kh < 5; kh += 2)      // taps of this row parity: kh = ph+1 (mod 2)
+#pragma unroll
+            for (int kw = 1 - pw; kw < 5; kw += 2) {
+              const int dy = (ph + 1 - kh) / 2, dx = (pw + 1 - kw) / 2;
+              const float* yr = ysm + ((ty + 1 + dy) * kHaloW + (tx + 1 + dx)) * kYPitch + (kh * 5 + kw) * 3;
+              v[pw * 3 + 0] += yr[0]; v[pw * 3 + 1] += yr[1]; v[pw * 3 + 2] += yr[2];
+            }
+        const size_t o = (((size_t)n * oH + 2 * qy + ph) * oW + 2 * qx) * 3;  // 6 contiguous bf16
+        if (mode == 0) {
+#pragma unroll
+          for (int j = 0; j < 6; ++j) v[j] = apply_act(v[j] + (bias ? bias[j % 3] : 0.f), act);
+        } else {
+          const uint32_t* ap = reinterpret_cast<const uint32_t*>(aux + o);
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            const float2 a = unpack_bf16x2(ap[j]);
+            v[2 * j] *= (1.f - a.x * a.x);
+            v[2 * j + 1] *= (1.f - a.y * a.y);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 6; ++j) csum[j % 3] += v[j];
+        uint32_t* op = reinterpret_cast<uint32_t*>(out + o);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) op[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+      }
+    }
+    __syncthreads();  // Y and the A tiles are free for the next tile
+  }
+  if (colsum != nullptr) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float s = warp_sum(csum[c]);
+      if ((t & 31) == 0) atomicAdd(&cred[c], s);
+    }
+    __syncthreads();
+    if (t < 3) atomicAdd(&colsum[t], cred[t]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 256);
+}
+
 constexpr int kTcSmem = 32768 + 16384 + kPatchMaxElems * 2 + 64 + 256 + 1024;
 
 }  // namespace dcgan
@@ -358,6 +527,27 @@ int dcgan_c3_fprop_tc(const void* x, const float* w, const float* bias, void* ou
   dim3 grid(tiles < cap_f ? tiles : cap_f, C / 64);
   c3_fprop_tc_kernel<<<grid, kTcThreads, kTcSmem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), w, bias,
                                                         reinterpret_cast<__nv_bfloat16*>(out), N, H, W, C, act, err);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_c3_tconv_tc(const void* x, const void* w_bf16, const float* bias, const void* aux, void* out, float* colsum,
+                      int N, int H, int W, int C, int act, int mode, cudaStream_t st) {
+  if (C != 64 || H % kTH2 || W % kTW2) return DCGAN_ERR_SHAPE;
+  static bool attr = false;
+  if (!attr) {
+    if (cudaFuncSetAttribute(c3_tconv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTconvTcSmem) !=
+        cudaSuccess)
+      return DCGAN_ERR_LAUNCH;
+    attr = true;
+  }
+  int* err = error_flag_ptr();
+  if (!err) return DCGAN_ERR_DRIVER;
+  const int tiles = N * (H / kTH2) * (W / kTW2);
+  dim3 grid(tiles < 296 ? tiles : 296);
+  c3_tconv_tc_kernel<<<grid, kTcThreads, kTconvTcSmem, st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(w_bf16), bias,
+      reinterpret_cast<const __nv_bfloat16*>(aux), reinterpret_cast<__nv_bfloat16*>(out), colsum, N, H, W, act, mode,
+      err);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 

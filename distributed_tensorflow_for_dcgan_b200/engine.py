@@ -249,7 +249,7 @@ class DCGANEngine:
                 K.conv_tconv(act[i - 1], w, p[f"g_h{i}/biases"], out=pre[i])
             self._bn_fwd(f"g_bn{i}", pre[i], act[i], train, stats_done=fused)
         out = self.d_in[B:] if train else self.s_img
-        K.c3_tconv(act[3], p["g_h4/w"], p["g_h4/biases"], act="tanh", out=out)
+        K.c3_tconv(act[3], p["g_h4/w"], p["g_h4/biases"], act="tanh", out=out, w_bf16=self.w_native["g_h4/w"])
         return out
 
     def discriminator_forward(self) -> None:
@@ -329,7 +329,8 @@ class DCGANEngine:
             K.c3_wgrad(self.d_in, self.dd_pre[0][:2 * B], g["d_h0_conv/w"])
         # g_loss slab only: gradient w.r.t. the generator's pre-tanh output
         K.c3_tconv(self.dd_pre[0][2 * B:], p["d_h0_conv/w"], None, aux=self.d_in[B:], out=self.dimg,
-                   colsum=g["g_h4/biases"])  # g_h4's bias gradient falls out of the same pass, in f32
+                   colsum=g["g_h4/biases"],  # g_h4's bias gradient falls out of the same pass, in f32
+                   w_bf16=self.w_native["d_h0_conv/w"])
 
     def generator_backward(self) -> None:
         p, g, B = self.params, self.grad_views, self.B

@@ -29,6 +29,7 @@ _SIGNATURES = {
     "dcgan_c3_wgrad": "pppiiiis",
     "dcgan_c3_fprop_tc": "ppppiiiiis",
     "dcgan_c3_wgrad_tc": "pppiiiis",
+    "dcgan_c3_tconv_tc": "ppppppiiiiiis",
     "dcgan_bn_stats": "ppiiis",
     "dcgan_bn_apply": "ppppppppiiiffiis",
     "dcgan_bn_bwd_reduce": "ppppppiiiiis",

@@ -99,6 +99,10 @@ int dcgan_c3_wgrad(const void* x3, const void* y, float* dw, int N, int Hs, int 
 int dcgan_c3_fprop_tc(const void* x, const float* w, const float* bias, void* out, int N, int H, int W, int C,
                       int act, cudaStream_t stream);
 int dcgan_c3_wgrad_tc(const void* x3, const void* y, float* dw, int N, int Hs, int Ws, int C, cudaStream_t stream);
+/* C=64 -> 3 transposed conv as a plain GEMM Y[q][tap*3+co] on tcgen05 followed by a col2im in shared memory;
+ * same contract as dcgan_c3_tconv but the filter comes as the bf16 shadow [75][64]. */
+int dcgan_c3_tconv_tc(const void* x, const void* w_bf16, const float* bias, const void* aux, void* out, float* colsum,
+                      int N, int H, int W, int C, int act, int mode, cudaStream_t stream);
 
 /* ---- batch norm fused with its activation (csrc/bn_act.cu; reference distriubted_model.py:15-52) --
  * x/y/da/dpre are bf16 [groups*rows_per_group][C]; sums/saved/red are f32 [groups][2][C]. */

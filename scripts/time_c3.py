@@ -26,3 +26,5 @@ print("cuda-core: fprop", t(lambda: K.c3_fprop(x, w, None, out=out, tensor_cores
 xx = torch.randn(64, 32, 32, 64, device="cuda").to(torch.bfloat16)
 oo = torch.empty(64, 64, 64, 3, dtype=torch.bfloat16, device="cuda")
 print("c3_tconv", t(lambda: K.c3_tconv(xx, w, None, act="tanh", out=oo)))
+wb = w.to(torch.bfloat16)
+print("c3_tconv_tc", t(lambda: K.c3_tconv(xx, w, None, act="tanh", out=oo, w_bf16=wb)))

@@ -133,17 +133,22 @@ def test_c3_fprop(cuda_lib, tc, S, C):
     _close(out, ref, name="c3_fprop")
 
 
-def test_c3_tconv_fwd_and_tanh_bwd(cuda_lib):
+@pytest.mark.parametrize("tc", [True, False])
+def test_c3_tconv_fwd_and_tanh_bwd(cuda_lib, tc):
     from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
-    x = _rand((2, 32, 32, 64))
+    x = _rand((3, 32, 32, 64))
     w = torch.randn(5, 5, 3, 64, device="cuda") * 0.05
+    wb = w.to(torch.bfloat16) if tc else None
+    if tc:
+        w = wb.float()
     b = torch.randn(3, device="cuda") * 0.1
-    out = K.c3_tconv(x, w, b, act="tanh")
+    out = K.c3_tconv(x, w, b, act="tanh", w_bf16=wb)
     ref = torch.tanh(Fn.deconv2d(x.float(), w, b))
+    K.check_device_error()
     _close(out, ref, name="c3_tconv")
     aux = out
     cs = torch.zeros(3, device="cuda")
-    out2 = K.c3_tconv(x, w, None, aux=aux, colsum=cs)
+    out2 = K.c3_tconv(x, w, None, aux=aux, colsum=cs, w_bf16=wb)
     ref2 = Fn.deconv2d(x.float(), w) * (1 - aux.float() ** 2)
     _close(out2, ref2, name="c3_tconv_tanh_bwd")
     _close(cs, ref2.sum((0, 1, 2)), rel=2e-3, name="c3_tconv colsum")
