@@ -26,6 +26,8 @@ constexpr int kRowBatch = 4;  // rows in flight per thread in the streaming loop
 __global__ void __launch_bounds__(kBnThreads)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, int rows_per_group, int C,
                 int rows_per_block) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float red[];  // [2][C]
   const int g = blockIdx.y;
   const int cvec = C >> 3;
@@ -74,6 +76,8 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__
                 float* __restrict__ ema_mean /*[G][C] or null*/, float* __restrict__ ema_var,
                 int rows_per_group, int C, float inv_count, float eps, float decay, int act, int use_ema,
                 int rows_per_block) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float ss[];  // scale[C], shift[C]
   const int g = blockIdx.y;
   for (int c = threadIdx.x; c < C; c += kBnThreads) {
@@ -155,6 +159,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* 
                      const float* __restrict__ saved, const float* __restrict__ gamma,
                      const float* __restrict__ beta, float* __restrict__ red_out, int rows_per_group, int C,
                      int n_stat_groups, int act, int rows_per_block) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float red[];  // [2][C]
   const int g = blockIdx.y;
   const int sg = min(g, n_stat_groups - 1);
@@ -229,6 +235,8 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* _
                     const float* __restrict__ red, float* __restrict__ dgamma, float* __restrict__ dbeta,
                     int rows_per_group, int C, int n_stat_groups, int n_param_groups, float inv_count, int act,
                     int rows_per_block) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float sm[];  // mean, rstd, gamma, beta, m1, m2 : 6*C
   const int g = blockIdx.y;
   const int sg = min(g, n_stat_groups - 1);
@@ -309,6 +317,8 @@ __global__ void __launch_bounds__(kBnThreads)
 act_bwd_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ a,
                __nv_bfloat16* __restrict__ dpre, float* __restrict__ dbias, int rows, int a_rows, int C, int act,
                int bias_rows, int rows_per_block) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float red[];  // [C]
   const int cvec = C >> 3;
   const int lanes = kBnThreads / cvec;
@@ -383,7 +393,7 @@ int dcgan_bn_stats(const void* x, float* sums, int groups, int rows_per_group, i
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  bn_stats_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(reinterpret_cast<const __nv_bfloat16*>(x), sums,
+  launch_k(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
                                                                   rows_per_group, C, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
@@ -394,7 +404,7 @@ int dcgan_bn_apply(const void* x, void* y, const float* sums, const float* gamma
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  bn_apply_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(
+  launch_k(bn_apply_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, 
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, saved,
       ema_mean, ema_var, rows_per_group, C, 1.0f / (float)rows_per_group, eps, decay, act, use_ema, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -406,7 +416,7 @@ int dcgan_bn_bwd_reduce(const void* da, const void* pre, const float* saved, con
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  bn_bwd_reduce_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(
+  launch_k(bn_bwd_reduce_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, 
       reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(pre), saved, gamma, beta,
       red, rows_per_group, C, stat_groups, act, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -418,7 +428,7 @@ int dcgan_bn_bwd_apply(const void* da, const void* pre, void* dpre, const float*
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  bn_bwd_apply_kernel<<<grid, kBnThreads, 6 * C * sizeof(float), st>>>(
+  launch_k(bn_bwd_apply_kernel, dim3(grid), dim3(kBnThreads), 6 * C * sizeof(float), st, 
       reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(pre),
       reinterpret_cast<__nv_bfloat16*>(dpre), saved, gamma, beta, red, dgamma, dbeta, rows_per_group, C,
       stat_groups, param_groups, 1.0f / (float)rows_per_group, act, rpb);
@@ -430,7 +440,7 @@ int dcgan_act_bwd(const void* da, const void* a, void* dpre, float* dbias, int r
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows, C, 1);
   dim3 grid((rows + rpb - 1) / rpb);
-  act_bwd_kernel<<<grid, kBnThreads, C * sizeof(float), st>>>(
+  launch_k(act_bwd_kernel, dim3(grid), dim3(kBnThreads), C * sizeof(float), st, 
       reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(a),
       reinterpret_cast<__nv_bfloat16*>(dpre), dbias, rows, a_rows, C, act, bias_rows, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -507,10 +517,10 @@ extern "C" int dcgan_bn_forward_static(const void* x, void* y, const float* gamm
   if (cudaMemsetAsync(sums, 0, need * sizeof(float), st) != cudaSuccess) return DCGAN_ERR_LAUNCH;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  bn_stats_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(reinterpret_cast<const __nv_bfloat16*>(x), sums,
+  launch_k(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
                                                                   rows_per_group, C, rpb);
   if (cudaGetLastError() != cudaSuccess) return DCGAN_ERR_LAUNCH;
-  bn_apply_kernel<<<grid, kBnThreads, 2 * C * sizeof(float), st>>>(
+  launch_k(bn_apply_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, 
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, saved,
       ema_mean, ema_var, rows_per_group, C, 1.0f / (float)rows_per_group, eps, decay, act, 0, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;

@@ -21,6 +21,34 @@ namespace dcgan {
 int* error_flag_ptr();       // host: device address of the flag on the current device
 int* mn_variant_ptr();       // host: device address of the MN-major descriptor switch
 
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch: every hot-path kernel lets its successor start early
+// (launch_dependents at the top) and waits for its predecessor only right before it first touches
+// global memory (pdl_wait), so barrier init / TMEM allocation / shared-memory setup of kernel N+1
+// overlap the tail wave of kernel N.  Without the launch attribute both instructions are no-ops.
+// ---------------------------------------------------------------------------------------------
+bool use_pdl();  // host: DCGAN_PDL env / dcgan_set_pdl()
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                            Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = use_pdl() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 enum DeviceError : int {
   kErrNone = 0,
   kErrMbarTimeout = 1,

@@ -116,6 +116,7 @@ __device__ __forceinline__ void zero_im2col_padding(uint8_t* a_tiles, int t) {
 __global__ void __launch_bounds__(kTcThreads)
 c3_fprop_tc_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                    __nv_bfloat16* __restrict__ out, int N, int H, int W, int C, int act, int* err_flag) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_tiles = smem;                       // 2 x [128][128 B]
@@ -136,6 +137,7 @@ c3_fprop_tc_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict_
   for (int i = t; i < 16384 / 16; i += kTcThreads) reinterpret_cast<uint4*>(b_tiles)[i] = make_uint4(0, 0, 0, 0);
   zero_im2col_padding(a_tiles, t);
   zero_patch(patch);
+  pdl_wait();
   {
     // thread -> output channel co = t & 63 and every other filter row; all 38 loads in flight first
     const int co = t & 63, r0 = t >> 6;
@@ -238,6 +240,7 @@ c3_fprop_tc_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict_
 __global__ void __launch_bounds__(kTcThreads)
 c3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ x3, const __nv_bfloat16* __restrict__ y, float* __restrict__ dw,
                    int N, int Hs, int Ws, int C, int* err_flag) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_tiles = smem;                       // 2 x [128 px][128 B]  (MN-major A: M = k index)
@@ -259,6 +262,7 @@ c3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ x3, const __nv_bfloat16* __
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();
   const uint32_t tmem_base = *tmem_ptr_smem;
   const uint32_t a_addr = smem_u32(a_tiles), b_addr = smem_u32(b_tile);
   constexpr uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);
@@ -346,6 +350,7 @@ c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
                    const float* __restrict__ bias, const __nv_bfloat16* __restrict__ aux,
                    __nv_bfloat16* __restrict__ out, float* __restrict__ colsum, int N, int H, int W, int act,
                    int mode, int* err_flag) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_tiles = smem;                       // 2 x [128 rows][128 B]: halo rows 0..179 (+ zero rows)
@@ -360,6 +365,7 @@ c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
   if (t == 0) { mbar_init(mma_bar, 1); *abort_flag = 0; fence_mbar_init(); }
   if (t < 3) cred[t] = 0.f;
   if (warp == 0) { tmem_alloc(tmem_ptr_smem, 256); tmem_relinquish(); }
+  pdl_wait();
   // B: filter rows (tap*3+co) x 64 channels, K-major SW128; rows 75..79 zero
   for (int i = t; i < 80 * 8; i += kTcThreads) {
     const int row = i >> 3, ch = i & 7;
@@ -525,7 +531,7 @@ int dcgan_c3_fprop_tc(const void* x, const float* w, const float* bias, void* ou
   const int tiles = N * oH * oW / 128;
   const int cap_f = g_c3_blocks_fprop > 0 ? g_c3_blocks_fprop : 148 * 3;
   dim3 grid(tiles < cap_f ? tiles : cap_f, C / 64);
-  c3_fprop_tc_kernel<<<grid, kTcThreads, kTcSmem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), w, bias,
+  launch_k(c3_fprop_tc_kernel, dim3(grid), dim3(kTcThreads), kTcSmem, st, reinterpret_cast<const __nv_bfloat16*>(x), w, bias,
                                                         reinterpret_cast<__nv_bfloat16*>(out), N, H, W, C, act, err);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
@@ -544,7 +550,7 @@ int dcgan_c3_tconv_tc(const void* x, const void* w_bf16, const float* bias, cons
   if (!err) return DCGAN_ERR_DRIVER;
   const int tiles = N * (H / kTH2) * (W / kTW2);
   dim3 grid(tiles < 296 ? tiles : 296);
-  c3_tconv_tc_kernel<<<grid, kTcThreads, kTconvTcSmem, st>>>(
+  launch_k(c3_tconv_tc_kernel, dim3(grid), dim3(kTcThreads), kTconvTcSmem, st, 
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(w_bf16), bias,
       reinterpret_cast<const __nv_bfloat16*>(aux), reinterpret_cast<__nv_bfloat16*>(out), colsum, N, H, W, act, mode,
       err);
@@ -564,7 +570,7 @@ int dcgan_c3_wgrad_tc(const void* x3, const void* y, float* dw, int N, int Hs, i
   const int tiles = N * Hs * Ws / 128;
   const int cap_w = g_c3_blocks_wgrad > 0 ? g_c3_blocks_wgrad : 148;  // few CTAs: the final f32 atomics contend per address
   dim3 grid(tiles < cap_w ? tiles : cap_w, C / 64);
-  c3_wgrad_tc_kernel<<<grid, kTcThreads, kTcSmem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x3),
+  launch_k(c3_wgrad_tc_kernel, dim3(grid), dim3(kTcThreads), kTcSmem, st, reinterpret_cast<const __nv_bfloat16*>(x3),
                                                         reinterpret_cast<const __nv_bfloat16*>(y), dw, N, Hs, Ws, C, err);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }

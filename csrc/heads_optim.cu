@@ -17,6 +17,8 @@ constexpr int kLinTile = 16;
 __global__ void __launch_bounds__(128)
 lin_fwd_kernel(const float* __restrict__ z, const __nv_bfloat16* __restrict__ W, const float* __restrict__ bias,
                __nv_bfloat16* __restrict__ out, int NB, int K, int F) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float zs[];  // [kLinTile][K]
   const int n0 = blockIdx.y * kLinTile;
   for (int i = threadIdx.x; i < kLinTile * K; i += 128) {
@@ -53,6 +55,8 @@ lin_fwd_kernel(const float* __restrict__ z, const __nv_bfloat16* __restrict__ W,
 __global__ void __launch_bounds__(128)
 lin_wgrad_kernel(const float* __restrict__ z, const __nv_bfloat16* __restrict__ dy, float* __restrict__ dW,
                  float* __restrict__ dbias, int NB, int K, int F) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float zs[];  // [NB][kt]
   const int kt = 20;             // rows of dW per block (K = 100 -> 5 blocks in y)
   const int k0 = blockIdx.y * kt;
@@ -94,6 +98,8 @@ lin_wgrad_kernel(const float* __restrict__ z, const __nv_bfloat16* __restrict__ 
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ w, const float* __restrict__ b,
                 float* __restrict__ logits, int F) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float part[8];
   const int n = blockIdx.x;
   float acc = 0.f;
@@ -133,6 +139,8 @@ __global__ void __launch_bounds__(256)
 gan_loss_kernel(const float* __restrict__ logits, float* __restrict__ losses, float* __restrict__ dlogit,
                 float* __restrict__ probs, long long* __restrict__ counters, int B, float grad_div,
                 int advance) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[3][8];
   float l0 = 0.f, l1 = 0.f, l2 = 0.f;
   const float scale = 1.f / ((float)B * grad_div);
@@ -172,6 +180,8 @@ __global__ void __launch_bounds__(128)
 head_bwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ w,
                 const float* __restrict__ dlogit, __nv_bfloat16* __restrict__ dh, float* __restrict__ dW,
                 float* __restrict__ db, int B, int F) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int k8 = blockIdx.x * 128 + threadIdx.x;
   const int n0 = blockIdx.y * kHeadBwdChunk;
   if (k8 * 8 >= F) return;
@@ -225,6 +235,8 @@ __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
             __nv_bfloat16* __restrict__ p_bf16, const long long* __restrict__ counters, size_t n, float lr,
             float b1, float b2, float eps, float gscale) {
+  pdl_launch_dependents();
+  pdl_wait();
   const float t = (float)counters[0];
   const float lr_t = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
   const size_t i4 = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4;
@@ -321,6 +333,8 @@ decode_f64_kernel(const double* __restrict__ src, __nv_bfloat16* __restrict__ ds
 __global__ void __launch_bounds__(256)
 f32_to_bf16_affine_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n, float scale,
                           float shift) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256)
     dst[i] = __float2bfloat16(src[i] * scale + shift);
 }
@@ -362,7 +376,7 @@ extern "C" {
 int dcgan_lin_fwd(const float* z, const void* W, const float* bias, void* out, int NB, int K, int F,
                   cudaStream_t st) {
   dim3 grid((F + 127) / 128, (NB + kLinTile - 1) / kLinTile);
-  lin_fwd_kernel<<<grid, 128, kLinTile * K * sizeof(float), st>>>(z, reinterpret_cast<const __nv_bfloat16*>(W),
+  launch_k(lin_fwd_kernel, dim3(grid), dim3(128), kLinTile * K * sizeof(float), st, z, reinterpret_cast<const __nv_bfloat16*>(W),
                                                                   bias, reinterpret_cast<__nv_bfloat16*>(out), NB,
                                                                   K, F);
   return LAUNCH_OK();
@@ -372,7 +386,7 @@ int dcgan_lin_wgrad(const float* z, const void* dy, float* dW, float* dbias, int
                     cudaStream_t st) {
   if ((size_t)NB * 20 * sizeof(float) > 48 * 1024) return DCGAN_ERR_SHAPE;
   dim3 grid((F + 127) / 128, (K + 19) / 20);
-  lin_wgrad_kernel<<<grid, 128, NB * 20 * sizeof(float), st>>>(z, reinterpret_cast<const __nv_bfloat16*>(dy), dW,
+  launch_k(lin_wgrad_kernel, dim3(grid), dim3(128), NB * 20 * sizeof(float), st, z, reinterpret_cast<const __nv_bfloat16*>(dy), dW,
                                                                dbias, NB, K, F);
   return LAUNCH_OK();
 }
@@ -380,13 +394,13 @@ int dcgan_lin_wgrad(const float* z, const void* dy, float* dW, float* dbias, int
 int dcgan_head_fwd(const void* h, const float* w, const float* b, float* logits, int rows, int F,
                    cudaStream_t st) {
   if (F % 8) return DCGAN_ERR_SHAPE;
-  head_fwd_kernel<<<rows, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(h), w, b, logits, F);
+  launch_k(head_fwd_kernel, dim3(rows), dim3(256), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w, b, logits, F);
   return LAUNCH_OK();
 }
 
 int dcgan_gan_loss(const float* logits, float* losses, float* dlogit, float* probs, long long* counters, int B,
                    float grad_div, int advance, cudaStream_t st) {
-  gan_loss_kernel<<<1, 256, 0, st>>>(logits, losses, dlogit, probs, counters, B, grad_div, advance);
+  launch_k(gan_loss_kernel, dim3(1), dim3(256), 0, st, logits, losses, dlogit, probs, counters, B, grad_div, advance);
   return LAUNCH_OK();
 }
 
@@ -395,7 +409,7 @@ int dcgan_head_bwd(const void* h, const float* w, const float* dlogit, void* dh,
   if (F % 8) return DCGAN_ERR_SHAPE;
   const int threads_needed = F / 8;
   dim3 grid((threads_needed + 127) / 128, (3 * B + kHeadBwdChunk - 1) / kHeadBwdChunk);
-  head_bwd_kernel<<<grid, 128, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(h), w,
+  launch_k(head_bwd_kernel, dim3(grid), dim3(128), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w,
                                                                  dlogit, reinterpret_cast<__nv_bfloat16*>(dh), dW,
                                                                  db, B, F);
   return LAUNCH_OK();
@@ -405,7 +419,7 @@ int dcgan_adam(float* p, const float* g, float* m, float* v, void* p_bf16, const
                float lr, float b1, float b2, float eps, float gscale, cudaStream_t st) {
   if (n == 0) return 0;
   const size_t blocks = (n + 1023) / 1024;
-  adam_kernel<<<(unsigned)blocks, 256, 0, st>>>(p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16), counters, n,
+  launch_k(adam_kernel, dim3((unsigned)blocks), dim3(256), 0, st, p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16), counters, n,
                                                lr, b1, b2, eps, gscale);
   return LAUNCH_OK();
 }
@@ -446,7 +460,7 @@ int dcgan_decode_f64(const double* src, void* dst, size_t n, float scale, float 
 int dcgan_f32_to_bf16(const float* src, void* dst, size_t n, float scale, float shift, cudaStream_t st) {
   size_t blocks = (n + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  f32_to_bf16_affine_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), n, scale,
+  launch_k(f32_to_bf16_affine_kernel, dim3((unsigned)blocks), dim3(256), 0, st, src, reinterpret_cast<__nv_bfloat16*>(dst), n, scale,
                                                               shift);
   return LAUNCH_OK();
 }

@@ -95,6 +95,7 @@ __global__ void __launch_bounds__(kNumThreads, (SmemLayout<BLOCK_N, STAGES>::kTo
                                               : (SmemLayout<BLOCK_N, STAGES>::kTotal <= 110 * 1024) ? 2
                                                                                                     : 1)
 igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
+  pdl_launch_dependents();
   using L = SmemLayout<BLOCK_N, STAGES>;
   constexpr int kGatherDepth = (STAGES >= 8) ? 6 : ((STAGES - 1 < 3) ? STAGES - 1 : 3);
   extern __shared__ uint8_t smem_raw[];
@@ -144,6 +145,7 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_wait();  // everything above overlapped the previous kernel's tail; global memory is touched from here on
 
   if (warp == 0) {
     // =================================== TMA producer ==========================================
@@ -430,6 +432,7 @@ template <int BLOCK_N, int A_STAGES, int B_SLOTS>
 __global__ void __launch_bounds__(kNumThreads, (SmemLayoutT4<BLOCK_N, A_STAGES, B_SLOTS>::kTotal <= 110 * 1024 &&
                                                 BLOCK_N <= 64) ? 2 : 1)
 igemm_t4_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
+  pdl_launch_dependents();
   using L = SmemLayoutT4<BLOCK_N, A_STAGES, B_SLOTS>;
   constexpr int kGatherDepth = (A_STAGES - 1 < 3) ? A_STAGES - 1 : 3;
   extern __shared__ uint8_t smem_raw[];
@@ -461,6 +464,7 @@ igemm_t4_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_wait();  // everything above overlapped the previous kernel's tail; global memory is touched from here on
 
   if (warp == 0) {
     // ============================ TMA producer: filter tiles =======================================
@@ -697,7 +701,7 @@ static int launch(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cuda
       return DCGAN_ERR_LAUNCH;
     attr_done = true;
   }
-  kern<<<grid, kNumThreads, L::kTotal, stream>>>(tmap, p);
+  launch_k(kern, dim3(grid), dim3(kNumThreads), L::kTotal, stream, tmap, p);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 
@@ -728,7 +732,7 @@ static int launch_t4(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, c
       return DCGAN_ERR_LAUNCH;
     attr_done = true;
   }
-  kern<<<grid, kNumThreads, L::kTotal, stream>>>(tmap, p);
+  launch_k(kern, dim3(grid), dim3(kNumThreads), L::kTotal, stream, tmap, p);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 

@@ -1,5 +1,6 @@
 // Library-wide runtime state: the sticky device error flag that bounded waits set instead of
 // hanging, and its host accessors.  No counterpart in the reference (its runtime is TensorFlow's).
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include "common.cuh"
 #include "../include/dcgan_b200.h"
@@ -23,6 +24,8 @@ int* error_flag_ptr() {
   return ptrs[dev];
 }
 
+void set_pdl(int v);
+
 int* mn_variant_ptr() {
   static int* ptrs[kMaxDevices] = {nullptr};
   int dev = 0;
@@ -35,9 +38,22 @@ int* mn_variant_ptr() {
   return ptrs[dev];
 }
 
+static int g_use_pdl = -1;
+bool use_pdl() {
+  if (g_use_pdl < 0) {
+    const char* e = getenv("DCGAN_PDL");
+    g_use_pdl = (e != nullptr && e[0] == '1') ? 1 : 0;  // measured: 0.979 ms with, 0.948 ms without -> off by default
+  }
+  return g_use_pdl != 0;
+}
+void set_pdl(int v) { g_use_pdl = v ? 1 : 0; }
+
 }  // namespace dcgan
 
 extern "C" {
+
+void dcgan_set_pdl(int v) { dcgan::set_pdl(v); }
+
 
 int dcgan_last_device_error(void) {
   int v = 0;

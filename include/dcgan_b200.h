@@ -37,6 +37,11 @@ int dcgan_last_device_error(void);
 /* Bring-up switch for the MN-major UMMA descriptor convention (0 = CuTe convention). */
 void dcgan_set_mn_desc_variant(int v);
 
+/* Programmatic dependent launch of the hot-path kernels (each kernel's set-up overlaps the tail of its
+ * predecessor).  Off by default -- on this step it measured 3 % slower (the early CTAs take SM slots from the
+ * side-stream filter-gradient kernels); DCGAN_PDL=1 in the environment or this call turns it on. */
+void dcgan_set_pdl(int v);
+
 /* Profiling switch for the implicit-GEMM kernels: bit 0 = two CTAs per SM (default on). */
 void dcgan_set_igemm_tuning(int v);
 
