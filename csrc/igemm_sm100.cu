@@ -52,6 +52,8 @@ struct IgemmParams {
                            // pre-activation output -- the batch-norm moments (distriubted_model.py:37)
   int stat_group_rows;     // rows per statistics group (multiple of 128)
   int b_mn;                // F/T: weights are [25][Ck][Cn] (Cn contiguous) -> MN-major B operand
+  int ksplit;              // F/T: CTAs of one thread-block cluster that share an output tile, each taking a
+                           // slice of K; partial accumulators meet in the leader's shared memory (DSMEM)
   int* err_flag;           // sticky device error flag (csrc/runtime.cu)
   const int* mn_variant;   // MN-major descriptor convention switch (bring-up harness only)
 };
@@ -87,6 +89,27 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// thread-block cluster helpers (split-K over distributed shared memory)
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t cta_rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta_rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d)
+               : "memory");
+}
+// every thread of every CTA in the cluster takes part (non-.aligned forms: callers may be diverged)
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
+}
+
 // k-blocks whose gather copies are in flight per producer thread before the oldest is published
 // (kGatherDepth is min(3, STAGES - 1), a kernel-local constant)
 
@@ -120,11 +143,17 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
     n0 = (blockIdx.y % n_tiles) * BLOCK_N;   // gathered channel tile
     kb_base = blockIdx.z * p.num_kb;
   } else {
-    m0 = blockIdx.x * kBlockM;  // pixel tile
-    n0 = blockIdx.y * BLOCK_N;  // out channel tile
+    m0 = (blockIdx.x / p.ksplit) * kBlockM;  // pixel tile (the ksplit CTAs of a cluster are consecutive in x)
+    n0 = blockIdx.y * BLOCK_N;               // out channel tile
     if (MODE == MODE_T) { ph = blockIdx.z >> 1; pw = blockIdx.z & 1; }
   }
-  const int num_kb = (MODE == MODE_T) ? ((ph ? 3 : 2) * (pw ? 3 : 2) * (p.gC / kBlockK)) : p.num_kb;
+  const int ksplit = (MODE == MODE_W) ? 1 : p.ksplit;
+  const int krank = (ksplit > 1) ? (int)cluster_ctarank() : 0;
+  int num_kb = (MODE == MODE_T) ? ((ph ? 3 : 2) * (pw ? 3 : 2) * (p.gC / kBlockK)) : p.num_kb;
+  if (MODE != MODE_W && ksplit > 1) {  // this CTA's slice of K (the host guarantees num_kb >= ksplit)
+    kb_base = (krank * num_kb) / ksplit;
+    num_kb = ((krank + 1) * num_kb) / ksplit - kb_base;
+  }
 
   // ---- one-time setup -------------------------------------------------------------------------
   if (tid == 0) {
@@ -165,8 +194,8 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
           tma_load_2d(sA + kATileBytes / 2, &tmap, &full_bar[s], m0 + 64, px0);
         } else {
           int tap;
-          const int lt = kb / cpt;
-          const int c0 = (kb - lt * cpt) * kBlockK;
+          const int lt = (kb_base + kb) / cpt;
+          const int c0 = (kb_base + kb - lt * cpt) * kBlockK;
           if (MODE == MODE_F) {
             tap = lt;
           } else {
@@ -218,7 +247,13 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
       }
       umma_commit(tmem_full_bar);  // accumulator complete
     }
-  } else {
+  }
+  if (MODE != MODE_W && ksplit > 1 && warp < 2) {  // the two cluster barriers of the split-K reduction (below)
+    __syncwarp();
+    cluster_sync_all();
+    cluster_sync_all();
+  }
+  if (warp >= 2) {
     // ============================ gather producers, then epilogue ==============================
     const int gt = tid - 64;       // 0..127
     const int chunk = gt & 7;      // 16-byte chunk inside the 128-byte row
@@ -254,8 +289,8 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
           const int kb = it;
           const int s = kb % STAGES;
           const uint32_t phase = (kb / STAGES) & 1;
-          const int lt = kb / cpt;
-          const int c0 = (kb - lt * cpt) * kBlockK;
+          const int lt = (kb_base + kb) / cpt;
+          const int c0 = (kb_base + kb - lt * cpt) * kBlockK;
           int dy, dx;
           if (MODE == MODE_F) {
             const int kh = lt / 5, kw = lt - kh * 5;
@@ -335,7 +370,31 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
     const int row_in_tile = q * 32 + lane;
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-    if (MODE != MODE_W) {
+    // Split-K across the cluster: once every CTA's ring is idle (barrier 1) the non-leaders store their f32
+    // partial tiles into the leader's ring through distributed shared memory, [col/4][row][4] so that a
+    // warp's 16-byte stores are contiguous; after barrier 2 the leader adds them in its epilogue.
+    constexpr int kPartialBytes = kBlockM * BLOCK_N * 4;
+    bool leader = true;
+    if (MODE != MODE_W && ksplit > 1) {
+      cluster_sync_all();
+      if (krank != 0) {
+        leader = false;
+        const uint32_t dst = mapa_shared(smem_u32(smem) + (uint32_t)(krank - 1) * kPartialBytes, 0) +
+                             (uint32_t)row_in_tile * 16u;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            st_cluster_v4(dst + (uint32_t)((c >> 2) + j) * (kBlockM * 16u), v[4 * j], v[4 * j + 1], v[4 * j + 2],
+                          v[4 * j + 3]);
+        }
+      }
+      cluster_sync_all();
+    }
+    if (MODE != MODE_W && leader) {
       const int R = m0 + row_in_tile;
       const bool valid = ok && R < p.rows_total;
       __nv_bfloat16* orow = nullptr;
@@ -352,6 +411,18 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
         uint32_t v[32];
         tmem_ld_32x32(taddr + c, v);
         tmem_ld_wait();
+        for (int r = 1; r < ksplit; ++r) {
+          const float4* part = reinterpret_cast<const float4*>(smem + (size_t)(r - 1) * kPartialBytes) +
+                               (size_t)(c >> 2) * kBlockM + row_in_tile;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 t = part[(size_t)j * kBlockM];
+            v[4 * j] = __float_as_uint(__uint_as_float(v[4 * j]) + t.x);
+            v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + t.y);
+            v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + t.z);
+            v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + t.w);
+          }
+        }
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
@@ -387,7 +458,7 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
           atomicAdd(gs + p.Cn + i, stat_smem[BLOCK_N + i]);
         }
       }
-    } else {
+    } else if (MODE == MODE_W) {
       float* obase = reinterpret_cast<float*>(p.out) + (size_t)tap_fixed * p.Cn * p.Cd + (m0 + row_in_tile);
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N; c += 32) {
@@ -701,12 +772,51 @@ static int launch(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cuda
       return DCGAN_ERR_LAUNCH;
     attr_done = true;
   }
+  if (MODE != MODE_W && p.ksplit > 1) {
+    // split-K: the ksplit CTAs that share an output tile form one thread-block cluster along x
+    if ((size_t)(p.ksplit - 1) * kBlockM * BLOCK_N * 4 > (size_t)STAGES * L::kStageBytes) return DCGAN_ERR_SHAPE;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kNumThreads);
+    cfg.dynamicSmemBytes = L::kTotal;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = p.ksplit;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, tmap, p) == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+  }
   launch_k(kern, dim3(grid), dim3(kNumThreads), L::kTotal, stream, tmap, p);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 
 // tuning knob (bring-up / profiling): bit 0 = two CTAs per SM with shallower stage rings
 static int g_igemm_tuning = 1;  // bit 3 (8): parity-fused transposed conv for large-M layers; bit 4: its N=128 tile
+                                // bit 5 (32): no cluster split-K
+static int g_igemm_ksplit = 0;  // 0 = choose per layer; 1, 2, 4 = forced (tests / profiling)
+
+// Split-K factor for an F/T launch of `ctas` tiles whose shortest K loop has `min_kb` k-blocks: small-M
+// layers leave most of the 148 SMs idle while each CTA walks a long serial K loop, so K is cut across a
+// cluster until the resident-CTA slots are filled.  The partial tiles must fit in the leader's stage ring.
+// Measured (profiles/igemm_splitk_r1.log): splitting pays while every CTA keeps >= `min_kb_per_cta` k-blocks
+// (16 for the strided mode, 8 for the shortest parity class of the transposed mode).
+static int pick_ksplit(long ctas, int min_kb, int min_kb_per_cta, int block_n) {
+  if (g_igemm_ksplit > 0) return (min_kb >= g_igemm_ksplit) ? g_igemm_ksplit : 1;
+  if (block_n > 128) return 1;
+  if (g_igemm_tuning & (32 | 4 | 2)) return 1;  // off, or a non-default stage ring is being profiled
+  const bool occ2 = (g_igemm_tuning & 1) != 0 && block_n <= 128;
+  const long slots = 148L * (occ2 ? 2 : 1);
+  const int stages = (block_n == 64) ? (occ2 ? 4 : 6) : (block_n == 128 ? (occ2 ? 3 : 5) : 4);
+  const long ring = (long)stages * (kATileBytes + block_n * kBlockK * 2);
+  int ks = 1;
+  while (ks < 4 && ctas * ks * 2 <= slots && min_kb / (ks * 2) >= min_kb_per_cta &&
+         (long)(ks * 2 - 1) * kBlockM * block_n * 4 <= ring)
+    ks *= 2;
+  return ks;
+}
 
 template <int MODE>
 static int dispatch_n(int block_n, const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cudaStream_t st) {
@@ -736,14 +846,16 @@ static int launch_t4(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, c
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 
-static int pick_block_n(int Cn, int rows_tiles, int extra_parallel) {
+static int pick_block_n(int Cn, int rows_tiles, int extra_parallel, int min_kb, int min_kb_per_cta) {
   // the kernels are bound by L2 traffic of the im2col gather, so prefer the widest tile (fewest re-reads
-  // of the gathered operand) that still occupies most of the 148 SMs (measured: profiles/igemm_*.log)
+  // of the gathered operand) that, together with its split-K factor, still occupies most of the 148 SMs
+  // (measured: profiles/igemm_*.log)
   const int cands[3] = {256, 128, 64};
   for (int i = 0; i < 3; ++i) {
     const int bn = cands[i];
     if (Cn % bn) continue;
-    if ((long)rows_tiles * (Cn / bn) * extra_parallel >= 90 || bn == 64) return bn;
+    const long ctas = (long)rows_tiles * (Cn / bn) * extra_parallel;
+    if (ctas * pick_ksplit(ctas, min_kb, min_kb_per_cta, bn) >= 90 || bn == 64) return bn;
   }
   return (Cn % 64 == 0) ? 64 : -1;
 }
@@ -755,6 +867,7 @@ using namespace dcgan;
 extern "C" {
 
 void dcgan_set_igemm_tuning(int v) { g_igemm_tuning = v; }
+void dcgan_set_igemm_ksplit(int v) { g_igemm_ksplit = (v == 1 || v == 2 || v == 4) ? v : 0; }
 
 static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                            int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream,
@@ -781,13 +894,14 @@ static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, v
   }
   p.out = out; p.bias = bias; p.act = act; p.oH = oH; p.oW = oW;
   const int mt = (p.rows_total + kBlockM - 1) / kBlockM;
-  if (block_n <= 0) block_n = pick_block_n(Cout, mt, 1);
+  if (block_n <= 0) block_n = pick_block_n(Cout, mt, 1, p.num_kb, 16);
   if (block_n < 0 || Cout % block_n) return DCGAN_ERR_SHAPE;
   CUtensorMap tmap;
   int rc = b_mn ? get_tmap_2d(w_nk, (uint64_t)25 * Cin, Cout, 64, 64, &tmap)
                 : get_tmap_2d(w_nk, (uint64_t)25 * Cout, Cin, block_n, 64, &tmap);
   if (rc) return rc;
-  dim3 grid(mt, Cout / block_n, 1);
+  p.ksplit = pick_ksplit((long)mt * (Cout / block_n), p.num_kb, 16, block_n);
+  dim3 grid(mt * p.ksplit, Cout / block_n, 1);
   return dispatch_n<MODE_F>(block_n, tmap, p, grid, stream);
 }
 
@@ -823,6 +937,7 @@ static int conv_tconv_impl(const void* x, const void* w_nk, const float* bias, v
   p.rows_total = NB * H * W;
   p.Cn = Cout; p.Cd = 0;
   p.num_kb = 0;  // per parity class, derived in-kernel
+  p.ksplit = 1;
   if (stats != nullptr) {
     if (stat_groups < 1 || p.rows_total % stat_groups || (p.rows_total / stat_groups) % kBlockM) return DCGAN_ERR_SHAPE;
     p.stats = stats;
@@ -842,12 +957,13 @@ static int conv_tconv_impl(const void* x, const void* w_nk, const float* bias, v
     return bn == 64 ? launch_t4<64, 3, 6>(tmap4, p, grid4, stream) : launch_t4<128, 3, 6>(tmap4, p, grid4, stream);
   }
   if (block_n < 0) block_n = 0;
-  if (block_n <= 0) block_n = pick_block_n(Cout, mt, 4);
+  if (block_n <= 0) block_n = pick_block_n(Cout, mt, 4, 4 * (Cin / 64), 8);
   if (block_n < 0 || Cout % block_n) return DCGAN_ERR_SHAPE;
   CUtensorMap tmap;
   int rc = get_tmap_2d(w_nk, (uint64_t)25 * Cout, Cin, block_n, 64, &tmap);
   if (rc) return rc;
-  dim3 grid(mt, Cout / block_n, 4);
+  p.ksplit = pick_ksplit((long)mt * (Cout / block_n) * 4, 4 * (Cin / 64), 8, block_n);
+  dim3 grid(mt * p.ksplit, Cout / block_n, 4);
   return dispatch_n<MODE_T>(block_n, tmap, p, grid, stream);
 }
 

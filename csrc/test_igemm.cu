@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -194,6 +195,35 @@ static void bench_layers() {
   }
 }
 
+// cluster split-K (DSMEM reduction) on the small-M layers: forced factors vs the per-layer choice (0)
+static void bench_splitk() {
+  struct Layer { const char* name; int tconv, NB, H, Cin, Cout; };
+  Layer ls[] = {{"g_h1 dgrad (F)", 0, 64, 8, 256, 512},  {"g_h2 dgrad (F)", 0, 64, 16, 128, 256},
+                {"g_h3 dgrad (F)", 0, 64, 32, 64, 128},  {"d_h3 fprop (F)", 0, 128, 8, 256, 512},
+                {"d_h2 fprop (F)", 0, 128, 16, 128, 256}, {"d_h1 fprop (F)", 0, 128, 32, 64, 128},
+                {"g_h1 tconv (T)", 1, 64, 4, 512, 256},  {"g_h2 tconv (T)", 1, 64, 8, 256, 128},
+                {"d_h3 dgrad (T)", 1, 192, 4, 512, 256}, {"d_h2 dgrad (T)", 1, 192, 8, 256, 128}};
+  for (auto& l : ls) {
+    Buf x, w; x.init((size_t)l.NB * l.H * l.H * l.Cin, 1.f); w.init((size_t)25 * l.Cout * l.Cin, 0.05f);
+    const size_t on = l.tconv ? (size_t)l.NB * l.H * l.H * 4 * l.Cout : (size_t)l.NB * l.H * l.H / 4 * l.Cout;
+    __nv_bfloat16* o; CK(cudaMalloc(&o, on * 2));
+    for (int bn : {0, 64, 128}) {
+      if (bn && l.Cout % bn) continue;
+      for (int ks : {1, 2, 4, 0}) {
+        dcgan_set_igemm_ksplit(ks);
+        int rc = 0;
+        float ms = time_ms([&] {
+          rc |= l.tconv ? dcgan_conv_tconv(x.d, w.d, nullptr, o, l.NB, l.H, l.H, l.Cin, l.Cout, 0, bn, 0)
+                        : dcgan_conv_fprop(x.d, w.d, nullptr, o, l.NB, l.H, l.H, l.Cin, l.Cout, 0, bn, 0);
+        }, 20);
+        printf("[SPLITK] %s bn=%d ksplit=%d rc=%d %.1f us err=%d\n", l.name, bn, ks, rc, ms * 1e3, dcgan_last_device_error());
+      }
+    }
+    dcgan_set_igemm_ksplit(0);
+    x.free(); w.free(); cudaFree(o);
+  }
+}
+
 int main(int argc, char** argv) {
   int fails = 0;
   cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, 0));
@@ -212,6 +242,19 @@ int main(int argc, char** argv) {
   dcgan_set_igemm_tuning(1 | 8 | 16);
   fails += test_tconv(48, 16, 16, 64, 128, 0);    // N=128 tile, 512 TMEM columns
   dcgan_set_igemm_tuning(1);
+  // split-K across a thread-block cluster, partial tiles reduced through distributed shared memory
+  for (int ks : {2, 4}) {
+    dcgan_set_igemm_ksplit(ks);
+    fails += test_fprop(2, 16, 16, 64, 64, 64);
+    fails += test_fprop(1, 4, 8, 128, 64, 64);    // partial M tile
+    fails += test_tconv(2, 8, 8, 64, 64, 64);
+    if (ks == 2) {
+      fails += test_fprop(2, 16, 16, 128, 128, 128);
+      fails += test_tconv(2, 4, 4, 128, 128, 128);
+      fails += test_fprop(3, 8, 8, 64, 256, 256);
+    }
+  }
+  dcgan_set_igemm_ksplit(0);
   int w0 = test_wgrad(2, 8, 8, 64, 128, 1, 64, 0);
   int w1 = 0;
   if (w0) { w1 = test_wgrad(2, 8, 8, 64, 128, 1, 64, 1); printf("MN-major variant 1 %s\n", w1 ? "also fails" : "passes"); }
@@ -220,6 +263,7 @@ int main(int argc, char** argv) {
   fails += test_wgrad(4, 4, 4, 256, 256, 1, 256, 0);
   fails += test_wgrad(4, 8, 8, 128, 256, 0, 0, 0);
   printf("correctness: %d failing tests\n", fails);
+  if (argc >= 2 && !strcmp(argv[1], "splitk")) bench_splitk();
   if (argc < 2) {
     for (int tune : {1, 9, 25}) {
       printf("=== igemm tuning %d ===\n", tune);

@@ -84,6 +84,14 @@ def load() -> ctypes.CDLL:
     lib.dcgan_last_device_error.restype = c_int
     lib.dcgan_set_mn_desc_variant.argtypes = [c_int]
     lib.dcgan_set_mn_desc_variant.restype = None
+    for setter in ("dcgan_set_igemm_tuning", "dcgan_set_igemm_ksplit"):
+        getattr(lib, setter).argtypes = [c_int]
+        getattr(lib, setter).restype = None
+    # profiling overrides (A/B runs of bench.py without a rebuild)
+    if os.environ.get("DCGAN_IGEMM_TUNING"):
+        lib.dcgan_set_igemm_tuning(int(os.environ["DCGAN_IGEMM_TUNING"]))
+    if os.environ.get("DCGAN_IGEMM_KSPLIT"):
+        lib.dcgan_set_igemm_ksplit(int(os.environ["DCGAN_IGEMM_KSPLIT"]))
     _lib = lib
     return lib
 

@@ -44,6 +44,10 @@ void dcgan_set_pdl(int v);
 
 /* Profiling switch for the implicit-GEMM kernels: bit 0 = two CTAs per SM (default on). */
 void dcgan_set_igemm_tuning(int v);
+/* Split-K factor of the strided / transposed convs (a thread-block cluster shares one output tile and reduces
+ * its partial accumulators through distributed shared memory): 0 = chosen per layer (default), 1/2/4 = forced.
+ * Tests and profiling only. */
+void dcgan_set_igemm_ksplit(int v);
 
 /* ---- implicit-GEMM convolutions on tcgen05 / TMEM / TMA (csrc/igemm_sm100.cu) ------------------ */
 

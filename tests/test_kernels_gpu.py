@@ -361,3 +361,33 @@ def test_no_out_of_bounds_writes(cuda_lib):
     assert intact(buf, pad)
     torch.cuda.synchronize()
     K.check_device_error()
+
+
+def test_cluster_split_k_matches_single_cta(cuda_lib):
+    """Small-M layers cut K across a thread-block cluster and reduce the partial accumulators through
+    distributed shared memory; the result (and the fused batch-norm moments) must match the one-CTA-per-tile
+    kernel up to f32 summation order."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    x = _rand((16, 8, 8, 256), 0.5)                 # 256 output rows of the strided conv -> 2 M tiles
+    w_kn = _rand((25, 256, 128), 0.05)
+    xt = _rand((16, 4, 4, 256), 0.5)                # transposed conv: 256 rows per parity class
+    w_nk = _rand((25, 128, 256), 0.05)
+    outs = {}
+    try:
+        for ks in (1, 2, 4):
+            cuda_lib.dcgan_set_igemm_ksplit(ks)
+            st = torch.zeros(2, 2, 128, device="cuda")
+            o = torch.empty(16, 4, 4, 128, device="cuda", dtype=torch.bfloat16)
+            K.conv_fprop_kn_stats(x, w_kn, None, o, st, 2, block_n=64)
+            t = K.conv_tconv(xt, w_nk, None, block_n=64)
+            K.check_device_error()
+            outs[ks] = (o.float(), st.clone(), t.float())
+    finally:
+        cuda_lib.dcgan_set_igemm_ksplit(0)
+    for ks in (2, 4):
+        for a, b, name in zip(outs[ks], outs[1], ("fprop", "moments", "tconv")):
+            _close(a, b, rel=1e-2, name=f"split-K {ks} {name}")
+    # and against a plain fp32 PyTorch reference of the strided conv (TF SAME: pad 1 before, 2 after)
+    xp = torch.nn.functional.pad(x.float().permute(0, 3, 1, 2), (1, 2, 1, 2))
+    ref = torch.nn.functional.conv2d(xp, w_kn.float().view(5, 5, 256, 128).permute(3, 2, 0, 1), stride=2)
+    _close(outs[4][0], ref.permute(0, 2, 3, 1), rel=2e-2, name="split-K 4 vs torch conv2d")
