@@ -11,7 +11,8 @@ namespace dcgan {
 
 // ---------------------------------------------------------------------------------------------
 // g_h0_lin forward: out[n, j] = sum_k z[n,k] * W[k,j] + b[j]  -> bf16.  W is the bf16 copy.
-// block = 128 threads = 128 consecutive j; z staged in smem; NB_TILE rows of z per block.
+// block = 128 threads x 2 adjacent j (one 4-byte weight load per k) x kLinTile rows of z; z is staged
+// in smem as [k][kLinTile] so that a k step reads its 16 values with four 16-byte broadcasts.
 // ---------------------------------------------------------------------------------------------
 constexpr int kLinTile = 16;
 __global__ void __launch_bounds__(128)
@@ -19,36 +20,45 @@ lin_fwd_kernel(const float* __restrict__ z, const __nv_bfloat16* __restrict__ W,
                __nv_bfloat16* __restrict__ out, int NB, int K, int F) {
   pdl_launch_dependents();
   pdl_wait();
-  extern __shared__ float zs[];  // [kLinTile][K]
+  extern __shared__ __align__(16) float zs[];  // [K][kLinTile]
   const int n0 = blockIdx.y * kLinTile;
   for (int i = threadIdx.x; i < kLinTile * K; i += 128) {
-    const int n = n0 + i / K;
-    zs[i] = n < NB ? z[(size_t)n * K + (i % K)] : 0.f;
+    const int r = i / K, k = i - r * K;  // consecutive threads read consecutive k of one row
+    zs[k * kLinTile + r] = (n0 + r < NB) ? z[(size_t)(n0 + r) * K + k] : 0.f;
   }
   __syncthreads();
-  const int j = blockIdx.x * 128 + threadIdx.x;
+  const int j = (blockIdx.x * 128 + threadIdx.x) * 2;
   if (j >= F) return;
-  float acc[kLinTile];
-  const float b = bias ? bias[j] : 0.f;
+  float acc[kLinTile][2];
+  const float b0 = bias ? bias[j] : 0.f, b1 = bias ? bias[j + 1] : 0.f;
 #pragma unroll
-  for (int i = 0; i < kLinTile; ++i) acc[i] = b;
+  for (int i = 0; i < kLinTile; ++i) { acc[i][0] = b0; acc[i][1] = b1; }
   constexpr int kBatch = 10;  // weight loads in flight per thread
   for (int k0 = 0; k0 < K; k0 += kBatch) {
-    __nv_bfloat16 wv[kBatch];
+    uint32_t wv[kBatch];
 #pragma unroll
-    for (int u = 0; u < kBatch; ++u) wv[u] = (k0 + u < K) ? W[(size_t)(k0 + u) * F + j] : __float2bfloat16(0.f);
+    for (int u = 0; u < kBatch; ++u)
+      wv[u] = (k0 + u < K) ? *reinterpret_cast<const uint32_t*>(W + (size_t)(k0 + u) * F + j) : 0u;
 #pragma unroll
     for (int u = 0; u < kBatch; ++u) {
       if (k0 + u < K) {
-        const float w = __bfloat162float(wv[u]);
+        const float w0 = __uint_as_float(wv[u] << 16), w1 = __uint_as_float(wv[u] & 0xffff0000u);
+        const float4* zr = reinterpret_cast<const float4*>(zs + (k0 + u) * kLinTile);
 #pragma unroll
-        for (int i = 0; i < kLinTile; ++i) acc[i] += zs[i * K + k0 + u] * w;
+        for (int q = 0; q < kLinTile / 4; ++q) {
+          const float4 zz = zr[q];
+          acc[4 * q][0] += zz.x * w0; acc[4 * q][1] += zz.x * w1;
+          acc[4 * q + 1][0] += zz.y * w0; acc[4 * q + 1][1] += zz.y * w1;
+          acc[4 * q + 2][0] += zz.z * w0; acc[4 * q + 2][1] += zz.z * w1;
+          acc[4 * q + 3][0] += zz.w * w0; acc[4 * q + 3][1] += zz.w * w1;
+        }
       }
     }
   }
 #pragma unroll
   for (int i = 0; i < kLinTile; ++i)
-    if (n0 + i < NB) out[(size_t)(n0 + i) * F + j] = __float2bfloat16(acc[i]);
+    if (n0 + i < NB)
+      *reinterpret_cast<__nv_bfloat162*>(out + (size_t)(n0 + i) * F + j) = __floats2bfloat162_rn(acc[i][0], acc[i][1]);
 }
 
 // g_h0_lin weight gradient: dW[k, j] = sum_n z[n,k] * dy[n,j]  (f32, overwrites).
@@ -375,7 +385,8 @@ extern "C" {
 
 int dcgan_lin_fwd(const float* z, const void* W, const float* bias, void* out, int NB, int K, int F,
                   cudaStream_t st) {
-  dim3 grid((F + 127) / 128, (NB + kLinTile - 1) / kLinTile);
+  if (F % 2) return DCGAN_ERR_SHAPE;
+  dim3 grid((F / 2 + 127) / 128, (NB + kLinTile - 1) / kLinTile);
   launch_k(lin_fwd_kernel, dim3(grid), dim3(128), kLinTile * K * sizeof(float), st, z, reinterpret_cast<const __nv_bfloat16*>(W),
                                                                   bias, reinterpret_cast<__nv_bfloat16*>(out), NB,
                                                                   K, F);

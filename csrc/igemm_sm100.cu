@@ -52,6 +52,7 @@ struct IgemmParams {
                            // pre-activation output -- the batch-norm moments (distriubted_model.py:37)
   int stat_group_rows;     // rows per statistics group (multiple of 128)
   int b_mn;                // F/T: weights are [25][Ck][Cn] (Cn contiguous) -> MN-major B operand
+  int t_long_first;        // T: schedule the parity classes with the longest K loop first
   int ksplit;              // F/T: CTAs of one thread-block cluster that share an output tile, each taking a
                            // slice of K; partial accumulators meet in the leader's shared memory (DSMEM)
   int* err_flag;           // sticky device error flag (csrc/runtime.cu)
@@ -145,7 +146,11 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
   } else {
     m0 = (blockIdx.x / p.ksplit) * kBlockM;  // pixel tile (the ksplit CTAs of a cluster are consecutive in x)
     n0 = blockIdx.y * BLOCK_N;               // out channel tile
-    if (MODE == MODE_T) { ph = blockIdx.z >> 1; pw = blockIdx.z & 1; }
+    // longest K loops first (z = 0 is the 3x3-tap class, z = 3 the 2x2 one) so the last wave is made of short CTAs
+    if (MODE == MODE_T) {
+      ph = blockIdx.z >> 1; pw = blockIdx.z & 1;
+      if (p.t_long_first) { ph = 1 - ph; pw = 1 - pw; }
+    }
   }
   const int ksplit = (MODE == MODE_W) ? 1 : p.ksplit;
   const int krank = (ksplit > 1) ? (int)cluster_ctarank() : 0;
@@ -795,7 +800,8 @@ static int launch(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cuda
 
 // tuning knob (bring-up / profiling): bit 0 = two CTAs per SM with shallower stage rings
 static int g_igemm_tuning = 1;  // bit 3 (8): parity-fused transposed conv for large-M layers; bit 4: its N=128 tile
-                                // bit 5 (32): no cluster split-K
+                                // bit 5 (32): no cluster split-K; bit 6 (64): transposed conv parity classes in
+                                // natural order instead of longest-first
 static int g_igemm_ksplit = 0;  // 0 = choose per layer; 1, 2, 4 = forced (tests / profiling)
 
 // Split-K factor for an F/T launch of `ctas` tiles whose shortest K loop has `min_kb` k-blocks: small-M
@@ -938,6 +944,7 @@ static int conv_tconv_impl(const void* x, const void* w_nk, const float* bias, v
   p.Cn = Cout; p.Cd = 0;
   p.num_kb = 0;  // per parity class, derived in-kernel
   p.ksplit = 1;
+  p.t_long_first = (g_igemm_tuning & 64) ? 0 : 1;
   if (stats != nullptr) {
     if (stat_groups < 1 || p.rows_total % stat_groups || (p.rows_total / stat_groups) % kBlockM) return DCGAN_ERR_SHAPE;
     p.stats = stats;
