@@ -21,6 +21,7 @@ from __future__ import annotations
 
 import contextlib
 import os
+import types
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -442,15 +443,72 @@ class DCGANEngine:
         else:
             self.step_body()
 
+    # -- pipelined public API ---------------------------------------------------------------------------
+    # The reference feeds its step from an asynchronous input queue (tf.train.shuffle_batch,
+    # image_input.py:41-46) and fetches the losses with the same sess.run (image_train.py:156-158).  Here the
+    # host->device copy of a step's inputs runs on a copy stream into one of two staging slots while the
+    # previous step computes, and the fetches land in pinned host slots: ``submit`` never blocks the host,
+    # ``result`` waits only for its own step.
+    def _pipe(self):
+        st = getattr(self, "_pipe_state", None)
+        if st is None:
+            st = types.SimpleNamespace()
+            st.copy_stream = torch.cuda.Stream(device=self.real_f32.device)
+            st.stage_real = [torch.empty_like(self.real_f32) for _ in range(2)]
+            st.stage_z = [torch.empty_like(self.z) for _ in range(2)]
+            st.host_loss = [torch.empty(self.losses.numel(), dtype=self.losses.dtype).pin_memory() for _ in range(2)]
+            st.host_cnt = [torch.empty(self.counters.numel(), dtype=self.counters.dtype).pin_memory()
+                           for _ in range(2)]
+            st.ev_in = [torch.cuda.Event() for _ in range(2)]
+            st.ev_consumed = [torch.cuda.Event() for _ in range(2)]
+            st.ev_out = [torch.cuda.Event() for _ in range(2)]
+            st.n = 0
+            self._pipe_state = st
+        return st
+
+    def submit(self, real: torch.Tensor, z: torch.Tensor) -> int:
+        """Enqueue one training step on ``real`` [B,S,S,3] / ``z`` [B,z_dim] (pinned-host, pageable or device
+        tensors) and return a ticket for :meth:`result`.  Nothing here waits for the GPU.  Host inputs must stay
+        untouched until ``result(ticket)`` returns; at most two tickets may be outstanding."""
+        st = self._pipe()
+        slot = st.n & 1
+        main = torch.cuda.current_stream()
+        if real.is_cuda and z.is_cuda:
+            self.real_f32.copy_(real, non_blocking=True)
+            self.z.copy_(z, non_blocking=True)
+        else:
+            with torch.cuda.stream(st.copy_stream):
+                st.copy_stream.wait_event(st.ev_consumed[slot])  # the step that last used this slot has read it
+                st.stage_real[slot].copy_(real, non_blocking=True)
+                st.stage_z[slot].copy_(z, non_blocking=True)
+                st.ev_in[slot].record(st.copy_stream)
+            main.wait_event(st.ev_in[slot])
+            self.real_f32.copy_(st.stage_real[slot], non_blocking=True)
+            self.z.copy_(st.stage_z[slot], non_blocking=True)
+            st.ev_consumed[slot].record(main)
+        self.run_step()
+        st.host_loss[slot].copy_(self.losses, non_blocking=True)
+        st.host_cnt[slot].copy_(self.counters, non_blocking=True)
+        st.ev_out[slot].record(main)
+        st.n += 1
+        return st.n - 1
+
+    def result(self, ticket: int) -> Tuple[float, float, float, int]:
+        """``(d_loss_real, d_loss_fake, g_loss, global_step)`` of a submitted step -- the fetches of
+        ``image_train.py:156-158``."""
+        st = self._pipe()
+        if not (st.n - 2 <= ticket < st.n):
+            raise ValueError(f"ticket {ticket} is no longer held (last submitted: {st.n - 1})")
+        slot = ticket & 1
+        st.ev_out[slot].synchronize()
+        l = st.host_loss[slot]
+        return float(l[0]), float(l[1]), float(l[2]), int(st.host_cnt[slot][1])
+
     def train_step(self, real: torch.Tensor, z: torch.Tensor) -> Tuple[float, float, float, int]:
         """Public single-step API: copies the inputs (pinned host or device tensors), runs the step and
-        reads back ``(d_loss_real, d_loss_fake, g_loss, global_step)`` -- the fetches of
-        ``image_train.py:156-158``."""
-        self.real_f32.copy_(real, non_blocking=True)
-        self.z.copy_(z, non_blocking=True)
-        self.run_step()
-        l = self.losses.tolist()
-        return l[0], l[1], l[2], int(self.counters[1].item())
+        reads back ``(d_loss_real, d_loss_fake, g_loss, global_step)``.  ``submit`` / ``result`` are the same
+        thing split in two so that the next step's input copy overlaps this step's compute."""
+        return self.result(self.submit(real, z))
 
     # ------------------------------------------------------------------------------------------------
     # sampler / state
