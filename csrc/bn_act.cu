@@ -19,6 +19,30 @@ namespace dcgan {
 constexpr int kBnThreads = 256;
 constexpr int kRowBatch = 4;  // rows in flight per thread in the streaming loops
 
+// Column sums of per-thread partials -> global accumulators, without shared-memory atomics: f32 atomicAdd on
+// shared memory compiles to a compare-and-swap loop (ATOMS.CAST.SPIN) and all row-lanes of one channel would
+// spin on the same word (profiles/ncu_step_v3_summary.md: the backward reduce ran at 10 % of DRAM bandwidth).
+// Every row-lane stores its NV x 8 partials in its own slice of `part` ([lanes][NV*C], at most NV * 2048
+// floats because lanes * C <= 8 * kBnThreads); then each thread adds one column over the row-lanes.
+template <int NV>
+__device__ __forceinline__ void block_colsum_to_global(float* part, const float (&v)[NV][8], bool active, int rl,
+                                                       int cv, int lanes, int C, float* __restrict__ out) {
+  if (active) {
+#pragma unroll
+    for (int n = 0; n < NV; ++n) {
+      float4* dst = reinterpret_cast<float4*>(part + (size_t)(rl * NV + n) * C + cv * 8);
+      dst[0] = make_float4(v[n][0], v[n][1], v[n][2], v[n][3]);
+      dst[1] = make_float4(v[n][4], v[n][5], v[n][6], v[n][7]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < NV * C; i += kBnThreads) {
+    float acc = 0.f;
+    for (int l = 0; l < lanes; ++l) acc += part[(size_t)l * NV * C + i];
+    atomicAdd(&out[i], acc);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // forward statistics: sums[g][0][c] += sum x, sums[g][1][c] += sum x^2   (zeroed by the caller)
 // grid = (row_chunks, groups); thread t handles 8 channels (t % (C/8)) of rows t/(C/8)+k*R
@@ -28,15 +52,15 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
                 int rows_per_block) {
   pdl_launch_dependents();
   pdl_wait();
-  extern __shared__ float red[];  // [2][C]
+  __shared__ __align__(16) float part[2 * 8 * kBnThreads];
   const int g = blockIdx.y;
   const int cvec = C >> 3;
   const int lanes = kBnThreads / cvec;  // rows processed in parallel (C <= 2048)
   const int cv = threadIdx.x % cvec;
   const int rl = threadIdx.x / cvec;
-  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) red[i] = 0.f;
-  __syncthreads();
-  float s[8], ss[8];
+  float acc[2][8];
+  float (&s)[8] = acc[0];
+  float (&ss)[8] = acc[1];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
   const int r0 = blockIdx.x * rows_per_block;
@@ -53,15 +77,8 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
         s[2 * j + 1] += f.y; ss[2 * j + 1] += f.y * f.y;
       }
     }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&red[cv * 8 + j], s[j]);
-      atomicAdd(&red[C + cv * 8 + j], ss[j]);
-    }
   }
-  __syncthreads();
-  float* out = sums + (size_t)g * 2 * C;
-  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) atomicAdd(&out[i], red[i]);
+  block_colsum_to_global<2>(part, acc, rl < lanes, rl, cv, lanes, C, sums + (size_t)g * 2 * C);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -154,31 +171,33 @@ __device__ __forceinline__ float act_grad(float y, int act) {
   return 1.f;
 }
 
-__global__ void __launch_bounds__(kBnThreads)
+__global__ void __launch_bounds__(kBnThreads, 2)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ pre,
                      const float* __restrict__ saved, const float* __restrict__ gamma,
                      const float* __restrict__ beta, float* __restrict__ red_out, int rows_per_group, int C,
                      int n_stat_groups, int act, int rows_per_block) {
   pdl_launch_dependents();
   pdl_wait();
-  extern __shared__ float red[];  // [2][C]
+  __shared__ __align__(16) float part[2 * 8 * kBnThreads];
   const int g = blockIdx.y;
   const int sg = min(g, n_stat_groups - 1);
   const int cvec = C >> 3;
   const int lanes = kBnThreads / cvec;
   const int cv = threadIdx.x % cvec;
   const int rl = threadIdx.x / cvec;
-  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) red[i] = 0.f;
-  __syncthreads();
+  float acc[2][8];
+  float (&s1)[8] = acc[0];
+  float (&s2)[8] = acc[1];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s1[j] = 0.f; s2[j] = 0.f; }
   if (rl < lanes) {
-    float mean[8], rstd[8], gm[8], bt[8], s1[8], s2[8];
+    float mean[8], rstd[8], gm[8], bt[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int c = cv * 8 + j;
       mean[j] = saved[((size_t)sg * 2) * C + c];
       rstd[j] = saved[((size_t)sg * 2 + 1) * C + c];
       gm[j] = gamma[c]; bt[j] = beta[c];
-      s1[j] = 0.f; s2[j] = 0.f;
     }
     const int r0 = blockIdx.x * rows_per_block;
     const int r1 = min(r0 + rows_per_block, rows_per_group);
@@ -213,15 +232,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* 
         }
       }
     }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&red[cv * 8 + j], s1[j]);
-      atomicAdd(&red[C + cv * 8 + j], s2[j]);
-    }
   }
-  __syncthreads();
-  float* out = red_out + (size_t)g * 2 * C;
-  for (int i = threadIdx.x; i < 2 * C; i += kBnThreads) atomicAdd(&out[i], red[i]);
+  block_colsum_to_global<2>(part, acc, rl < lanes, rl, cv, lanes, C, red_out + (size_t)g * 2 * C);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -319,17 +331,16 @@ act_bwd_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __rest
                int bias_rows, int rows_per_block) {
   pdl_launch_dependents();
   pdl_wait();
-  extern __shared__ float red[];  // [C]
+  __shared__ __align__(16) float part[8 * kBnThreads];
   const int cvec = C >> 3;
   const int lanes = kBnThreads / cvec;
   const int cv = threadIdx.x % cvec;
   const int rl = threadIdx.x / cvec;
-  for (int i = threadIdx.x; i < C; i += kBnThreads) red[i] = 0.f;
-  __syncthreads();
-  if (rl < lanes) {
-    float s[8];
+  float acc[1][8];
+  float (&s)[8] = acc[0];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  if (rl < lanes) {
     const int r0 = blockIdx.x * rows_per_block;
     const int r1 = min(r0 + rows_per_block, rows);
     for (int rb = r0 + rl; rb < r1; rb += lanes * kRowBatch) {
@@ -363,14 +374,8 @@ act_bwd_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __rest
         *reinterpret_cast<uint4*>(dpre + (size_t)r * C + cv * 8) = make_uint4(o[0], o[1], o[2], o[3]);
       }
     }
-    if (dbias) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) atomicAdd(&red[cv * 8 + j], s[j]);
-    }
   }
-  __syncthreads();
-  if (dbias)
-    for (int i = threadIdx.x; i < C; i += kBnThreads) atomicAdd(&dbias[i], red[i]);
+  if (dbias) block_colsum_to_global<1>(part, acc, rl < lanes, rl, cv, lanes, C, dbias);
 }
 
 static int pick_rows_per_block(int rows, int C, int groups) {
@@ -393,7 +398,7 @@ int dcgan_bn_stats(const void* x, float* sums, int groups, int rows_per_group, i
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  launch_k(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
+  launch_k(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 0, st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
                                                                   rows_per_group, C, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
@@ -416,7 +421,7 @@ int dcgan_bn_bwd_reduce(const void* da, const void* pre, const float* saved, con
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  launch_k(bn_bwd_reduce_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, 
+  launch_k(bn_bwd_reduce_kernel, dim3(grid), dim3(kBnThreads), 0, st, 
       reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(pre), saved, gamma, beta,
       red, rows_per_group, C, stat_groups, act, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -440,7 +445,7 @@ int dcgan_act_bwd(const void* da, const void* a, void* dpre, float* dbias, int r
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows, C, 1);
   dim3 grid((rows + rpb - 1) / rpb);
-  launch_k(act_bwd_kernel, dim3(grid), dim3(kBnThreads), C * sizeof(float), st, 
+  launch_k(act_bwd_kernel, dim3(grid), dim3(kBnThreads), 0, st, 
       reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(a),
       reinterpret_cast<__nv_bfloat16*>(dpre), dbias, rows, a_rows, C, act, bias_rows, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -517,7 +522,7 @@ extern "C" int dcgan_bn_forward_static(const void* x, void* y, const float* gamm
   if (cudaMemsetAsync(sums, 0, need * sizeof(float), st) != cudaSuccess) return DCGAN_ERR_LAUNCH;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  launch_k(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
+  launch_k(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 0, st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
                                                                   rows_per_group, C, rpb);
   if (cudaGetLastError() != cudaSuccess) return DCGAN_ERR_LAUNCH;
   launch_k(bn_apply_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, 

@@ -70,8 +70,8 @@ struct SmemLayout {
   static constexpr int kBTileBytes = BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kATileBytes + kBTileBytes;
   static constexpr int kBarOffset = STAGES * kStageBytes;
-  static constexpr int kStatOffset = kBarOffset + 256;     // [2][BLOCK_N] f32 epilogue column sums
-  static constexpr int kTotal = kStatOffset + 2 * BLOCK_N * 4 + 1024;  // + alignment slack
+  static constexpr int kStatOffset = kBarOffset + 256;     // [4 warps][2][BLOCK_N] f32 epilogue column sums
+  static constexpr int kTotal = kStatOffset + 8 * BLOCK_N * 4 + 1024;  // + alignment slack
 };
 
 // 16-byte chunk (row, chunk) of a [rows][128 B] tile in the SWIZZLE_128B pattern
@@ -366,10 +366,6 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
 
     // ------------------------------------ epilogue ----------------------------------------------
     const bool do_stats = (MODE != MODE_W) && p.stats != nullptr;
-    if (do_stats) {
-      for (int i = gt; i < 2 * BLOCK_N; i += kNumGatherThreads) stat_smem[i] = 0.f;
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-    }
     if (ok) ok = mbar_wait(tmem_full_bar, 0, abort_flag, p.err_flag);
     tc_fence_after();
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
@@ -451,16 +447,23 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
           for (int j = 0; j < 32; ++j) sq[j] = f[j] * f[j];
           const float s1 = warp_transpose_reduce32(f);
           const float s2 = warp_transpose_reduce32(sq);
-          atomicAdd(&stat_smem[c + lane], s1);
-          atomicAdd(&stat_smem[BLOCK_N + c + lane], s2);
+          // one slice per warp: plain stores (f32 atomics on shared memory are compare-and-swap loops)
+          stat_smem[(q * 2) * BLOCK_N + c + lane] = s1;
+          stat_smem[(q * 2 + 1) * BLOCK_N + c + lane] = s2;
         }
       }
       if (do_stats) {
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
         float* gs = p.stats + (size_t)(m0 / p.stat_group_rows) * 2 * p.Cn + n0;
         for (int i = gt; i < BLOCK_N; i += kNumGatherThreads) {
-          atomicAdd(gs + i, stat_smem[i]);
-          atomicAdd(gs + p.Cn + i, stat_smem[BLOCK_N + i]);
+          float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            t1 += stat_smem[(w * 2) * BLOCK_N + i];
+            t2 += stat_smem[(w * 2 + 1) * BLOCK_N + i];
+          }
+          atomicAdd(gs + i, t1);
+          atomicAdd(gs + p.Cn + i, t2);
         }
       }
     } else if (MODE == MODE_W) {
