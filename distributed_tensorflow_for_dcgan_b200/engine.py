@@ -190,6 +190,7 @@ class DCGANEngine:
         # filter gradients are off the critical path (only the optimizer consumes them): they run on a side
         # stream next to the data-gradient chain, filling the SMs that the small grids leave idle
         self.wgrad_overlap = os.environ.get("DCGAN_WGRAD_OVERLAP", "1") != "0"
+        self.split_d_forward = self.wgrad_overlap and os.environ.get("DCGAN_SPLIT_D_FORWARD", "0") != "0"
         self.side = torch.cuda.Stream(self.device)
         self._side_used = False
         self._graph: Optional[torch.cuda.CUDAGraph] = None
@@ -266,6 +267,31 @@ class DCGANEngine:
                 K.conv_fprop_kn(self.d_act[i - 1], w, p[f"d_h{i}_conv/biases"], out=self.d_pre[i])
             self._bn_fwd(f"d_bn{i}", self.d_pre[i], self.d_act[i], stats_done=fused)
         K.head_fwd(self.d_act[3].view(2 * self.B, -1), p["d_h3_lin/Matrix"], p["d_h3_lin/bias"], self.logits)
+
+    def discriminator_forward_half(self, h: int) -> None:
+        """D on one half of the [real; fake] batch (h = 0 real, 1 fake).  The two calls of the reference's
+        discriminator (image_train.py:80-82) share weights but not batch statistics, so the real half does not
+        depend on the generator at all: the step runs it on the side stream underneath the generator's forward
+        pass, whose small layers leave most SMs idle."""
+        p, B = self.params, self.B
+        sl = slice(h * B, (h + 1) * B)
+        K.c3_fprop(self.d_in[sl], p["d_h0_conv/w"], p["d_h0_conv/biases"], act="lrelu", out=self.d_act[0][sl])
+        for i in (1, 2, 3):
+            name = f"d_bn{i}"
+            st = self.bn[name]
+            C = st["C"]
+            w = self.w_native[f"d_h{i}_conv/w"].view(25, self.d_ch[i], self.d_ch[i + 1])
+            pre, act = self.d_pre[i][sl], self.d_act[i][sl]
+            sums = st["sums"][h:h + 1]
+            if (pre.numel() // C) % 128 == 0:
+                K.conv_fprop_kn_stats(self.d_act[i - 1][sl], w, p[f"d_h{i}_conv/biases"], pre, sums, 1)
+            else:
+                K.conv_fprop_kn(self.d_act[i - 1][sl], w, p[f"d_h{i}_conv/biases"], out=pre)
+                K.bn_stats(pre.view(-1, C), sums, 1)
+            K.bn_apply(pre.view(-1, C), act.view(-1, C), sums, p[f"{name}/gamma"], p[f"{name}/beta"],
+                       st["saved"][h:h + 1], st["ema_mean"][h:h + 1], st["ema_var"][h:h + 1], 1, st["act"],
+                       self.cfg.bn_eps, self.cfg.bn_momentum)
+        K.head_fwd(self.d_act[3][sl].view(B, -1), p["d_h3_lin/Matrix"], p["d_h3_lin/bias"], self.logits[sl])
 
     # ------------------------------------------------------------------------------------------------
     # backward
@@ -383,10 +409,18 @@ class DCGANEngine:
             self.grads.zero_()
         self._scratch.zero_()
         K.f32_to_bf16(self.real_f32, self.d_in[:B])
+        split = self.split_d_forward and not (self.comm is not None and getattr(self.comm, "sync_bn", False))
+        if split:  # D(real) needs nothing from G: it runs beside the generator's forward pass
+            with self._off_critical_path():
+                self.discriminator_forward_half(0)
         with self._range("G_forward"):
             self.generator_forward(train=True)
         with self._range("D_forward"):
-            self.discriminator_forward()
+            if split:
+                self.discriminator_forward_half(1)
+                self._join_side()
+            else:
+                self.discriminator_forward()
             K.gan_loss(self.logits, self.losses, self.dlogit, self.probs, self.counters, B, 1.0, True)
         self._join_side()
         with self._range("D_backward"):
