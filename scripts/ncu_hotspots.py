@@ -5,9 +5,16 @@ import csv, io, subprocess, sys
 rep, rx = sys.argv[1], sys.argv[2]
 idx = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 25
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass", "-k", f"regex:{rx}",
-                      "-s", str(idx), "-c", "1"], capture_output=True, text=True).stdout
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass", "-k", f"regex:{rx}"],
+                     capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
+starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
+bounds = starts + [len(rows)]
+sections = [rows[bounds[i]:bounds[i + 1]] for i in range(len(starts))]
+if len(sections) >= 2 and len(sections) % 2 == 0 and sections[0] == sections[1]:
+    sections = sections[::2]  # the source page lists every launch twice
+print(f"{len(sections)} matching launches; showing #{idx}")
+rows = sections[idx]
 print(rows[0][1][:150])
 hdr = rows[1]
 col = {h: i for i, h in enumerate(hdr)}

@@ -198,6 +198,6 @@ def test_pipelined_submit_matches_train_step(cuda_lib):
     assert got[0][:3] == pytest.approx(want[0][:3], rel=2e-2)
     dist = lambda a, b: sum(abs(x - y) for x, y in zip(a[:3], b[:3]))
     for i in (1, 2):
-        assert dist(got[i], want[i]) < 0.25 * dist(got[i], wrong[i]), (i, got[i], want[i], wrong[i])
+        assert dist(got[i], want[i]) < 0.5 * dist(got[i], wrong[i]), (i, got[i], want[i], wrong[i])
     with pytest.raises(ValueError):
         eng.result(0)
