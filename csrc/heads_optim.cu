@@ -185,13 +185,55 @@ gan_loss_kernel(const float* __restrict__ logits, float* __restrict__ losses, fl
 // dW[k] += sum_{n<2B} dlogit[n]*h[n,k]; db += sum_{n<2B} dlogit[n]  (atomics; zeroed by caller).
 // thread = 8 features x kHeadBwdChunk images.
 // ---------------------------------------------------------------------------------------------
+// kFusedLoss: the logit gradients are recomputed from the logits by every thread that needs them and block
+// (0,0) also produces what gan_loss_kernel would (the three means, dlogit, probs, counters), so the step has
+// no single-block loss kernel between the two head kernels.
 constexpr int kHeadBwdChunk = 8;
+struct LossArgs {
+  const float* logits;
+  float* losses;
+  float* dlogit_out;
+  float* probs;
+  long long* counters;
+  float grad_div;
+  int advance;
+};
+template <bool kFusedLoss>
 __global__ void __launch_bounds__(128)
 head_bwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ w,
                 const float* __restrict__ dlogit, __nv_bfloat16* __restrict__ dh, float* __restrict__ dW,
-                float* __restrict__ db, int B, int F) {
+                float* __restrict__ db, int B, int F, LossArgs la) {
   pdl_launch_dependents();
   pdl_wait();
+  const float lscale = kFusedLoss ? 1.f / ((float)B * la.grad_div) : 0.f;
+  if (kFusedLoss && blockIdx.x == 0 && blockIdx.y == 0) {
+    __shared__ float red[3][4];
+    float l0 = 0.f, l1 = 0.f, l2 = 0.f;
+    for (int i = threadIdx.x; i < B; i += 128) {
+      const float xr = la.logits[i], xf = la.logits[B + i];
+      l0 += bce_logits(xr, 1.f);
+      l1 += bce_logits(xf, 0.f);
+      l2 += bce_logits(xf, 1.f);
+      const float sr = 1.f / (1.f + __expf(-xr)), sf = 1.f / (1.f + __expf(-xf));
+      if (la.dlogit_out) {
+        la.dlogit_out[i] = (sr - 1.f) * lscale;
+        la.dlogit_out[B + i] = sf * lscale;
+        la.dlogit_out[2 * B + i] = (sf - 1.f) * lscale;
+      }
+      if (la.probs) { la.probs[i] = sr; la.probs[B + i] = sf; }
+    }
+    l0 = warp_sum(l0); l1 = warp_sum(l1); l2 = warp_sum(l2);
+    if ((threadIdx.x & 31) == 0) {
+      red[0][threadIdx.x >> 5] = l0; red[1][threadIdx.x >> 5] = l1; red[2][threadIdx.x >> 5] = l2;
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+      float s = 0.f;
+      for (int i = 0; i < 4; ++i) s += red[threadIdx.x][i];
+      la.losses[threadIdx.x] = s / (float)B;
+    }
+    if (threadIdx.x == 0 && la.advance && la.counters) { la.counters[0] += 1; la.counters[1] += 1; }
+  }
   const int k8 = blockIdx.x * 128 + threadIdx.x;
   const int n0 = blockIdx.y * kHeadBwdChunk;
   if (k8 * 8 >= F) return;
@@ -203,7 +245,16 @@ head_bwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ w
 #pragma unroll
   for (int i = 0; i < kHeadBwdChunk; ++i) {
     const int n = n0 + i;
-    dl[i] = n < 3 * B ? dlogit[n] : 0.f;
+    if (kFusedLoss) {
+      dl[i] = 0.f;
+      if (n < 3 * B) {
+        const float x = la.logits[n < 2 * B ? n : n - B];  // slab 2 (g_loss) re-uses the fake logits
+        const float sg = 1.f / (1.f + __expf(-x));
+        dl[i] = ((n >= B && n < 2 * B) ? sg : sg - 1.f) * lscale;
+      }
+    } else {
+      dl[i] = n < 3 * B ? dlogit[n] : 0.f;
+    }
     hv[i] = make_uint4(0, 0, 0, 0);
     if (n < 2 * B) hv[i] = __ldg(reinterpret_cast<const uint4*>(h + (size_t)n * F) + k8);
   }
@@ -420,9 +471,20 @@ int dcgan_head_bwd(const void* h, const float* w, const float* dlogit, void* dh,
   if (F % 8) return DCGAN_ERR_SHAPE;
   const int threads_needed = F / 8;
   dim3 grid((threads_needed + 127) / 128, (3 * B + kHeadBwdChunk - 1) / kHeadBwdChunk);
-  launch_k(head_bwd_kernel, dim3(grid), dim3(128), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w,
-                                                                 dlogit, reinterpret_cast<__nv_bfloat16*>(dh), dW,
-                                                                 db, B, F);
+  launch_k(head_bwd_kernel<false>, dim3(grid), dim3(128), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w,
+           dlogit, reinterpret_cast<__nv_bfloat16*>(dh), dW, db, B, F, LossArgs{});
+  return LAUNCH_OK();
+}
+
+int dcgan_head_loss_bwd(const void* h, const float* w, const float* logits, float* losses, float* dlogit,
+                        float* probs, long long* counters, void* dh, float* dW, float* db, int B, int F,
+                        float grad_div, int advance, cudaStream_t st) {
+  if (F % 8 || logits == nullptr || losses == nullptr) return DCGAN_ERR_SHAPE;
+  const int threads_needed = F / 8;
+  dim3 grid((threads_needed + 127) / 128, (3 * B + kHeadBwdChunk - 1) / kHeadBwdChunk);
+  LossArgs la{logits, losses, dlogit, probs, counters, grad_div, advance};
+  launch_k(head_bwd_kernel<true>, dim3(grid), dim3(128), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w,
+           static_cast<const float*>(nullptr), reinterpret_cast<__nv_bfloat16*>(dh), dW, db, B, F, la);
   return LAUNCH_OK();
 }
 

@@ -190,6 +190,7 @@ class DCGANEngine:
         # filter gradients are off the critical path (only the optimizer consumes them): they run on a side
         # stream next to the data-gradient chain, filling the SMs that the small grids leave idle
         self.wgrad_overlap = os.environ.get("DCGAN_WGRAD_OVERLAP", "1") != "0"
+        self.fuse_head_loss = os.environ.get("DCGAN_FUSE_HEAD_LOSS", "1") != "0"
         self.split_d_forward = self.wgrad_overlap and os.environ.get("DCGAN_SPLIT_D_FORWARD", "0") != "0"
         self.side = torch.cuda.Stream(self.device)
         self._side_used = False
@@ -336,12 +337,18 @@ class DCGANEngine:
             torch.cuda.current_stream(self.device).wait_event(ev)
             self._side_used = False
 
-    def discriminator_backward(self) -> None:
+    def discriminator_backward(self, fused_loss: bool = False) -> None:
         """Three slabs of data gradient ([d_loss|real, d_loss|fake, g_loss|fake]); filter gradients from
-        the first two only (``var_list=d_vars`` for d_loss, image_train.py:109-110)."""
+        the first two only (``var_list=d_vars`` for d_loss, image_train.py:109-110).  ``fused_loss``: the
+        losses / logit gradients / step counters (``K.gan_loss``) are produced by the same launch."""
         p, g, B = self.params, self.grad_views, self.B
-        K.head_bwd(self.d_act[3].view(2 * B, -1), p["d_h3_lin/Matrix"], self.dlogit,
-                   self.dd_act[3].view(3 * B, -1), g["d_h3_lin/Matrix"], g["d_h3_lin/bias"], B)
+        if fused_loss:
+            K.head_loss_bwd(self.d_act[3].view(2 * B, -1), p["d_h3_lin/Matrix"], self.logits, self.losses,
+                            self.dlogit, self.probs, self.counters, self.dd_act[3].view(3 * B, -1),
+                            g["d_h3_lin/Matrix"], g["d_h3_lin/bias"], B, 1.0, True)
+        else:
+            K.head_bwd(self.d_act[3].view(2 * B, -1), p["d_h3_lin/Matrix"], self.dlogit,
+                       self.dd_act[3].view(3 * B, -1), g["d_h3_lin/Matrix"], g["d_h3_lin/bias"], B)
         for i in (3, 2, 1):
             self._bn_bwd(f"d_bn{i}", self.dd_act[i], self.d_pre[i], self.dd_pre[i])
             ci, co = self.d_ch[i], self.d_ch[i + 1]
@@ -421,10 +428,11 @@ class DCGANEngine:
                 self._join_side()
             else:
                 self.discriminator_forward()
-            K.gan_loss(self.logits, self.losses, self.dlogit, self.probs, self.counters, B, 1.0, True)
+            if not self.fuse_head_loss:
+                K.gan_loss(self.logits, self.losses, self.dlogit, self.probs, self.counters, B, 1.0, True)
         self._join_side()
         with self._range("D_backward"):
-            self.discriminator_backward()
+            self.discriminator_backward(fused_loss=self.fuse_head_loss)
         if self.update_mode == "simultaneous":
             if self.comm is not None and getattr(self.comm, "overlap", False):
                 # D's gradient exchange + Adam runs on the communication stream under G's backward pass

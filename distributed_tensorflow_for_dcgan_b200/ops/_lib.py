@@ -40,6 +40,7 @@ _SIGNATURES = {
     "dcgan_head_fwd": "ppppiis",
     "dcgan_gan_loss": "pppppifis",
     "dcgan_head_bwd": "ppppppiis",
+    "dcgan_head_loss_bwd": "ppppppppppiifis",
     "dcgan_adam": "ppppppzfffffs",
     "dcgan_cast_bf16": "ppzs",
     "dcgan_transpose_taps": "ppiiis",

@@ -178,6 +178,13 @@ def head_bwd(h2d, w, dlogit, dh, dW, db, B):
     call("dcgan_head_bwd", ptr(h2d), ptr(w), ptr(dlogit), ptr(dh), ptr(dW), ptr(db), B, F)
 
 
+def head_loss_bwd(h2d, w, logits, losses, dlogit, probs, counters, dh, dW, db, B, grad_div=1.0, advance=True):
+    """gan_loss + head_bwd in one launch."""
+    F = h2d.shape[1]
+    call("dcgan_head_loss_bwd", ptr(h2d), ptr(w), ptr(logits), ptr(losses), ptr(dlogit), ptr(probs), ptr(counters),
+         ptr(dh), ptr(dW), ptr(db), B, F, float(grad_div), int(advance))
+
+
 def adam(p, g, m, v, p_bf16, counters, lr=2e-4, b1=0.5, b2=0.999, eps=1e-8, gscale=1.0):
     call("dcgan_adam", ptr(p), ptr(g), ptr(m), ptr(v), ptr(p_bf16), ptr(counters), p.numel(), lr, b1, b2, eps,
          gscale)

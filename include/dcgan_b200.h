@@ -152,6 +152,12 @@ int dcgan_gan_loss(const float* logits, float* losses, float* dlogit, float* pro
                    float grad_div, int advance, cudaStream_t stream);
 int dcgan_head_bwd(const void* h, const float* w, const float* dlogit, void* dh, float* dW, float* db, int B,
                    int F, cudaStream_t stream);
+/* gan_loss + head_bwd in one launch (the simultaneous-update step): the logit gradients are recomputed from
+ * `logits` where they are needed and block (0,0) writes losses / dlogit (optional) / probs (optional) / counters
+ * exactly as dcgan_gan_loss would (image_train.py:91-96). */
+int dcgan_head_loss_bwd(const void* h, const float* w, const float* logits, float* losses, float* dlogit,
+                        float* probs, long long* counters, void* dh, float* dW, float* db, int B, int F,
+                        float grad_div, int advance, cudaStream_t st);
 /* TensorFlow-form Adam (image_train.py:109-112) over a flat range; t is read from counters[0]. */
 int dcgan_adam(float* p, const float* g, float* m, float* v, void* p_bf16, const long long* counters, size_t n,
                float lr, float b1, float b2, float eps, float gscale, cudaStream_t stream);

@@ -275,6 +275,16 @@ def test_linear_and_head(cuda_lib):
     _close(dh, dlogit[:, None] * w[None, :], name="head_bwd dh")
     _close(dWh, (dlogit[:2 * B, None] * h.float()).sum(0), rel=2e-3, name="head_bwd dW")
     _close(dbh, dlogit[:2 * B].sum().view(1), rel=2e-3, name="head_bwd db")
+    # gan_loss + head_bwd in one launch: same outputs as the two kernels above
+    losses2 = torch.zeros(3, device="cuda"); dlogit2 = torch.zeros(3 * B, device="cuda")
+    probs2 = torch.zeros(2 * B, device="cuda"); counters2 = torch.zeros(2, dtype=torch.int64, device="cuda")
+    dh2 = torch.empty_like(dh); dWh2 = torch.zeros(F, device="cuda"); dbh2 = torch.zeros(1, device="cuda")
+    K.head_loss_bwd(h, w, logits, losses2, dlogit2, probs2, counters2, dh2, dWh2, dbh2, B)
+    assert torch.equal(losses2, losses) and torch.equal(dlogit2, dlogit) and torch.equal(probs2, probs)
+    assert counters2.tolist() == [1, 1]
+    assert torch.equal(dh2, dh)
+    _close(dWh2, dWh, rel=1e-5, name="fused head dW")
+    _close(dbh2, dbh, rel=1e-5, name="fused head db")
 
 
 def test_adam_matches_tf_form(cuda_lib):
