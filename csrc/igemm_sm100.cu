@@ -806,6 +806,7 @@ static int g_igemm_tuning = 1;  // bit 3 (8): parity-fused transposed conv for l
                                 // bit 5 (32): no cluster split-K; bit 6 (64): transposed conv parity classes in
                                 // natural order instead of longest-first
 static int g_igemm_ksplit = 0;  // 0 = choose per layer; 1, 2, 4 = forced (tests / profiling)
+static int g_wgrad_cta_target = 148;  // filter-gradient launches split K until they have this many CTAs
 
 // Split-K factor for an F/T launch of `ctas` tiles whose shortest K loop has `min_kb` k-blocks: small-M
 // layers leave most of the 148 SMs idle while each CTA walks a long serial K loop, so K is cut across a
@@ -877,6 +878,7 @@ extern "C" {
 
 void dcgan_set_igemm_tuning(int v) { g_igemm_tuning = v; }
 void dcgan_set_igemm_ksplit(int v) { g_igemm_ksplit = (v == 1 || v == 2 || v == 4) ? v : 0; }
+void dcgan_set_wgrad_cta_target(int v) { g_wgrad_cta_target = v > 0 ? v : 148; }
 
 static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                            int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream,
@@ -1001,7 +1003,7 @@ int dcgan_conv_wgrad(const void* big, const void* small, float* dw, int NB, int 
   const int tiles = 25 * (Cd / kBlockM) * (Cg / block_n);
   if (splits <= 0) {
     splits = 1;
-    while (tiles * splits < 148 && splits * 2 <= total_kb && total_kb % (splits * 2) == 0 &&
+    while (tiles * splits < g_wgrad_cta_target && splits * 2 <= total_kb && total_kb % (splits * 2) == 0 &&
            total_kb / (splits * 2) >= 4)
       splits *= 2;
   }

@@ -48,6 +48,8 @@ void dcgan_set_igemm_tuning(int v);
  * its partial accumulators through distributed shared memory): 0 = chosen per layer (default), 1/2/4 = forced.
  * Tests and profiling only. */
 void dcgan_set_igemm_ksplit(int v);
+/* CTA count up to which the filter-gradient kernel keeps doubling its split-K factor (default 148). */
+void dcgan_set_wgrad_cta_target(int v);
 
 /* ---- implicit-GEMM convolutions on tcgen05 / TMEM / TMA (csrc/igemm_sm100.cu) ------------------ */
 
