@@ -300,8 +300,8 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   pdl_wait();
   const float t = (float)counters[0];
   const float lr_t = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
-  const size_t i4 = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4;
-  if (i4 >= n) return;
+  // grid-stride: the launch may cap its block count (dcgan_set_adam_blocks) to leave SMs to concurrent kernels
+  for (size_t i4 = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4; i4 < n; i4 += (size_t)gridDim.x * 1024) {
   if (i4 + 4 <= n) {
     float4 pv = *reinterpret_cast<float4*>(p + i4);
     const float4 gv = *reinterpret_cast<const float4*>(g + i4);
@@ -330,6 +330,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
       p[i] -= lr_t * m[i] / (sqrtf(v[i]) + eps);
       if (p_bf16) p_bf16[i] = __float2bfloat16(p[i]);
     }
+  }
   }
 }
 
@@ -432,7 +433,11 @@ count_zeros_kernel(const __nv_bfloat16* __restrict__ x, unsigned long long* __re
 using namespace dcgan;
 #define LAUNCH_OK() (cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH)
 
+static int g_adam_blocks = 0;  // 0 = one block per 1024 parameters; > 0 caps the grid (grid-stride loop)
+
 extern "C" {
+
+void dcgan_set_adam_blocks(int v) { g_adam_blocks = v > 0 ? v : 0; }
 
 int dcgan_lin_fwd(const float* z, const void* W, const float* bias, void* out, int NB, int K, int F,
                   cudaStream_t st) {
@@ -491,7 +496,8 @@ int dcgan_head_loss_bwd(const void* h, const float* w, const float* logits, floa
 int dcgan_adam(float* p, const float* g, float* m, float* v, void* p_bf16, const long long* counters, size_t n,
                float lr, float b1, float b2, float eps, float gscale, cudaStream_t st) {
   if (n == 0) return 0;
-  const size_t blocks = (n + 1023) / 1024;
+  size_t blocks = (n + 1023) / 1024;
+  if (g_adam_blocks > 0 && blocks > (size_t)g_adam_blocks) blocks = g_adam_blocks;
   launch_k(adam_kernel, dim3((unsigned)blocks), dim3(256), 0, st, p, g, m, v, reinterpret_cast<__nv_bfloat16*>(p_bf16), counters, n,
                                                lr, b1, b2, eps, gscale);
   return LAUNCH_OK();

@@ -85,7 +85,8 @@ def load() -> ctypes.CDLL:
     lib.dcgan_last_device_error.restype = c_int
     lib.dcgan_set_mn_desc_variant.argtypes = [c_int]
     lib.dcgan_set_mn_desc_variant.restype = None
-    for setter in ("dcgan_set_igemm_tuning", "dcgan_set_igemm_ksplit", "dcgan_set_wgrad_cta_target"):
+    for setter in ("dcgan_set_igemm_tuning", "dcgan_set_igemm_ksplit", "dcgan_set_wgrad_cta_target",
+                   "dcgan_set_adam_blocks"):
         getattr(lib, setter).argtypes = [c_int]
         getattr(lib, setter).restype = None
     # profiling overrides (A/B runs of bench.py without a rebuild)
@@ -95,6 +96,8 @@ def load() -> ctypes.CDLL:
         lib.dcgan_set_igemm_ksplit(int(os.environ["DCGAN_IGEMM_KSPLIT"]))
     if os.environ.get("DCGAN_WGRAD_CTAS"):
         lib.dcgan_set_wgrad_cta_target(int(os.environ["DCGAN_WGRAD_CTAS"]))
+    if os.environ.get("DCGAN_ADAM_BLOCKS"):
+        lib.dcgan_set_adam_blocks(int(os.environ["DCGAN_ADAM_BLOCKS"]))
     if os.environ.get("DCGAN_C3_TUNING"):  # "fprop_blocks,wgrad_blocks" of the 3-channel tensor-core kernels
         fb, wb = (int(v) for v in os.environ["DCGAN_C3_TUNING"].split(","))
         lib.dcgan_set_c3_tuning.argtypes = [c_int, c_int]
