@@ -880,6 +880,28 @@ void dcgan_set_igemm_tuning(int v) { g_igemm_tuning = v; }
 void dcgan_set_igemm_ksplit(int v) { g_igemm_ksplit = (v == 1 || v == 2 || v == 4) ? v : 0; }
 void dcgan_set_wgrad_cta_target(int v) { g_wgrad_cta_target = v > 0 ? v : 148; }
 
+// Host-only view of the launch plan of a strided (transposed = 0) or transposed (1) conv: tile width, split-K
+// factor, grid and whether the partial tiles fit the leader's stage ring.  No CUDA call; used by the CPU tests.
+int dcgan_debug_plan_conv(int transposed, int NB, int H, int W, int Cin, int Cout, int* block_n, int* ksplit,
+                          int* grid_xyz, int* partials_fit) {
+  if (Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
+  const int rows = transposed ? NB * H * W : NB * (H / 2) * (W / 2);
+  const int mt = (rows + kBlockM - 1) / kBlockM;
+  const int extra = transposed ? 4 : 1;
+  const int min_kb = transposed ? 4 * (Cin / 64) : 25 * (Cin / 64);
+  const int per_cta = transposed ? 8 : 16;
+  const int bn = pick_block_n(Cout, mt, extra, min_kb, per_cta);
+  if (bn < 0) return DCGAN_ERR_SHAPE;
+  const int ks = pick_ksplit((long)mt * (Cout / bn) * extra, min_kb, per_cta, bn);
+  const bool occ2 = (g_igemm_tuning & 1) != 0 && bn <= 128;
+  const int stages = (bn == 64) ? (occ2 ? 4 : 6) : (bn == 128 ? (occ2 ? 3 : 5) : 4);
+  *block_n = bn;
+  *ksplit = ks;
+  grid_xyz[0] = mt * ks; grid_xyz[1] = Cout / bn; grid_xyz[2] = extra;
+  *partials_fit = (long)(ks - 1) * kBlockM * bn * 4 <= (long)stages * (kATileBytes + bn * kBlockK * 2);
+  return 0;
+}
+
 static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                            int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream,
                            float* stats = nullptr, int stat_groups = 1) {

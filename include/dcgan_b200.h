@@ -53,6 +53,10 @@ void dcgan_set_wgrad_cta_target(int v);
 /* Cap on the block count of dcgan_adam (0 = one block per 1024 parameters): a capped launch walks its range
  * with a grid-stride loop and leaves SMs to kernels running beside it. */
 void dcgan_set_adam_blocks(int v);
+/* Host-only: the launch plan (tile width, split-K factor, grid, partial tiles fit the stage ring) that
+ * dcgan_conv_fprop* (transposed = 0) / dcgan_conv_tconv* (transposed = 1) would use.  Makes no CUDA call. */
+int dcgan_debug_plan_conv(int transposed, int NB, int H, int W, int Cin, int Cout, int* block_n, int* ksplit,
+                          int* grid_xyz, int* partials_fit);
 
 /* ---- implicit-GEMM convolutions on tcgen05 / TMEM / TMA (csrc/igemm_sm100.cu) ------------------ */
 
