@@ -529,7 +529,7 @@ int dcgan_c3_fprop_tc(const void* x, const float* w, const float* bias, void* ou
   int* err = error_flag_ptr();
   if (!err) return DCGAN_ERR_DRIVER;
   const int tiles = N * oH * oW / 128;
-  const int cap_f = g_c3_blocks_fprop > 0 ? g_c3_blocks_fprop : 148 * 2;  // in-step: 444 CTAs 0.8748, 296 0.8717
+  const int cap_f = g_c3_blocks_fprop > 0 ? g_c3_blocks_fprop : 148 * 3;  // in-step, chain at high priority: 444 CTAs 0.8112, 296 0.8134
   dim3 grid(tiles < cap_f ? tiles : cap_f, C / 64);
   launch_k(c3_fprop_tc_kernel, dim3(grid), dim3(kTcThreads), kTcSmem, st, reinterpret_cast<const __nv_bfloat16*>(x), w, bias,
                                                         reinterpret_cast<__nv_bfloat16*>(out), N, H, W, C, act, err);
@@ -569,9 +569,10 @@ int dcgan_c3_wgrad_tc(const void* x3, const void* y, float* dw, int N, int Hs, i
   if (!err) return DCGAN_ERR_DRIVER;
   const int tiles = N * Hs * Ws / 128;
   // Few CTAs: every CTA ends with 75 x 64 f32 atomics on the same addresses, and in the training step this kernel
-  // runs on the side stream beside the data-gradient chain, which wants the SMs.  In-step sweep (profiles/README.md):
-  // 444 CTAs 0.931 ms/step, 148 0.874, 74 0.832, 64 0.820, 48 0.819, 37 0.843, 24 0.921.
-  const int cap_w = g_c3_blocks_wgrad > 0 ? g_c3_blocks_wgrad : 64;
+  // runs on the side stream beside the data-gradient chain.  In-step sweeps (profiles/README.md): without stream
+  // priorities 444 CTAs 0.931 ms/step, 148 0.874, 64 0.820, 24 0.921; with the chain captured at high priority
+  // (engine default) 444 0.895, 296 0.849, 222 0.834, 148 0.811-0.813, 64 0.821.
+  const int cap_w = g_c3_blocks_wgrad > 0 ? g_c3_blocks_wgrad : 148;
   dim3 grid(tiles < cap_w ? tiles : cap_w, C / 64);
   launch_k(c3_wgrad_tc_kernel, dim3(grid), dim3(kTcThreads), kTcSmem, st, reinterpret_cast<const __nv_bfloat16*>(x3),
                                                         reinterpret_cast<const __nv_bfloat16*>(y), dw, N, Hs, Ws, C, err);

@@ -191,6 +191,9 @@ class DCGANEngine:
         # stream next to the data-gradient chain, filling the SMs that the small grids leave idle
         self.wgrad_overlap = os.environ.get("DCGAN_WGRAD_OVERLAP", "1") != "0"
         self.fuse_head_loss = os.environ.get("DCGAN_FUSE_HEAD_LOSS", "1") != "0"
+        # measured on one GPU (profiles/README.md); with a communicator the exchange kernels spin on their peers, so
+        # the default stays off there until it has been measured (DCGAN_MAIN_PRIORITY=1 forces it)
+        self.prioritize_main = os.environ.get("DCGAN_MAIN_PRIORITY", "1" if comm is None else "0") != "0"
         self.split_d_forward = self.wgrad_overlap and os.environ.get("DCGAN_SPLIT_D_FORWARD", "0") != "0"
         self.side = torch.cuda.Stream(self.device)
         self._side_used = False
@@ -474,7 +477,10 @@ class DCGANEngine:
         torch.cuda.synchronize()
         self.restore_state(state)
         self._graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self._graph):
+        # Kernel nodes inherit the priority of the stream they were captured on: capturing the chain on a
+        # high-priority stream lets the block scheduler serve it before the side-stream filler kernels.
+        hp = torch.cuda.Stream(device=self.device, priority=-1) if self.prioritize_main else None
+        with torch.cuda.graph(self._graph, stream=hp):
             self.step_body()
         self.restore_state(state)
 
