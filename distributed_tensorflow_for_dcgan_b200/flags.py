@@ -65,6 +65,9 @@ def define_flags() -> None:
     flags.DEFINE_bool("profile", False, "NVTX ranges + CUDA-event step timing report")
     flags.DEFINE_bool("identical_replicas", False, "testing aid: every worker draws the same data and z, so "
                       "synchronous replicas must reproduce the single-process run exactly")
+    flags.DEFINE_integer("worker_timeout_secs", 120, "ps role: a worker that stays silent this long while others wait "
+                         "for it (sync round / shutdown) is presumed dead and dropped; 0 = wait forever like "
+                         "server.join() (image_train.py:62-63)")
     flags.DEFINE_integer("log_every", 1, "print the step line every N steps (reference: every step)")
 
 

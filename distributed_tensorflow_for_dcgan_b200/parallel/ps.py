@@ -22,6 +22,9 @@ are not reproduced on purpose.
 """
 from __future__ import annotations
 
+import queue
+import threading
+import time
 from typing import Dict, List
 
 import torch
@@ -75,7 +78,7 @@ class PSServer:
     (image_train.py:62-63) except that it returns once every worker has said goodbye."""
 
     def __init__(self, cfg, ps_index: int, num_ps: int, worker_ranks: List[int], sync: bool, lr: float = 2e-4,
-                 beta1: float = 0.5, beta2: float = 0.999, eps: float = 1e-8):
+                 beta1: float = 0.5, beta2: float = 0.999, eps: float = 1e-8, worker_timeout: float = 0.0):
         specs = manifest.trainable_specs(cfg)
         shapes = {s.name: s.shape for s in specs}
         self.names = shard_variables(specs, num_ps)[ps_index]
@@ -88,6 +91,29 @@ class PSServer:
         self.ps_index, self.workers, self.sync = ps_index, list(worker_ranks), sync
         self.lr, self.beta1, self.beta2, self.eps = lr, beta1, beta2, eps
         self.applies = 0
+        # failure detection: the reference's ps blocks in server.join() forever and a dead worker
+        # stalls a synchronous round for good.  Here a worker that has been silent for `worker_timeout` seconds
+        # while somebody is waiting for it -- a sync round it has not joined, or a shutdown that only misses its
+        # goodbye -- is presumed dead and dropped; 0 keeps the wait-forever behaviour.
+        self.worker_timeout = float(worker_timeout)
+        self.dropped: List[int] = []
+
+    def _receiver(self, inbox: "queue.Queue") -> None:
+        """Receiver thread: reads whole requests (header + payload) from any worker into ``inbox``.  gloo cannot
+        time out a receive and carry on (a timed-out wait leaves the pair unusable), so the blocking receive
+        lives here and the serving loop waits on the queue, where a timeout is harmless."""
+        while True:
+            header = torch.zeros(4, dtype=torch.int64)
+            src = dist.recv(header)
+            op = int(header[0])
+            payload = []
+            if self.flat.numel:
+                n = {OP_PUSH: 1, OP_SET: 1, OP_SET_SLOTS: 2}.get(op, 0)
+                for _ in range(n):
+                    buf = torch.zeros(self.flat.numel)
+                    dist.recv(buf, src)
+                    payload.append(buf)
+            inbox.put((src, op, header, payload))
 
     def _apply(self, grad: torch.Tensor) -> None:
         self.t += 1
@@ -103,19 +129,34 @@ class PSServer:
     def serve(self) -> int:
         alive = set(self.workers)
         pending: Dict[int, torch.Tensor] = {}
-        header = torch.zeros(4, dtype=torch.int64)
+        inbox: "queue.Queue" = queue.Queue()
+        threading.Thread(target=self._receiver, args=(inbox,), daemon=True, name="ps-receiver").start()
+        last_seen = {w: time.time() for w in alive}
+        said_goodbye = False
         while alive:
-            src = dist.recv(header)
-            op = int(header[0])
-            if op == OP_DONE:
-                alive.discard(src)
+            try:
+                src, op, header, payload = inbox.get(timeout=1.0 if self.worker_timeout > 0 else None)
+            except queue.Empty:
+                # somebody waits for the silent ones: an open sync round, or a shutdown already under way
+                if not (pending or said_goodbye):
+                    continue
+                now = time.time()
+                for w in [w for w in alive if w not in pending and now - last_seen[w] > self.worker_timeout]:
+                    print(f"ps {self.ps_index}: worker rank {w} silent for more than {self.worker_timeout:.0f} s, "
+                          f"presumed dead and dropped", flush=True)
+                    alive.discard(w)
+                    self.dropped.append(w)
                 if self.sync and pending and set(pending) >= alive and alive:
                     self._finish_round(pending)
                 continue
-            if op == OP_PUSH:
-                grad = torch.zeros(self.flat.numel)
-                if self.flat.numel:
-                    dist.recv(grad, src)
+            last_seen[src] = time.time()
+            if op == OP_DONE:
+                alive.discard(src)
+                said_goodbye = True
+                if self.sync and pending and set(pending) >= alive and alive:
+                    self._finish_round(pending)
+            elif op == OP_PUSH:
+                grad = payload[0] if payload else torch.zeros(0)
                 if self.sync:
                     pending[src] = grad
                     if set(pending) >= alive:
@@ -126,13 +167,13 @@ class PSServer:
             elif op == OP_PULL:
                 self._reply(src)
             elif op == OP_SET:
-                if self.flat.numel:
-                    dist.recv(self.p, src)
+                if payload:
+                    self.p.copy_(payload[0])
                 self.global_step, self.t = int(header[1]), int(header[2])
             elif op == OP_SET_SLOTS:
-                if self.flat.numel:
-                    dist.recv(self.m, src)
-                    dist.recv(self.v, src)
+                if payload:
+                    self.m.copy_(payload[0])
+                    self.v.copy_(payload[1])
             elif op == OP_GET_SLOTS:
                 if self.flat.numel:
                     dist.send(self.m, src)

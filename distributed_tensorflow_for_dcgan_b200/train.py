@@ -52,11 +52,13 @@ def run_ps(FLAGS, role, cfg) -> int:
     cl.init_process_group(role, "gloo")
     workers = [role.cluster.worker_rank(i) for i in range(role.cluster.num_workers)]
     server = PSServer(cfg, role.task_index, role.cluster.num_ps, workers, FLAGS.sync_replicas, FLAGS.learning_rate,
-                      FLAGS.beta1)
+                      FLAGS.beta1, worker_timeout=FLAGS.worker_timeout_secs)
     applies = server.serve()
-    print(f"ps {role.task_index}: served {applies} applies, global_step {server.global_step}")
-    cl.shutdown()
-    return 0
+    print(f"ps {role.task_index}: served {applies} applies, global_step {server.global_step}", flush=True)
+    # the receiver thread is still blocked in a receive from any worker, so the process group is not torn down
+    # collectively: leave directly (the workers destroy their side on their own)
+    sys.stdout.flush()
+    os._exit(0)
 
 
 def _use_cuda(FLAGS) -> bool:

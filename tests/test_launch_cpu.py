@@ -93,3 +93,56 @@ def test_sync_replicas_reproduce_single_process_run(tmp_path):
     sd_b = checkpoint.load_latest(str(b / "ckpt"))
     for k in ("g_h1/w", "d_h2_conv/w", "g_bn1/gamma", "d_h3_lin/Matrix", "g_h2/w/Adam_1"):
         assert torch.allclose(sd_a[k], sd_b[k], rtol=1e-4, atol=1e-6), k
+
+
+def _kill_worker_one(tmp_path, mode_flags, budget):
+    import threading
+    import time
+    ports = _free_ports(3)
+    ps_hosts = f"127.0.0.1:{ports[0]}"
+    worker_hosts = ",".join(f"127.0.0.1:{p}" for p in ports[1:])
+    extra = ["--batch_size=4", f"--max_steps={budget}", "--worker_timeout_secs=6"] + mode_flags
+    procs = {"ps": _launch("ps", 0, ps_hosts, worker_hosts, extra, tmp_path),
+             "w0": _launch("worker", 0, ps_hosts, worker_hosts, extra, tmp_path),
+             "w1": _launch("worker", 1, ps_hosts, worker_hosts, extra, tmp_path)}
+    lines = {k: [] for k in procs}
+
+    def pump(tag):
+        for l in procs[tag].stdout:
+            lines[tag].append(l.rstrip())
+    threads = [threading.Thread(target=pump, args=(k,), daemon=True) for k in procs]
+    for t in threads:
+        t.start()
+    try:
+        t0 = time.time()
+        while time.time() - t0 < 300 and sum(l.startswith("Epoch:") for l in lines["w1"]) < 2:
+            assert procs["w1"].poll() is None, "\n".join(lines["w1"][-20:])
+            time.sleep(0.2)
+        procs["w1"].kill()                               # the non-chief worker dies mid-run
+        assert procs["w0"].wait(timeout=300) == 0, "\n".join(lines["w0"][-20:])
+        assert procs["ps"].wait(timeout=120) == 0, "\n".join(lines["ps"][-20:])
+    finally:
+        for p in procs.values():
+            if p.poll() is None:
+                p.kill()
+    for t in threads:
+        t.join(timeout=5)
+    return lines
+
+
+def test_async_mode_survives_a_killed_worker(tmp_path):
+    """Fault tier of SURVEY.md 4 / 5.3: asynchronous replicas tolerate the loss of a non-chief worker by
+    construction (the others keep training); here the parameter server additionally notices the silent worker
+    at shutdown and leaves instead of blocking forever like ``server.join()`` (image_train.py:62-63)."""
+    lines = _kill_worker_one(tmp_path, ["--sync_replicas=false"], 16)
+    assert any("step: [16]" in l for l in lines["w0"])   # the survivor reached the step budget
+    assert any("presumed dead and dropped" in l for l in lines["ps"])
+    assert any("served" in l and "applies" in l for l in lines["ps"])
+
+
+def test_sync_mode_drops_a_dead_worker_and_continues(tmp_path):
+    """Synchronous rounds wait for every live worker; one that has been silent for --worker_timeout_secs while
+    a round is open is dropped and the round completes with the survivors (the reference would hang)."""
+    lines = _kill_worker_one(tmp_path, ["--sync_replicas=true"], 6)
+    assert any("step: [ 6]" in l for l in lines["w0"])
+    assert any("presumed dead and dropped" in l for l in lines["ps"])
