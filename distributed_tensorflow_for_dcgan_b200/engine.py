@@ -520,19 +520,24 @@ class DCGANEngine:
         st = self._pipe()
         slot = st.n & 1
         main = torch.cuda.current_stream()
-        if real.is_cuda and z.is_cuda:
-            self.real_f32.copy_(real, non_blocking=True)
-            self.z.copy_(z, non_blocking=True)
-        else:
+        # Host tensors go through the staging slot on the copy stream.  Device tensors are copied on the current
+        # stream, which is the one their producer has been ordered against (e.g. DevicePrefetcher.next()).
+        staged = [(src, stage, dst) for src, stage, dst in ((real, st.stage_real[slot], self.real_f32),
+                                                            (z, st.stage_z[slot], self.z)) if not src.is_cuda]
+        if staged:
             with torch.cuda.stream(st.copy_stream):
                 st.copy_stream.wait_event(st.ev_consumed[slot])  # the step that last used this slot has read it
-                st.stage_real[slot].copy_(real, non_blocking=True)
-                st.stage_z[slot].copy_(z, non_blocking=True)
+                for src, stage, _ in staged:
+                    stage.copy_(src, non_blocking=True)
                 st.ev_in[slot].record(st.copy_stream)
             main.wait_event(st.ev_in[slot])
-            self.real_f32.copy_(st.stage_real[slot], non_blocking=True)
-            self.z.copy_(st.stage_z[slot], non_blocking=True)
+            for _, stage, dst in staged:
+                dst.copy_(stage, non_blocking=True)
             st.ev_consumed[slot].record(main)
+        if real.is_cuda:
+            self.real_f32.copy_(real, non_blocking=True)
+        if z.is_cuda:
+            self.z.copy_(z, non_blocking=True)
         self.run_step()
         st.host_loss[slot].copy_(self.losses, non_blocking=True)
         st.host_cnt[slot].copy_(self.counters, non_blocking=True)
