@@ -1,0 +1,52 @@
+"""Layout of the flat parameter arena (engine.ParamArena) -- the contract the optimizer / communication kernels
+rely on: [G bf16-consumed | G f32-consumed | D bf16-consumed | D f32-consumed], every tensor 32-byte aligned,
+TF names and TF layouts, padded to whole 1024-element blocks."""
+import torch
+
+from distributed_tensorflow_for_dcgan_b200.config import ModelConfig
+from distributed_tensorflow_for_dcgan_b200.engine import ParamArena
+from distributed_tensorflow_for_dcgan_b200.models import manifest
+
+
+def test_arena_layout():
+    cfg = ModelConfig(batch_size=4)
+    A = ParamArena(cfg, "cpu")
+    specs = {s.name: s for s in manifest.trainable_specs(cfg)}
+    assert set(A.offsets) == set(specs) and len(specs) == 34
+    assert sum(s.numel for s in specs.values()) == 9451908      # G 5,135,363 + D 4,316,545
+    spans = sorted((off, off + specs[n].numel, n) for n, (off, _) in A.offsets.items())
+    for (a0, a1, an), (b0, _, bn) in zip(spans, spans[1:]):
+        assert a1 <= b0, (an, bn)                                # no overlap
+    for off, _, name in spans:
+        assert off % 8 == 0, name                                # 32-byte aligned f32 (16-byte aligned bf16)
+    assert A.padded % 1024 == 0 and A.numel <= A.padded < A.numel + 1024
+    # region order
+    for name, (off, _) in A.offsets.items():
+        is_g = manifest.is_g_var(name)
+        assert (off < A.g_end) == is_g, name
+        key = "g" if is_g else "d"
+        assert (off < A.f32_start[key]) == A.reads_bf16(name), name
+    assert A.f32_start["g"] < A.g_end < A.f32_start["d"] < A.numel
+    # the tensors the kernels read in f32: biases, batch-norm parameters, the 3-channel filters, d_h3_lin
+    f32_names = {n for n in specs if not A.reads_bf16(n)}
+    assert {"g_h4/w", "d_h0_conv/w", "d_h3_lin/Matrix", "g_h0_lin/bias", "g_bn0/gamma", "d_bn3/beta"} <= f32_names
+    assert {"g_h0_lin/Matrix", "g_h1/w", "g_h2/w", "g_h3/w", "d_h1_conv/w", "d_h2_conv/w", "d_h3_conv/w"} == \
+        set(specs) - f32_names
+
+
+def test_named_views_alias_the_flat_buffers():
+    cfg = ModelConfig(batch_size=4)
+    A = ParamArena(cfg, "cpu")
+    views = A.named(A.master)
+    assert views["g_h1/w"].shape == (5, 5, 256, 512) and views["d_h1_conv/w"].shape == (5, 5, 64, 128)
+    views["d_h3_lin/bias"].fill_(3.0)
+    off, _ = A.offsets["d_h3_lin/bias"]
+    assert A.master[off].item() == 3.0 and A.master.sum().item() == 3.0
+    assert A.bf16.dtype == torch.bfloat16 and A.bf16.numel() == A.master.numel() == A.m.numel() == A.v.numel()
+
+
+def test_wide_config_arena():
+    cfg = ModelConfig(batch_size=2, output_size=128, gf_dim=128, df_dim=128)
+    A = ParamArena(cfg, "cpu")
+    assert A.named(A.master)["g_h1/w"].shape == (5, 5, 512, 1024)
+    assert A.padded % 1024 == 0
