@@ -50,3 +50,25 @@ def test_wide_config_arena():
     A = ParamArena(cfg, "cpu")
     assert A.named(A.master)["g_h1/w"].shape == (5, 5, 512, 1024)
     assert A.padded % 1024 == 0
+
+
+def test_optimizer_shards_tile_the_buckets():
+    """parallel/fused_comm.py shard_range() mirrors shard_quads() of csrc/comm_sm100.cu: per bucket the ranks own
+    consecutive, disjoint ranges that cover it exactly, and every boundary falls on an even number of float4
+    quads so that no 16-byte bf16 chunk (8 elements) straddles two owners."""
+    from distributed_tensorflow_for_dcgan_b200.parallel.fused_comm import FusedComm
+    A = ParamArena(ModelConfig(batch_size=4), "cpu")
+    for world in (2, 4, 8):
+        comm = FusedComm.__new__(FusedComm)          # only the pure bookkeeping is exercised here
+        comm.world = world
+        comm.buckets = {"g": (0, A.g_end), "d": (A.g_end, A.padded)}
+        for bucket, (lo, hi) in comm.buckets.items():
+            cursor = lo
+            for r in range(world):
+                s0, s1 = comm.shard_range(bucket, r)
+                assert s0 == cursor and s1 >= s0, (world, bucket, r)
+                assert (s0 - lo) % 8 == 0, (world, bucket, r)
+                cursor = s1
+            assert cursor == hi, (world, bucket)
+            sizes = [comm.shard_range(bucket, r)[1] - comm.shard_range(bucket, r)[0] for r in range(world)]
+            assert max(sizes) - min(sizes[:-1] or sizes) <= 8 or sizes[-1] <= max(sizes)   # balanced up to rounding
