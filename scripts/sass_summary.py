@@ -5,7 +5,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OBJ = os.path.join(ROOT, "build", "obj")
 OUT = os.path.join(ROOT, "docs", "sass")
 os.makedirs(OUT, exist_ok=True)
-PAT = re.compile(r"^(UTC\w*MMA|UTCBAR|UTCATOM\w*|UTMALDG|UTMASTG|UTMAPF|UBLKCP|LDTM|STTM|SYNCS|LDGSTS|LDGMC|STGMC|REDGMC|"
+PAT = re.compile(r"^(UCGABAR_ARV|UCGABAR_WAIT|UTC\w*MMA|UTCBAR|UTCATOM\w*|UTMALDG|UTMASTG|UTMAPF|UBLKCP|LDTM|STTM|SYNCS|LDGSTS|LDGMC|STGMC|REDGMC|"
                  r"REDG|ATOMG|ATOM|LDG\.E\.\d*\.?STRONG\.SYS|STG\.E\.\d*\.?STRONG\.SYS|LD\.E\.\d*\.?STRONG\.SYS|HMMA|FFMA|CCTL)")
 for obj in sorted(os.listdir(OBJ)):
     if not obj.endswith(".o"):
