@@ -34,6 +34,7 @@ from ..models import manifest
 from ..optim.adam_tf import adam_tf_step_
 
 OP_PUSH, OP_PULL, OP_SET, OP_GET_SLOTS, OP_SET_SLOTS, OP_DONE = 1, 2, 3, 4, 5, 6
+OP_DEAD = -1  # internal: the receiver thread lost the connection to a worker in the middle of a request
 
 
 def shard_variables(specs, num_ps: int) -> List[List[str]]:
@@ -104,16 +105,25 @@ class PSServer:
         lives here and the serving loop waits on the queue, where a timeout is harmless."""
         while True:
             header = torch.zeros(4, dtype=torch.int64)
-            src = dist.recv(header)
-            op = int(header[0])
-            payload = []
-            if self.flat.numel:
-                n = {OP_PUSH: 1, OP_SET: 1, OP_SET_SLOTS: 2}.get(op, 0)
-                for _ in range(n):
-                    buf = torch.zeros(self.flat.numel)
-                    dist.recv(buf, src)
-                    payload.append(buf)
-            inbox.put((src, op, header, payload))
+            src = None
+            try:
+                src = dist.recv(header)
+                op = int(header[0])
+                payload = []
+                if self.flat.numel:
+                    n = {OP_PUSH: 1, OP_SET: 1, OP_SET_SLOTS: 2}.get(op, 0)
+                    for _ in range(n):
+                        buf = torch.zeros(self.flat.numel)
+                        dist.recv(buf, src)
+                        payload.append(buf)
+                inbox.put((src, op, header, payload))
+            except RuntimeError as e:
+                # a worker died in the middle of a request ("Connection closed by peer"): tell the serving loop
+                # which one, then keep receiving from the others
+                if src is not None:
+                    inbox.put((src, OP_DEAD, header, [str(e)]))
+                else:
+                    time.sleep(0.2)
 
     def _apply(self, grad: torch.Tensor) -> None:
         self.t += 1
@@ -150,7 +160,15 @@ class PSServer:
                     self._finish_round(pending)
                 continue
             last_seen[src] = time.time()
-            if op == OP_DONE:
+            if op == OP_DEAD:
+                if src in alive:
+                    print(f"ps {self.ps_index}: lost worker rank {src} in the middle of a request, dropped", flush=True)
+                    alive.discard(src)
+                    pending.pop(src, None)
+                    self.dropped.append(src)
+                    if self.sync and pending and set(pending) >= alive and alive:
+                        self._finish_round(pending)
+            elif op == OP_DONE:
                 alive.discard(src)
                 said_goodbye = True
                 if self.sync and pending and set(pending) >= alive and alive:
