@@ -298,8 +298,16 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
             float b1, float b2, float eps, float gscale) {
   pdl_launch_dependents();
   pdl_wait();
-  const float t = (float)counters[0];
-  const float lr_t = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
+  // the bias-corrected step size is the same for every thread: one thread evaluates the two powf (a few hundred
+  // instructions; ncu showed this kernel at 60 % issue utilisation, which matters while it runs beside G's
+  // backward pass) and the block reads it from shared memory
+  __shared__ float s_lr_t;
+  if (threadIdx.x == 0) {
+    const float t = (float)counters[0];
+    s_lr_t = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
+  }
+  __syncthreads();
+  const float lr_t = s_lr_t;
   // grid-stride: the launch may cap its block count (dcgan_set_adam_blocks) to leave SMs to concurrent kernels
   for (size_t i4 = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4; i4 < n; i4 += (size_t)gridDim.x * 1024) {
   if (i4 + 4 <= n) {

@@ -84,6 +84,13 @@ __device__ __forceinline__ void cp_async_16(uint32_t smem_dst, const void* src, 
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(src), "r"(src_bytes)
                : "memory");
 }
+// same copy with the "ignore-src" predicate form: when `valid` is zero nothing is read and 16 zero bytes are written
+__device__ __forceinline__ void cp_async_16_or_zero(uint32_t smem_dst, const void* src, uint32_t valid) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %2, 0;\n\tcp.async.cg.shared.global [%0], [%1], 16, p;\n\t}" ::"r"(smem_dst),
+      "l"(src), "r"(valid)
+      : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
@@ -268,63 +275,70 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
     bool ok = true;
 
     if (MODE != MODE_W) {
-      // rows are fixed per thread: decode (n, qh, qw) once
-      int pix_base[8];  // n * gH * gW, or -1 when the row is past the end
-      int yx[8];        // (stride*qh) << 16 | (stride*qw)
+      // The producer warps are bound by instruction issue, not by L2 (ncu: ~350 warp instructions per warp and
+      // k-block, IPC 1.8 with 12 resident warps), so everything that does not change from one k-block to the
+      // next is hoisted: per row the element offset of the unshifted tap and a validity bit per (dy, dx) shift,
+      // per k-block one uniform offset and one bit index, advanced without divisions
+      // (tests/test_gather_math_cpu.py emulates exactly this arithmetic against the per-k-block formula).
+      int base_off[8];      // ((n*gH + y0)*gW + x0)*gC + chunk*8, element units (host: numel < 2^31)
+      uint32_t vmask[8];    // bit (dy+1)*5 + (dx+1): the shifted pixel exists; 0 for rows past the end
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const int R = m0 + rbase + 16 * i;
+        base_off[i] = 0;
+        vmask[i] = 0;
         if (R < p.rows_total) {
           const int qw = R & (rW - 1);
           const int qh = (R >> p.rW_log2) & (rH - 1);
           const int n = R >> (p.rW_log2 + p.rH_log2);
-          pix_base[i] = n * p.gH * p.gW;
-          yx[i] = ((stride * qh) << 16) | (stride * qw);
-        } else {
-          pix_base[i] = -1;
-          yx[i] = 0;
+          const int y0 = stride * qh, x0 = stride * qw;
+          base_off[i] = ((n * p.gH + y0) * p.gW + x0) * p.gC + chunk * 8;
+          uint32_t my = 0, mx = 0;
+#pragma unroll
+          for (int sft = 0; sft < 5; ++sft) {
+            if ((unsigned)(y0 + sft - 1) < (unsigned)p.gH) my |= 1u << sft;
+            if ((unsigned)(x0 + sft - 1) < (unsigned)p.gW) mx |= 1u << sft;
+          }
+          uint32_t m = 0;
+#pragma unroll
+          for (int sy = 0; sy < 5; ++sy)
+            if ((my >> sy) & 1u) m |= mx << (5 * sy);
+          vmask[i] = m;
         }
       }
       const int cpt = p.gC / kBlockK;
-      const int nkw = pw ? 3 : 2;
+      const int nb = (MODE == MODE_F) ? 5 : (pw ? 3 : 2);  // taps per filter row of this class
+      // position of this CTA's first k-block (the only divisions); then (ta, tb, cc) advance like an odometer
+      const int lt0 = kb_base / cpt;
+      int cc = kb_base - lt0 * cpt;
+      int ta = lt0 / nb, tb = lt0 - ta * nb;               // F: (kh, kw).  T: (ikh, ikw)
+      int s_issue = 0, s_pub = 0;
+      uint32_t ph_issue = 0;
       // cp.async pipeline: the copies of kGatherDepth k-blocks are in flight per thread; a k-block is
       // published (proxy fence + mbarrier arrive) once its group has landed.
       for (int it = 0; it < num_kb + kGatherDepth - 1; ++it) {
         if (it < num_kb) {
-          const int kb = it;
-          const int s = kb % STAGES;
-          const uint32_t phase = (kb / STAGES) & 1;
-          const int lt = (kb_base + kb) / cpt;
-          const int c0 = (kb_base + kb - lt * cpt) * kBlockK;
-          int dy, dx;
-          if (MODE == MODE_F) {
-            const int kh = lt / 5, kw = lt - kh * 5;
-            dy = kh - 1;
-            dx = kw - 1;
-          } else {
-            const int ikh = lt / nkw, ikw = lt - ikh * nkw;
-            const int kh = ph ? 2 * ikh : 2 * ikh + 1;
-            const int kw = pw ? 2 * ikw : 2 * ikw + 1;
-            dy = (ph + 1 - kh) / 2;  // exact: the numerator is even by construction
-            dx = (pw + 1 - kw) / 2;
-          }
-          if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
-          const uint32_t sA = smem_u32(smem + s * L::kStageBytes);
+          const int dy = (MODE == MODE_F) ? ta - 1 : ph - ta;
+          const int dx = (MODE == MODE_F) ? tb - 1 : pw - tb;
+          const int delta = (dy * p.gW + dx) * p.gC + cc * kBlockK;
+          const uint32_t bitmask = 1u << ((dy + 1) * 5 + (dx + 1));
+          if (!mbar_wait(&empty_bar[s_issue], ph_issue ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+          const uint32_t sA = smem_u32(smem + s_issue * L::kStageBytes);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const int y = (yx[i] >> 16) + dy;
-            const int x = (yx[i] & 0xffff) + dx;
-            const bool valid =
-                pix_base[i] >= 0 && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW;
-            const size_t off = valid ? ((size_t)(pix_base[i] + y * p.gW + x)) * p.gC + c0 + chunk * 8 : 0;
-            cp_async_16(sA + swz128(rbase + 16 * i, chunk), p.g + off, valid ? 16u : 0u);
+            const uint32_t valid = vmask[i] & bitmask;
+            const uint32_t off = valid ? (uint32_t)(base_off[i] + delta) : 0u;  // a valid offset is never negative
+            cp_async_16_or_zero(sA + swz128(rbase + 16 * i, chunk), p.g + off, valid);
           }
+          if (++cc == cpt) { cc = 0; if (++tb == nb) { tb = 0; ++ta; } }
+          if (++s_issue == STAGES) { s_issue = 0; ph_issue ^= 1; }
         }
         cp_async_commit();
         if (it >= kGatherDepth - 1) {
           cp_async_wait<kGatherDepth - 1>();
           fence_proxy_async_smem();
-          mbar_arrive(&full_bar[(it - (kGatherDepth - 1)) % STAGES]);
+          mbar_arrive(&full_bar[s_pub]);
+          if (++s_pub == STAGES) s_pub = 0;
         }
       }
     } else {
@@ -346,13 +360,14 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
             const int qh = (R >> p.rW_log2) & (rH - 1);
             const int n = R >> (p.rW_log2 + p.rH_log2);
             const int y = 2 * qh + kh - 1, x = 2 * qw + kw - 1;
-            const bool valid =
-                R < p.rows_total && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW;
-            const size_t off = valid ? ((size_t)((n * p.gH + y) * p.gW + x)) * p.gC + n0 + chunk * 8 : 0;
+            const uint32_t valid =
+                (R < p.rows_total && (unsigned)y < (unsigned)p.gH && (unsigned)x < (unsigned)p.gW) ? 1u : 0u;
+            // 32-bit element offsets (host: numel < 2^31); an ignored copy still gets an in-bounds address
+            const uint32_t off = valid ? (uint32_t)(((n * p.gH + y) * p.gW + x) * p.gC + n0 + chunk * 8) : 0u;
+            const __nv_bfloat16* src = p.g + off;
 #pragma unroll
             for (int j = 0; j < kSub; ++j)
-              cp_async_16(sB + j * 8192 + swz128(rbase + 16 * i, chunk), p.g + off + (valid ? 64 * j : 0),
-                          valid ? 16u : 0u);
+              cp_async_16_or_zero(sB + j * 8192 + swz128(rbase + 16 * i, chunk), src + 64 * j, valid);
           }
         }
         cp_async_commit();
@@ -906,6 +921,7 @@ static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, v
                            int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream,
                            float* stats = nullptr, int stat_groups = 1) {
   if ((H & 1) || (W & 1) || Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
+  if ((long)NB * H * W * Cin >= (1L << 31)) return DCGAN_ERR_SHAPE;  // the gather uses 32-bit element offsets
   const int oH = H / 2, oW = W / 2;
   const int lh = ilog2_exact(oH), lw = ilog2_exact(oW);
   if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;
@@ -958,6 +974,7 @@ static int conv_tconv_impl(const void* x, const void* w_nk, const float* bias, v
                            int Cin, int Cout, int act, int block_n, cudaStream_t stream, float* stats,
                            int stat_groups) {
   if (Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
+  if ((long)NB * H * W * Cin >= (1L << 31)) return DCGAN_ERR_SHAPE;  // the gather uses 32-bit element offsets
   const int lh = ilog2_exact(H), lw = ilog2_exact(W);
   if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;
   IgemmParams p{};
@@ -1019,6 +1036,7 @@ int dcgan_conv_wgrad(const void* big, const void* small, float* dw, int NB, int 
   if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;
   const int rows = NB * Hs * Ws;
   if (rows % kBlockK) return DCGAN_ERR_SHAPE;
+  if ((long)rows * 4 * Cg >= (1L << 31)) return DCGAN_ERR_SHAPE;  // the gather uses 32-bit element offsets
   const int total_kb = rows / kBlockK;
   if (block_n <= 0) block_n = (Cg % 256 == 0) ? 256 : (Cg % 128 == 0 ? 128 : 64);
   if (Cg % block_n) return DCGAN_ERR_SHAPE;
