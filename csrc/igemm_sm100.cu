@@ -22,6 +22,9 @@
 //
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer (one lane),
 // warps 2-5 = im2col gather producers, then the epilogue (one TMEM lane quadrant each).
+// The gather producers are bound by instruction issue, so per-row constants (element offset of the unshifted
+// tap, a 5x5 bit mask of which shifted taps exist) are computed once and a k-block costs one uniform offset,
+// one bit test and one cp.async (ignore-src form = zero fill for padding) per row.
 #include <mutex>
 #include <unordered_map>
 #include <vector>
