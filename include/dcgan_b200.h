@@ -50,6 +50,9 @@ void dcgan_set_igemm_tuning(int v);
 void dcgan_set_igemm_ksplit(int v);
 /* CTA count up to which the filter-gradient kernel keeps doubling its split-K factor (default 148). */
 void dcgan_set_wgrad_cta_target(int v);
+/* CTA caps of the 3-channel tensor-core kernels (0 = default): forward / data-gradient kernel, filter-gradient
+ * kernel.  Profiling only. */
+void dcgan_set_c3_tuning(int fprop_blocks, int wgrad_blocks);
 /* Cap on the block count of dcgan_adam (0 = one block per 1024 parameters): a capped launch walks its range
  * with a grid-stride loop and leaves SMs to kernels running beside it. */
 void dcgan_set_adam_blocks(int v);

@@ -65,3 +65,18 @@ def test_rejects_unsupported_channels(lib):
     grid = (ctypes.c_int * 3)()
     assert lib.dcgan_debug_plan_conv(0, 8, 16, 16, 48, 64, ctypes.byref(bn), ctypes.byref(ks), grid,
                                      ctypes.byref(fit)) < 0
+
+
+def test_header_declares_every_exported_entry_point():
+    """include/dcgan_b200.h is the C ABI: every dcgan_* symbol the library exports is declared there, and
+    everything declared is exported."""
+    import re
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.exists(_lib.lib_path()):
+        pytest.skip("library not built")
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.lib_path()], capture_output=True, text=True).stdout
+    exported = {l.split()[-1] for l in out.splitlines() if l.split() and l.split()[-1].startswith("dcgan_")}
+    header = open(os.path.join(root, "include", "dcgan_b200.h")).read()
+    declared = set(re.findall(r"\b(dcgan_[a-z0-9_]+)\s*\(", header))
+    assert exported == declared, (sorted(exported - declared), sorted(declared - exported))
