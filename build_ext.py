@@ -14,10 +14,11 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(ROOT, "csrc")
 PKG = os.path.join(ROOT, "distributed_tensorflow_for_dcgan_b200")
 LIB = os.path.join(PKG, "lib", "libdcgan_b200.so")
-SOURCES = ["igemm_sm100.cu", "runtime.cu", "bn_act.cu", "heads_optim.cu", "conv_c3.cu", "conv_c3_tc.cu", "comm_sm100.cu"]
+SOURCES = ["igemm_sm100.cu", "igemm2_sm100.cu", "runtime.cu", "bn_act.cu", "heads_optim.cu", "conv_c3.cu", "conv_c3_tc.cu", "comm_sm100.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
-HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(ROOT, "include", "dcgan_b200.h")]
+HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "igemm2.h"),
+           os.path.join(ROOT, "include", "dcgan_b200.h")]
 
 
 def _nvcc() -> str:
@@ -67,5 +68,23 @@ def build(verbose: bool = False, force: bool = False) -> str:
     return LIB
 
 
+def build_harness(name: str = "test_igemm2") -> str:
+    """Stand-alone kernel harness (csrc/<name>.cu) linked against the library objects; runs without torch."""
+    build()
+    objdir = os.path.join(ROOT, "build", "obj")
+    exe = os.path.join(ROOT, "build", name)
+    objs = [os.path.join(objdir, s.replace(".cu", ".o")) for s in SOURCES]
+    src = os.path.join(CSRC, name + ".cu")
+    if _stale(exe, [src] + objs):
+        cmd = [_nvcc()] + [f for f in NVCC_FLAGS if f not in ("-Xcompiler", "-fPIC")] + ["-o", exe, src] + objs + ["-lcuda"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"harness build failed:\n{r.stdout}\n{r.stderr}")
+    return exe
+
+
 if __name__ == "__main__":
     print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))
+    for arg in sys.argv[1:]:
+        if arg.startswith("harness="):
+            print(build_harness(arg.split("=", 1)[1]))

@@ -65,13 +65,16 @@ __device__ __forceinline__ void multimem_st_b64(void* mc, uint2 v) {
 }
 
 // bounded wait until every rank's slot in `mine` has reached `epoch`
-constexpr unsigned kPeerSpinLimit = 1u << 24;
+// polls before a rank gives up on its peers (about 0.7 us each: ~12 s by default); host-settable, because a
+// chief that writes a checkpoint or fills its sample queue between two steps keeps its peers waiting for longer
+static __device__ unsigned g_peer_spin_limit = 1u << 24;
 __device__ __forceinline__ bool wait_all(const unsigned* mine, int world, unsigned epoch, int* err_flag) {
   bool ok = true;
   if ((int)threadIdx.x < world) {
     unsigned spins = 0;
+    const unsigned limit = g_peer_spin_limit;
     while ((int)(ld_acquire_sys(mine + threadIdx.x) - epoch) < 0) {
-      if (++spins > kPeerSpinLimit) {
+      if (++spins > limit) {
         atomicExch(err_flag, (int)kErrPeerTimeout);
         ok = false;
         break;
@@ -114,8 +117,14 @@ rs_adam_ag_kernel(PeerTable peers, float* __restrict__ master, float* __restrict
   }
   const bool ok = wait_all(sig_row(peers.sig[rank], slot, 0), world, epoch, err_flag);
 
-  const float t = (float)counters[0];
-  const float lr_t = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
+  // the bias-corrected step size is evaluated once per block, not by every thread (two powf ~ 300 instructions)
+  __shared__ float s_lr_t;
+  if (threadIdx.x == 0) {
+    const float t = (float)counters[0];
+    s_lr_t = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
+  }
+  __syncthreads();
+  const float lr_t = s_lr_t;
   const float inv_world = 1.f / (float)world;
   // shard of [lo, hi) owned by this rank (multiples of 4 elements)
   const size_t total4 = (hi - lo) / 4;
@@ -362,6 +371,11 @@ static void fill(void** dst, const void* const* src, int world) {
 using namespace dcgan;
 
 extern "C" {
+
+int dcgan_comm_set_peer_spin_limit(unsigned polls) {
+  if (polls < (1u << 10)) polls = 1u << 10;
+  return cudaMemcpyToSymbol(g_peer_spin_limit, &polls, sizeof(unsigned)) == cudaSuccess ? 0 : DCGAN_ERR_DRIVER;
+}
 
 int dcgan_comm_rs_adam_ag(const void* const* grad_ptrs, const void* const* bf16_ptrs, const void* const* sig_ptrs,
                           const void* const* master_ptrs, float* master, float* m, float* v,

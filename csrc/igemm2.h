@@ -1,0 +1,54 @@
+// Internal interface between the C entry points (csrc/igemm_sm100.cu) and the TMA-fed persistent
+// implicit-GEMM kernels (csrc/igemm2_sm100.cu).  Not part of the public ABI (include/dcgan_b200.h).
+#pragma once
+#include <cmath>
+#include <cstddef>
+#include <cuda_runtime.h>
+
+namespace dcgan {
+
+enum { MODE_F = 0, MODE_T = 1, MODE_W = 2 };
+
+struct Igemm2Params {
+  int rH_log2, rW_log2;  // pixel-row space (F: output grid, T: input grid, W: the small grid), powers of two
+  int rows_total;        // NB * rH * rW
+  int gC;                // channels of the gathered (4-D) tensor
+  int Cn;                // F/T: output channels.  W: gathered channels (GEMM N extent)
+  int Cd;                // W: dense channels (GEMM M extent)
+  int num_kb;            // F: 25 * gC / 64.  W: pixels / 64.  T: derived per parity class
+  int m_tiles, n_tiles;  // tile grid (T: per parity class; W: per filter tap)
+  int ksplit;            // K slices per tile
+  int cluster;           // CTAs per thread-block cluster: consecutive M tiles that share (multicast) the filter tile
+  int m_groups;          // ceil(m_tiles / cluster)
+  int total_groups;      // work groups (one per cluster and iteration): tiles / cluster * ksplit
+  int b_mn;              // F: filter is [25][Ck][Cn] (TensorFlow layout) -> MN-major B operand
+  // epilogue
+  void* out;              // F/T: bf16 NHWC.  W: f32 [25][Cn][Cd]
+  const float* bias;      // F/T optional, per out channel
+  int act;                // F/T activation
+  int oH, oW;             // F/T output spatial dims
+  float* stats;           // F/T optional: [groups][2][Cn] += per-channel (sum, sum of squares), pre-activation
+  int stat_group_rows;    // rows per statistics group (multiple of 128)
+  float* partials;        // split-K scratch: [tile][slice][BLOCK_N / 4][128] float4
+  int* counters;          // split-K arrival counters per tile (zero between launches)
+  int* err_flag;          // sticky device error flag (csrc/runtime.cu)
+  const int* mn_variant;  // MN-major descriptor convention switch (bring-up harness only)
+};
+
+// Strided (transposed = 0) or transposed (1) 5x5 / stride-2 conv; see dcgan_conv_fprop* / dcgan_conv_tconv*.
+int igemm2_conv(int transposed, const void* x, const void* w, const float* bias, void* out, int NB, int H, int W,
+                int Cin, int Cout, int act, int block_n, int b_mn, float* stats, int stat_groups,
+                cudaStream_t stream);
+// Filter gradient; see dcgan_conv_wgrad.
+int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd, int splits,
+                 int block_n, cudaStream_t stream);
+// (tile width, K slices) for `tiles_bn64` 64-wide tiles of `kb_per_tile` k-blocks on the persistent grid
+void igemm2_plan(long tiles_bn64, double kb_per_tile, int Cn, int min_kb, int force_bn, int* block_n, int* ksplit);
+
+void igemm2_set_max_ctas(int v);
+void igemm2_set_ksplit(int v);
+void igemm2_set_stage_mode(int v);
+void igemm2_set_cluster(int v);
+int igemm2_set_workspace(void* ptr, size_t bytes);
+
+}  // namespace dcgan

@@ -1,0 +1,868 @@
+// Implicit-GEMM convolution kernels, second generation: BOTH operands arrive by TMA, the CTAs are persistent,
+// the accumulator is double-buffered in TMEM and the epilogue of one tile runs under the main loop of the next.
+//
+// What changed against csrc/igemm_sm100.cu (kept as the A/B reference, dcgan_set_igemm_tuning bit 7):
+//   * The im2col operand is no longer gathered by 128 threads with cp.async.  The NHWC activation tensor is
+//     described to the TMA unit as a 4-D tiled tensor map {C, W, H, N}; a 128-row GEMM tile is a box
+//     {64 channels, bw pixels, bh rows, bn images}.  The filter tap is a shift of the box origin, TensorFlow's
+//     asymmetric SAME padding (1 before / 2 after) is the TMA unit's out-of-bounds zero fill (signed
+//     coordinates), and the stride-2 sampling of the forward conv is the tensor map's element stride {1,2,2,1}.
+//     One elected lane issues one bulk tensor copy per operand and k-block; no address arithmetic in the SM.
+//   * One CTA per SM loops over work items (tile x K slice) with a static round-robin schedule; the smem ring
+//     keeps streaming across tile boundaries, so a short K loop (8-18 k-blocks in the transposed layers) no
+//     longer pays barrier init / TMEM allocation / pipeline fill / epilogue per tile.
+//   * TMEM holds two accumulators (2 x BLOCK_N columns): warps 2-5 drain tile i (tcgen05.ld -> bias / activation /
+//     batch-norm moments -> bf16 stores) while warp 1 already issues the MMAs of tile i+1.
+//   * Split-K is deterministic: every slice stores its f32 partial tile to a scratch buffer, bumps the tile's
+//     arrival counter, and the slice that arrives last adds all partials in slice order and runs the epilogue.
+//     Nobody waits for anybody (no co-residency requirement), and the filter gradients no longer depend on the
+//     order of floating-point atomics.
+//
+// Modes (same math as igemm_sm100.cu; geometry = TensorFlow 5x5 / stride 2 / SAME):
+//   MODE_F  strided conv          = tf.nn.conv2d (distriubted_model.py:183) / data gradient of conv2d_transpose
+//   MODE_T  transposed conv       = tf.nn.conv2d_transpose (distriubted_model.py:200) / data gradient of conv2d;
+//           the four output parity classes (3x3, 3x2, 2x3, 2x2 taps) are work items of ONE launch, longest first
+//   MODE_W  filter gradient       (autodiff of image_train.py:109-112): K = pixels, both operands MN-major
+#include <mutex>
+#include <unordered_map>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+#include "igemm2.h"
+#include "../include/dcgan_b200.h"
+
+namespace dcgan {
+
+namespace {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;
+constexpr int kATileBytes = kBlockM * kBlockK * 2;  // 16 KiB
+constexpr int kThreads = 192;                       // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int kEpiThreads = 128;
+
+template <int BLOCK_N, int STAGES>
+struct Smem2 {
+  static constexpr int kBTileBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+  static constexpr int kBarOffset = STAGES * kStageBytes;  // full[STAGES], empty[STAGES], tfull[2], tempty[2]
+  static constexpr int kMiscOffset = kBarOffset + 256;     // tmem base, abort flag, split-K "last" flag
+  static constexpr int kStatOffset = kMiscOffset + 64;     // [2 accumulators][4 warps][2][BLOCK_N] f32
+  static constexpr int kTotal = kStatOffset + 16 * BLOCK_N * 4 + 1024;  // + slack for the 1024-byte alignment
+  static_assert(2 * STAGES + 4 <= 32, "barrier block is 256 bytes");
+};
+
+struct WorkItem {
+  int m0, n0;    // F/T: first pixel row / first out channel.  W: first dense channel / first gathered channel
+  int tile;      // tile id (scratch slot of the split-K partials)
+  int ks;        // K slice
+  int kb0, nkb;  // k-block range of this slice
+  int ph, pw;    // T: output parity class
+  int tap;       // W: filter tap
+};
+
+// Work item of cluster rank `r` in work group `u`.  A group is `p.cluster` tiles that differ only in their
+// M tile (consecutive M tiles): they walk the same K range against the same filter tile, which is therefore
+// fetched from L2 once per cluster and multicast (F/T).  W runs with clusters of one.
+template <int MODE, int BLOCK_N>
+__device__ __forceinline__ WorkItem decode_work(int u, int r, const Igemm2Params& p) {
+  WorkItem it;
+  it.ks = u % p.ksplit;
+  const int t = u / p.ksplit;
+  it.ph = it.pw = 0;
+  it.tap = 0;
+  int total_kb;
+  if (MODE == MODE_W) {
+    it.tile = t;
+    it.tap = t % 25;  // neighbouring CTAs share the dense operand tile (L2) and differ in the tap
+    const int q = t / 25;
+    it.n0 = (q % p.n_tiles) * BLOCK_N;
+    it.m0 = (q / p.n_tiles) * kBlockM;
+    total_kb = p.num_kb;
+  } else if (MODE == MODE_F) {
+    const int mt = (t % p.m_groups) * p.cluster + r;  // neighbouring clusters share the filter tile as well
+    const int nt = t / p.m_groups;
+    it.m0 = mt * kBlockM;
+    it.n0 = nt * BLOCK_N;
+    it.tile = nt * (p.m_groups * p.cluster) + mt;
+    total_kb = p.num_kb;
+  } else {
+    const int per_class = p.m_groups * p.n_tiles;
+    const int rank = t / per_class;  // 0: 3x3 taps, 1: 3x2, 2: 2x3, 3: 2x2 -- the long K loops are scheduled first
+    const int q = t - rank * per_class;
+    const int mt = (q % p.m_groups) * p.cluster + r;
+    const int nt = q / p.m_groups;
+    it.m0 = mt * kBlockM;
+    it.n0 = nt * BLOCK_N;
+    it.tile = (rank * p.n_tiles + nt) * (p.m_groups * p.cluster) + mt;
+    it.ph = 1 - (rank >> 1);
+    it.pw = 1 - (rank & 1);
+    total_kb = (it.ph ? 3 : 2) * (it.pw ? 3 : 2) * (p.gC / kBlockK);
+  }
+  it.kb0 = (it.ks * total_kb) / p.ksplit;
+  it.nkb = ((it.ks + 1) * total_kb) / p.ksplit - it.kb0;
+  return it;
+}
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// every thread of every CTA in the cluster takes part (non-.aligned forms: callers may be diverged)
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
+}
+
+__device__ __forceinline__ float4 ldcg_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void stcg_f4(float4* p, float4 v) {
+  asm volatile("st.global.cg.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+template <int MODE, int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 4-D NHWC activation tensor
+              const __grid_constant__ CUtensorMap tmap_d,  // dense operand: 2-D (filter, or W: the small activation)
+              const Igemm2Params p) {
+  pdl_launch_dependents();
+  using L = Smem2<BLOCK_N, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + L::kMiscOffset);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+  volatile int* last_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 2);
+  float* stat_smem = reinterpret_cast<float*>(smem + L::kStatOffset);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+
+  const int csize = p.cluster;                                  // CTAs that share (multicast) the filter tile
+  const int crank = (csize > 1) ? (int)cluster_ctarank() : 0;
+  const uint16_t cmask = (uint16_t)((1u << csize) - 1u);
+  const int first_group = blockIdx.x / csize;                   // clusters are consecutive in x
+  const int group_step = gridDim.x / csize;
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], csize);  // every consumer of the cluster releases the slot (multicast B)
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], 4);  // one elected lane of each epilogue warp
+    }
+    *abort_flag = 0;
+    *last_flag = 0;
+    fence_mbar_init();
+    tma_prefetch_desc(&tmap_g);
+    tma_prefetch_desc(&tmap_d);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr_smem, 2 * BLOCK_N);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (csize > 1) cluster_sync_all();  // peers' barriers are initialised before anything is multicast at them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_wait();  // set-up above overlaps the previous kernel's tail; global memory is touched from here on
+
+  const int cpt = p.gC / kBlockK;  // F/T: 64-channel chunks per filter tap
+  const int rW = 1 << p.rW_log2, rH = 1 << p.rH_log2;
+
+  if (warp == 0) {
+    // =================================== TMA producer ==========================================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t phase = 0;
+      bool ok = true;
+      for (int u = first_group; u < p.total_groups && ok; u += group_step) {
+        const WorkItem wi = decode_work<MODE, BLOCK_N>(u, crank, p);
+        // origin of the tile's pixel box (F/T); the box always starts at column 0
+        const int img0 = wi.m0 >> (p.rW_log2 + p.rH_log2);
+        const int h0 = (wi.m0 >> p.rW_log2) & (rH - 1);
+        // (ta, tb, cc): filter-tap row / column index inside the class and channel chunk, advanced like an odometer
+        const int nb = (MODE == MODE_F) ? 5 : (wi.pw ? 3 : 2);
+        int cc = 0, ta = 0, tb = 0;
+        if (MODE != MODE_W) {
+          const int lt0 = wi.kb0 / cpt;
+          cc = wi.kb0 - lt0 * cpt;
+          ta = lt0 / nb;
+          tb = lt0 - ta * nb;
+        }
+        const int kh_w = wi.tap / 5, kw_w = wi.tap - 5 * (wi.tap / 5);
+        for (int kb = 0; kb < wi.nkb; ++kb) {
+          if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+          uint8_t* sA = smem + s * L::kStageBytes;
+          uint8_t* sB = sA + kATileBytes;
+          mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
+          if (MODE == MODE_W) {
+            const int px0 = (wi.kb0 + kb) * kBlockK;
+            tma_load_2d(sA, &tmap_d, &full_bar[s], wi.m0, px0);
+            tma_load_2d(sA + kATileBytes / 2, &tmap_d, &full_bar[s], wi.m0 + 64, px0);
+            const int imgk = px0 >> (p.rW_log2 + p.rH_log2);
+            const int hk = (px0 >> p.rW_log2) & (rH - 1);
+#pragma unroll
+            for (int j = 0; j < BLOCK_N / 64; ++j)
+              tma_load_4d(sB + j * 8192, &tmap_g, &full_bar[s], wi.n0 + 64 * j, kw_w - 1, 2 * hk + kh_w - 1, imgk);
+          } else {
+            int tap;
+            if (MODE == MODE_F) {
+              tma_load_4d(sA, &tmap_g, &full_bar[s], cc * kBlockK, tb - 1, 2 * h0 + ta - 1, img0);
+              tap = ta * 5 + tb;
+            } else {
+              // out[2q+p] takes x[q + (p - i)] through tap k = 2i (p = 1) or 2i+1 (p = 0)
+              tma_load_4d(sA, &tmap_g, &full_bar[s], cc * kBlockK, wi.pw - tb, h0 + wi.ph - ta, img0);
+              const int kh = wi.ph ? 2 * ta : 2 * ta + 1;
+              const int kw = wi.pw ? 2 * tb : 2 * tb + 1;
+              tap = kh * 5 + kw;
+            }
+            if (csize == 1) {
+              if (p.b_mn) {  // TensorFlow layout [tap][Ck][Cn]: 64(k) x 64(n) boxes, one per 64 output channels
+#pragma unroll
+                for (int j = 0; j < BLOCK_N / 64; ++j)
+                  tma_load_2d(sB + j * 8192, &tmap_d, &full_bar[s], wi.n0 + 64 * j, tap * p.gC + cc * kBlockK);
+              } else {
+                tma_load_2d(sB, &tmap_d, &full_bar[s], cc * kBlockK, tap * p.Cn + wi.n0);
+              }
+            } else {
+              // this CTA fetches 1/csize of the filter tile and the TMA unit delivers it to every CTA of the cluster
+              if (p.b_mn) {  // slice of the k rows of every 64 x 64 box
+                const int kr = 64 / csize;
+#pragma unroll
+                for (int j = 0; j < BLOCK_N / 64; ++j)
+                  tma_load_2d_mc(sB + j * 8192 + crank * kr * 128, &tmap_d, &full_bar[s], wi.n0 + 64 * j,
+                                 tap * p.gC + cc * kBlockK + crank * kr, cmask);
+              } else {       // slice of the output-channel rows
+                const int nr = BLOCK_N / csize;
+                tma_load_2d_mc(sB + crank * nr * 128, &tmap_d, &full_bar[s], cc * kBlockK,
+                               tap * p.Cn + wi.n0 + crank * nr, cmask);
+              }
+            }
+            if (++cc == cpt) { cc = 0; if (++tb == nb) { tb = 0; ++ta; } }
+          }
+          if (++s == STAGES) { s = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // =================================== MMA issuer ============================================
+    if (lane == 0) {
+      constexpr bool kMN = (MODE == MODE_W);
+      const bool b_mn = kMN || (p.b_mn != 0);
+      const uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, kMN, b_mn);
+      const bool swap = (kMN || b_mn) && (*p.mn_variant != 0);
+      const uint32_t lbo = kMN ? (swap ? 1024u : 8192u) : 16u;
+      const uint32_t sbo = kMN ? (swap ? 8192u : 1024u) : 1024u;
+      const uint32_t kstep = kMN ? 2048u : 32u;  // bytes per UMMA_K = 16 step
+      const uint32_t lbo_b = b_mn ? (swap ? 1024u : 8192u) : 16u;
+      const uint32_t sbo_b = b_mn ? (swap ? 8192u : 1024u) : 1024u;
+      const uint32_t kstep_b = b_mn ? 2048u : 32u;
+      int s = 0;
+      uint32_t phase = 0;
+      int ti = 0;
+      bool ok = true;
+      for (int u = first_group; u < p.total_groups && ok; u += group_step, ++ti) {
+        const WorkItem wi = decode_work<MODE, BLOCK_N>(u, crank, p);
+        const int a = ti & 1;
+        // the epilogue must have drained this accumulator (two tiles ago)
+        if (!mbar_wait(&tempty_bar[a], ((ti >> 1) & 1) ^ 1, abort_flag, p.err_flag)) break;
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + (uint32_t)(a * BLOCK_N);
+        for (int kb = 0; kb < wi.nkb; ++kb) {
+          if (!mbar_wait(&full_bar[s], phase, abort_flag, p.err_flag)) { ok = false; break; }
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
+          const uint32_t b_addr = a_addr + kATileBytes;
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            const uint64_t da = make_smem_desc_sw128(a_addr + k * kstep, lbo, sbo);
+            const uint64_t db = make_smem_desc_sw128(b_addr + k * kstep_b, lbo_b, sbo_b);
+            umma_bf16(tacc, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          // frees the smem slot once these MMAs retire -- in every CTA of the cluster, whose producers all write it
+          if (csize == 1) umma_commit(&empty_bar[s]);
+          else umma_commit_mc(&empty_bar[s], cmask);
+          if (++s == STAGES) { s = 0; phase ^= 1; }
+        }
+        if (ok) umma_commit(&tfull_bar[a]);  // accumulator complete
+      }
+    }
+  } else {
+    // =================================== epilogue warps ========================================
+    const int et = tid - 64;  // 0..127
+    const int q = warp & 3;   // TMEM lane quadrant this warp may read
+    const int row_in_tile = q * 32 + lane;
+    const bool do_stats = (MODE != MODE_W) && p.stats != nullptr;
+    int ti = 0;
+    bool ok = true;
+    for (int u = first_group; u < p.total_groups && ok; u += group_step, ++ti) {
+      const WorkItem wi = decode_work<MODE, BLOCK_N>(u, crank, p);
+      const int a = ti & 1;
+      if (!mbar_wait(&tfull_bar[a], (ti >> 1) & 1, abort_flag, p.err_flag)) { ok = false; break; }
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (uint32_t)(a * BLOCK_N) + ((uint32_t)(q * 32) << 16);
+
+      // ---- split-K: park the partial tile, the last slice to arrive finishes the tile ----------------
+      bool from_scratch = false;
+      if (p.ksplit > 1) {
+        float4* part = reinterpret_cast<float4*>(p.partials) +
+                       ((size_t)wi.tile * p.ksplit + wi.ks) * (size_t)(BLOCK_N / 4) * kBlockM + row_in_tile;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            stcg_f4(part + (size_t)((c >> 2) + j) * kBlockM,
+                    make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                                __uint_as_float(v[4 * j + 3])));
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[a]);  // the MMA warp may reuse this accumulator
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) {
+          const int old = atomicAdd(p.counters + wi.tile, 1);
+          const int last = (old == p.ksplit - 1) ? 1 : 0;
+          if (last) p.counters[wi.tile] = 0;  // ready for the next launch (stream order)
+          *last_flag = last;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const bool last = (*last_flag != 0);
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // everybody has read the flag before it is rewritten
+        if (!last) continue;
+        __threadfence();
+        from_scratch = true;
+      }
+      const float4* part0 = reinterpret_cast<const float4*>(p.partials) +
+                            (size_t)wi.tile * p.ksplit * (size_t)(BLOCK_N / 4) * kBlockM + row_in_tile;
+      // one 32-column chunk of this thread's accumulator row, from TMEM or as the ordered sum of the K slices
+      auto load_chunk = [&](int c, float (&f)[32]) {
+        if (!from_scratch) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = 0.f;
+          for (int sidx = 0; sidx < p.ksplit; ++sidx) {
+            const float4* ps = part0 + (size_t)sidx * (size_t)(BLOCK_N / 4) * kBlockM + (size_t)(c >> 2) * kBlockM;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 t = ldcg_f4(ps + (size_t)j * kBlockM);
+              f[4 * j] += t.x; f[4 * j + 1] += t.y; f[4 * j + 2] += t.z; f[4 * j + 3] += t.w;
+            }
+          }
+        }
+      };
+
+      if (MODE != MODE_W) {
+        const int R = wi.m0 + row_in_tile;
+        const bool valid = R < p.rows_total;
+        __nv_bfloat16* orow = nullptr;
+        if (valid) {
+          if (MODE == MODE_F) {
+            orow = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)R * p.Cn + wi.n0;
+          } else {
+            const int qw = R & (rW - 1);
+            const int qh = (R >> p.rW_log2) & (rH - 1);
+            const int n = R >> (p.rW_log2 + p.rH_log2);
+            orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
+                   ((size_t)((n * p.oH + 2 * qh + wi.ph) * p.oW + 2 * qw + wi.pw)) * p.Cn + wi.n0;
+          }
+        }
+        float* ssm = stat_smem + a * (8 * BLOCK_N);
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N; c += 32) {
+          float f[32];
+          load_chunk(c, f);
+          if (p.bias != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + wi.n0 + c + j));
+              f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
+            }
+          }
+          if (valid) {
+            uint32_t packed[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              packed[j] = pack_bf16x2(apply_act(f[2 * j], p.act), apply_act(f[2 * j + 1], p.act));
+            uint4* dst = reinterpret_cast<uint4*>(orow + c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+          }
+          if (do_stats) {  // batch-norm moments of this tile, reduced over the warp's 32 rows
+            float sq[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              f[j] = valid ? f[j] : 0.f;
+              sq[j] = f[j] * f[j];
+            }
+            const float s1 = warp_transpose_reduce32(f);
+            const float s2 = warp_transpose_reduce32(sq);
+            ssm[(q * 2) * BLOCK_N + c + lane] = s1;
+            ssm[(q * 2 + 1) * BLOCK_N + c + lane] = s2;
+          }
+        }
+        if (!from_scratch) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty_bar[a]);
+        }
+        if (do_stats) {
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          float* gs = p.stats + (size_t)(wi.m0 / p.stat_group_rows) * 2 * p.Cn + wi.n0;
+          // (a tile that only pads the last cluster group has no rows and no statistics group)
+          for (int i = et; i < BLOCK_N && wi.m0 < p.rows_total; i += kEpiThreads) {
+            float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+            for (int ww = 0; ww < 4; ++ww) {
+              t1 += ssm[(ww * 2) * BLOCK_N + i];
+              t2 += ssm[(ww * 2 + 1) * BLOCK_N + i];
+            }
+            atomicAdd(gs + i, t1);
+            atomicAdd(gs + p.Cn + i, t2);
+          }
+          // the other statistics buffer is used by the next tile; this one is rewritten two tiles from now,
+          // after every thread has passed the next tile's barrier
+        }
+      } else {
+        // dW[tap][n0 + col][m0 + row] += acc: one writer per element (split-K slices were summed in order above)
+        float* obase = reinterpret_cast<float*>(p.out) + (size_t)wi.tap * p.Cn * p.Cd + (wi.m0 + row_in_tile);
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N; c += 32) {
+          float f[32];
+          load_chunk(c, f);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) atomicAdd(obase + (size_t)(wi.n0 + c + j) * p.Cd, f[j]);
+        }
+        if (!from_scratch) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty_bar[a]);
+        }
+      }
+    }
+  }
+
+  // ---- teardown ---------------------------------------------------------------------------------
+  tc_fence_before();
+  __syncthreads();
+  if (csize > 1) cluster_sync_all();  // no CTA leaves while a peer may still multicast into it or signal its barriers
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
+}
+
+// =================================================================================================
+// host side
+// =================================================================================================
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr;
+  uint64_t d[4];
+  uint32_t box[4];
+  uint32_t stride, rank;
+  int dev;
+  bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < sizeof(MapKey) / 8; ++i) h = (h ^ w[i]) * 1099511628211ull;
+    return (size_t)h;
+  }
+};
+static_assert(sizeof(MapKey) % 8 == 0, "hashed as 64-bit words");
+
+std::mutex g_map_mu;
+std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_map_cache;
+constexpr size_t kMapCacheLimit = 4096;  // the engine's buffers are static (a few dozen maps); callers that feed
+                                         // fresh tensors every call would otherwise grow the cache without bound
+
+int cached_encode(const MapKey& key, const cuuint64_t* dims, const cuuint64_t* strides, const cuuint32_t* box,
+                  const cuuint32_t* estr, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lock(g_map_mu);
+  auto it = g_map_cache.find(key);
+  if (it != g_map_cache.end()) { *out = it->second; return 0; }
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return DCGAN_ERR_DRIVER;
+  CUtensorMap m;
+  CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, key.rank, const_cast<void*>(key.ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return DCGAN_ERR_DRIVER;
+  if (g_map_cache.size() >= kMapCacheLimit) g_map_cache.clear();
+  g_map_cache.emplace(key, m);
+  *out = m;
+  return 0;
+}
+
+int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev;
+}
+
+// 2-D row-major bf16 [rows][cols], box [box_r][box_c]
+int tmap_2d(const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_r, uint32_t box_c, CUtensorMap* out) {
+  MapKey key;
+  std::memset(&key, 0, sizeof key);
+  key.ptr = ptr; key.d[0] = cols; key.d[1] = rows; key.box[0] = box_c; key.box[1] = box_r;
+  key.stride = 1; key.rank = 2; key.dev = current_device();
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {box_c, box_r};
+  cuuint32_t estr[2] = {1, 1};
+  return cached_encode(key, dims, strides, box, estr, out);
+}
+
+// 4-D NHWC bf16 activation tensor {C, W, H, N}; the box takes 64 channels of bw x bh x bn pixels, sampling every
+// `stride`-th pixel in x and y (the box extent passed to the driver is count * stride, see cuTensorMapEncodeTiled)
+int tmap_nhwc(const void* ptr, int N, int H, int W, int C, int bw, int bh, int bn, int stride, CUtensorMap* out) {
+  if (bw * stride > 256 || bh * stride > 256 || bn > 256) return DCGAN_ERR_SHAPE;
+  MapKey key;
+  std::memset(&key, 0, sizeof key);
+  key.ptr = ptr;
+  key.d[0] = (uint64_t)C; key.d[1] = (uint64_t)W; key.d[2] = (uint64_t)H; key.d[3] = (uint64_t)N;
+  key.box[0] = 64; key.box[1] = (uint32_t)bw; key.box[2] = (uint32_t)bh; key.box[3] = (uint32_t)bn;
+  key.stride = (uint32_t)stride; key.rank = 4; key.dev = current_device();
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)(bw * stride), (cuuint32_t)(bh * stride), (cuuint32_t)bn};
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  return cached_encode(key, dims, strides, box, estr, out);
+}
+
+// `rows` consecutive pixels (x fastest, then y, then image) of a rH x rW grid as a box; every extent a power of two
+bool pixel_box(int rows, int rH, int rW, int* bw, int* bh, int* bn) {
+  if (rW > rows || rows % rW) return false;
+  *bw = rW;
+  if (rH * rW >= rows) {
+    *bh = rows / rW;
+    *bn = 1;
+    return rH % *bh == 0;
+  }
+  *bh = rH;
+  *bn = rows / (rH * rW);
+  return rows % (rH * rW) == 0;
+}
+
+// ---- split-K scratch ------------------------------------------------------------------------------------
+constexpr size_t kCounterBytes = 64 * 1024;            // 16384 tile counters (zero between launches)
+constexpr size_t kDefaultScratch = 48u * 1024 * 1024;  // default scratch per device, allocated on first need
+struct Workspace { void* ptr = nullptr; size_t bytes = 0; };
+thread_local Workspace t_ws;                            // set by dcgan_set_workspace
+std::mutex g_ws_mu;
+Workspace g_default_ws[64];
+
+int get_workspace(Workspace* out) {
+  if (t_ws.ptr != nullptr) { *out = t_ws; return 0; }
+  const int dev = current_device();
+  if (dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
+  std::lock_guard<std::mutex> lock(g_ws_mu);
+  if (g_default_ws[dev].ptr == nullptr) {
+    void* ptr = nullptr;
+    // not possible inside a stream capture: callers that capture graphs either run one step before capturing
+    // (the engine does) or hand over their own buffer with dcgan_set_workspace
+    if (cudaMalloc(&ptr, kDefaultScratch) != cudaSuccess) { cudaGetLastError(); return DCGAN_ERR_DRIVER; }
+    if (cudaMemset(ptr, 0, kCounterBytes) != cudaSuccess) { cudaFree(ptr); return DCGAN_ERR_DRIVER; }
+    g_default_ws[dev].ptr = ptr;
+    g_default_ws[dev].bytes = kDefaultScratch;
+  }
+  *out = g_default_ws[dev];
+  return 0;
+}
+
+int num_sms() {
+  static int sms[64] = {0};
+  const int dev = current_device();
+  if (dev < 0 || dev >= 64) return 148;
+  if (sms[dev] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    sms[dev] = v;
+  }
+  return sms[dev];
+}
+
+int g_max_ctas = 0;        // 0 = one CTA per SM
+int g_force_ksplit2 = 0;   // 0 = chosen per layer
+int g_stage_override = 0;  // 0 = deepest ring that fits
+int g_cluster = 0;         // 0 = chosen per layer; 1, 2, 4 = forced
+
+template <int MODE, int BLOCK_N, int STAGES>
+int launch2(const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p, int grid, cudaStream_t stream) {
+  using L = Smem2<BLOCK_N, STAGES>;
+  auto kern = igemm2_kernel<MODE, BLOCK_N, STAGES>;
+  static bool attr_done[64] = {false};  // per instantiation and device
+  const int dev = current_device();
+  if (dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
+  if (!attr_done[dev]) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal) != cudaSuccess)
+      return DCGAN_ERR_LAUNCH;
+    attr_done[dev] = true;
+  }
+  if (p.cluster > 1) {
+    // persistent clusters: never launch more than can be resident at once (a cluster that waits for a free GPC
+    // slot would only start when the whole first wave has finished)
+    static int max_clusters[64][9] = {{0}};
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = L::kTotal;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = p.cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (max_clusters[dev][p.cluster] == 0) {
+      int n = 0;
+      cfg.gridDim = dim3(num_sms() / p.cluster * p.cluster);
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) { cudaGetLastError(); n = 1; }
+      max_clusters[dev][p.cluster] = n;
+    }
+    int clusters = grid / p.cluster;
+    if (clusters > max_clusters[dev][p.cluster]) clusters = max_clusters[dev][p.cluster];
+    cfg.gridDim = dim3(clusters * p.cluster);
+    return cudaLaunchKernelEx(&cfg, kern, tg, td, p) == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+  }
+  launch_k(kern, dim3(grid), dim3(kThreads), L::kTotal, stream, tg, td, p);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+template <int MODE>
+int dispatch2(int block_n, const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p, int grid,
+              cudaStream_t st) {
+  const bool shallow = g_stage_override == 1;  // half-depth rings (two CTAs of different kernels can share an SM)
+  switch (block_n) {
+    case 64: return shallow ? launch2<MODE, 64, 4>(tg, td, p, grid, st) : launch2<MODE, 64, 8>(tg, td, p, grid, st);
+    case 128: return shallow ? launch2<MODE, 128, 3>(tg, td, p, grid, st) : launch2<MODE, 128, 6>(tg, td, p, grid, st);
+    case 256: return launch2<MODE, 256, 4>(tg, td, p, grid, st);
+    default: return DCGAN_ERR_SHAPE;
+  }
+}
+
+}  // namespace
+
+void igemm2_set_max_ctas(int v) { g_max_ctas = v > 0 ? v : 0; }
+void igemm2_set_ksplit(int v) { g_force_ksplit2 = (v >= 1 && v <= 16) ? v : 0; }
+void igemm2_set_stage_mode(int v) { g_stage_override = v; }
+void igemm2_set_cluster(int v) { g_cluster = (v == 1 || v == 2 || v == 4) ? v : 0; }
+
+int igemm2_set_workspace(void* ptr, size_t bytes) {
+  if (ptr != nullptr && bytes < kCounterBytes + (1u << 20)) return DCGAN_ERR_LIMIT;
+  t_ws.ptr = ptr;
+  t_ws.bytes = ptr ? bytes : 0;
+  return 0;
+}
+
+// Cost model behind the (tile width, split-K) choice, in SM cycles.  A k-block costs the slower of its MMAs
+// (128 x bn x 64 MACs at 8192 MACs per cycle and SM) and its bytes from L2 at the per-SM share of the fabric;
+// a work item adds a fixed cost (epilogue tail, scheduling) plus the partial-tile traffic when K is split.
+static double plan_cost(long tiles, double kb_per_tile, int bn, int ks, int ctas) {
+  const double kBytesPerCycle = 36.0;  // measured-order L2 -> SM rate per SM with every SM loading
+  const double t_kb = fmax(2.0 * bn, (kATileBytes + bn * 128.0) / kBytesPerCycle);
+  const double part = (ks > 1) ? (128.0 * bn * 4.0 * 2.0) / kBytesPerCycle + 1500.0 : 0.0;
+  const double item = (kb_per_tile / ks) * t_kb + 1200.0 + part;
+  const long items = tiles * ks;
+  const long waves = (items + ctas - 1) / ctas;
+  return (double)waves * item;
+}
+
+void igemm2_plan(long tiles_bn64, double kb_per_tile, int Cn, int min_kb, int force_bn, int* block_n, int* ksplit) {
+  const int ctas = g_max_ctas > 0 ? g_max_ctas : num_sms();
+  double best = 1e30;
+  *block_n = -1;
+  *ksplit = 1;
+  const int cands[3] = {256, 128, 64};
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cands[i];
+    if (Cn % bn) continue;
+    if (force_bn > 0 && bn != force_bn) continue;
+    const long tiles = tiles_bn64 / (bn / 64);
+    for (int ks = 1; ks <= 16; ++ks) {
+      if (g_force_ksplit2 > 0 && ks != g_force_ksplit2) continue;
+      if (g_force_ksplit2 == 0 && ks > 8) break;
+      // every slice keeps at least four k-blocks (a forced factor only has to leave one)
+      if (ks > 1 && min_kb / ks < (g_force_ksplit2 > 0 ? 1 : 4)) break;
+      const double c = plan_cost(tiles, kb_per_tile, bn, ks, ctas);
+      if (c < best) { best = c; *block_n = bn; *ksplit = ks; }
+    }
+  }
+  if (*block_n < 0 && g_force_ksplit2 > 0) {  // forced factor too large for this layer: fall back to the free choice
+    const int keep = g_force_ksplit2;
+    g_force_ksplit2 = 0;
+    igemm2_plan(tiles_bn64, kb_per_tile, Cn, min_kb, force_bn, block_n, ksplit);
+    g_force_ksplit2 = keep;
+  }
+}
+
+static int ilog2_exact(int v) {
+  int l = 0;
+  while ((1 << l) < v) ++l;
+  return ((1 << l) == v) ? l : -1;
+}
+
+static int attach_scratch(Igemm2Params* p, long tiles, int block_n) {
+  p->partials = nullptr;
+  p->counters = nullptr;
+  if (p->ksplit <= 1) return 0;
+  Workspace ws;
+  int rc = get_workspace(&ws);
+  if (rc) return rc;
+  const size_t need = kCounterBytes + (size_t)tiles * p->ksplit * kBlockM * block_n * 4;
+  if (tiles > (long)(kCounterBytes / 4) || need > ws.bytes) { p->ksplit = 1; return 0; }  // too big: do not split
+  p->counters = reinterpret_cast<int*>(ws.ptr);
+  p->partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ws.ptr) + kCounterBytes);
+  return 0;
+}
+
+int igemm2_conv(int transposed, const void* x, const void* w, const float* bias, void* out, int NB, int H, int W,
+                int Cin, int Cout, int act, int block_n, int b_mn, float* stats, int stat_groups,
+                cudaStream_t stream) {
+  if (Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
+  if (!transposed && ((H & 1) || (W & 1))) return DCGAN_ERR_SHAPE;
+  if (transposed && b_mn) return DCGAN_ERR_SHAPE;
+  const int rH = transposed ? H : H / 2, rW = transposed ? W : W / 2;
+  const int lh = ilog2_exact(rH), lw = ilog2_exact(rW);
+  if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;
+  int bw, bh, bn_img;
+  if (!pixel_box(kBlockM, rH, rW, &bw, &bh, &bn_img)) return DCGAN_ERR_SHAPE;
+  Igemm2Params p{};
+  p.err_flag = error_flag_ptr();
+  p.mn_variant = mn_variant_ptr();
+  if (!p.err_flag || !p.mn_variant) return DCGAN_ERR_DRIVER;
+  p.rH_log2 = lh; p.rW_log2 = lw;
+  p.rows_total = NB * rH * rW;
+  p.gC = Cin; p.Cn = Cout; p.Cd = 0;
+  p.b_mn = b_mn;
+  p.out = out; p.bias = bias; p.act = act;
+  p.oH = transposed ? 2 * H : rH; p.oW = transposed ? 2 * W : rW;
+  if (stats != nullptr) {
+    if (stat_groups < 1 || p.rows_total % stat_groups || (p.rows_total / stat_groups) % kBlockM) return DCGAN_ERR_SHAPE;
+    p.stats = stats;
+    p.stat_group_rows = p.rows_total / stat_groups;
+  }
+  const int cpt = Cin / 64;
+  const int mt = (p.rows_total + kBlockM - 1) / kBlockM;
+  const int classes = transposed ? 4 : 1;
+  const int min_kb = transposed ? 4 * cpt : 25 * cpt;
+  const double avg_kb = transposed ? 6.25 * cpt : 25.0 * cpt;
+  p.num_kb = transposed ? 0 : 25 * cpt;
+  int ks;
+  igemm2_plan((long)mt * (Cout / 64) * classes, avg_kb, Cout, min_kb, block_n > 0 ? block_n : 0, &block_n, &ks);
+  if (block_n <= 0 || Cout % block_n) return DCGAN_ERR_SHAPE;
+  p.ksplit = ks;
+  p.m_tiles = mt;
+  p.n_tiles = Cout / block_n;
+  // CTAs of a cluster take consecutive M tiles and share the filter tile through TMA multicast
+  int cl = g_cluster > 0 ? g_cluster : 2;
+  while (cl > 1 && cl > mt) cl >>= 1;
+  p.cluster = cl;
+  p.m_groups = (mt + cl - 1) / cl;
+  const long tiles = (long)p.m_groups * cl * p.n_tiles * classes;  // including the tiles that pad the last group
+  int rc = attach_scratch(&p, tiles, block_n);
+  if (rc) return rc;
+  p.total_groups = (int)((long)p.m_groups * p.n_tiles * classes * p.ksplit);
+  CUtensorMap tg, td;
+  rc = tmap_nhwc(x, NB, H, W, Cin, bw, bh, bn_img, transposed ? 1 : 2, &tg);
+  if (rc) return rc;
+  rc = b_mn ? tmap_2d(w, (uint64_t)25 * Cin, Cout, 64 / cl, 64, &td)
+            : tmap_2d(w, (uint64_t)25 * Cout, Cin, block_n / cl, 64, &td);
+  if (rc) return rc;
+  int ctas = g_max_ctas > 0 ? g_max_ctas : num_sms();
+  if (ctas < cl) ctas = cl;
+  ctas = ctas / cl * cl;
+  const long want = (long)p.total_groups * cl;
+  const int grid = want < ctas ? (int)want : ctas;
+  return transposed ? dispatch2<MODE_T>(block_n, tg, td, p, grid, stream)
+                    : dispatch2<MODE_F>(block_n, tg, td, p, grid, stream);
+}
+
+int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd, int splits,
+                 int block_n, cudaStream_t stream) {
+  if (Cg % 64 || Cd % 128) return DCGAN_ERR_SHAPE;
+  const int lh = ilog2_exact(Hs), lw = ilog2_exact(Ws);
+  if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;
+  const int rows = NB * Hs * Ws;
+  if (rows % kBlockK) return DCGAN_ERR_SHAPE;
+  int bw, bh, bn_img;
+  if (!pixel_box(kBlockK, Hs, Ws, &bw, &bh, &bn_img)) return DCGAN_ERR_SHAPE;
+  const int total_kb = rows / kBlockK;
+  Igemm2Params p{};
+  p.err_flag = error_flag_ptr();
+  p.mn_variant = mn_variant_ptr();
+  if (!p.err_flag || !p.mn_variant) return DCGAN_ERR_DRIVER;
+  p.rH_log2 = lh; p.rW_log2 = lw;
+  p.rows_total = rows;
+  p.gC = Cg; p.Cn = Cg; p.Cd = Cd;
+  p.num_kb = total_kb;
+  p.out = dw;
+  int ks;
+  if (block_n <= 0 && splits > 0) block_n = (Cg % 256 == 0) ? 256 : (Cg % 128 == 0 ? 128 : 64);
+  if (splits > 0) {
+    if (Cg % block_n) return DCGAN_ERR_SHAPE;
+    ks = splits < total_kb ? splits : total_kb;
+  } else {
+    igemm2_plan((long)25 * (Cd / kBlockM) * (Cg / 64), (double)total_kb, Cg, total_kb, block_n > 0 ? block_n : 0,
+                &block_n, &ks);
+  }
+  if (block_n <= 0 || Cg % block_n) return DCGAN_ERR_SHAPE;
+  p.ksplit = ks;
+  p.m_tiles = Cd / kBlockM;
+  p.n_tiles = Cg / block_n;
+  p.cluster = 1;
+  p.m_groups = p.m_tiles;
+  const long tiles = (long)25 * p.m_tiles * p.n_tiles;
+  int rc = attach_scratch(&p, tiles, block_n);
+  if (rc) return rc;
+  p.total_groups = (int)(tiles * p.ksplit);
+  CUtensorMap tg, td;
+  rc = tmap_nhwc(big, NB, 2 * Hs, 2 * Ws, Cg, bw, bh, bn_img, 2, &tg);
+  if (rc) return rc;
+  rc = tmap_2d(small, (uint64_t)rows, Cd, 64, 64, &td);
+  if (rc) return rc;
+  const int ctas = g_max_ctas > 0 ? g_max_ctas : num_sms();
+  const int grid = p.total_groups < ctas ? p.total_groups : ctas;
+  return dispatch2<MODE_W>(block_n, tg, td, p, grid, stream);
+}
+
+}  // namespace dcgan

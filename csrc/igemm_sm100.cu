@@ -32,11 +32,10 @@
 #include <cstring>
 
 #include "common.cuh"
+#include "igemm2.h"
 #include "../include/dcgan_b200.h"
 
 namespace dcgan {
-
-enum { MODE_F = 0, MODE_T = 1, MODE_W = 2 };
 
 struct IgemmParams {
   const __nv_bfloat16* g;  // gathered tensor, NHWC bf16
@@ -820,7 +819,8 @@ static int launch(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cuda
 }
 
 // tuning knob (bring-up / profiling): bit 0 = two CTAs per SM with shallower stage rings
-static int g_igemm_tuning = 1;  // bit 3 (8): parity-fused transposed conv for large-M layers; bit 4: its N=128 tile
+static int g_igemm_tuning = 1;  // bit 7 (128): first-generation kernels of this file (cp.async gather) instead of
+                                // the TMA-fed persistent kernels of igemm2_sm100.cu; bit 3 (8): parity-fused transposed conv for large-M layers; bit 4: its N=128 tile
                                 // bit 5 (32): no cluster split-K; bit 6 (64): transposed conv parity classes in
                                 // natural order instead of longest-first
 static int g_igemm_ksplit = 0;  // 0 = choose per layer; 1, 2, 4 = forced (tests / profiling)
@@ -895,7 +895,15 @@ using namespace dcgan;
 extern "C" {
 
 void dcgan_set_igemm_tuning(int v) { g_igemm_tuning = v; }
-void dcgan_set_igemm_ksplit(int v) { g_igemm_ksplit = (v == 1 || v == 2 || v == 4) ? v : 0; }
+void dcgan_set_igemm_ksplit(int v) {
+  g_igemm_ksplit = (v == 1 || v == 2 || v == 4) ? v : 0;
+  igemm2_set_ksplit(v);
+}
+void dcgan_set_igemm_max_ctas(int v) { igemm2_set_max_ctas(v); }
+void dcgan_set_igemm_stage_mode(int v) { igemm2_set_stage_mode(v); }
+void dcgan_set_igemm_cluster(int v) { igemm2_set_cluster(v); }
+int dcgan_set_workspace(void* ptr, size_t bytes) { return igemm2_set_workspace(ptr, bytes); }
+static inline bool use_v2() { return (g_igemm_tuning & 128) == 0; }
 void dcgan_set_wgrad_cta_target(int v) { g_wgrad_cta_target = v > 0 ? v : 148; }
 
 // Host-only view of the launch plan of a strided (transposed = 0) or transposed (1) conv: tile width, split-K
@@ -923,6 +931,8 @@ int dcgan_debug_plan_conv(int transposed, int NB, int H, int W, int Cin, int Cou
 static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                            int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream,
                            float* stats = nullptr, int stat_groups = 1) {
+  if (use_v2())
+    return igemm2_conv(0, x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n, b_mn, stats, stat_groups, stream);
   if ((H & 1) || (W & 1) || Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
   if ((long)NB * H * W * Cin >= (1L << 31)) return DCGAN_ERR_SHAPE;  // the gather uses 32-bit element offsets
   const int oH = H / 2, oW = W / 2;
@@ -976,6 +986,9 @@ int dcgan_conv_fprop_kn_stats(const void* x, const void* w_kn, const float* bias
 static int conv_tconv_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                            int Cin, int Cout, int act, int block_n, cudaStream_t stream, float* stats,
                            int stat_groups) {
+  if (use_v2())
+    return igemm2_conv(1, x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n < 0 ? 0 : block_n, 0, stats,
+                       stat_groups, stream);
   if (Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
   if ((long)NB * H * W * Cin >= (1L << 31)) return DCGAN_ERR_SHAPE;  // the gather uses 32-bit element offsets
   const int lh = ilog2_exact(H), lw = ilog2_exact(W);
@@ -1034,6 +1047,7 @@ int dcgan_conv_tconv_stats(const void* x, const void* w_nk, const float* bias, v
 
 int dcgan_conv_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd,
                      int splits, int block_n, cudaStream_t stream) {
+  if (use_v2()) return igemm2_wgrad(big, small, dw, NB, Hs, Ws, Cg, Cd, splits, block_n, stream);
   if (Cg % 64 || Cd % 128) return DCGAN_ERR_SHAPE;
   const int lh = ilog2_exact(Hs), lw = ilog2_exact(Ws);
   if (lh < 0 || lw < 0) return DCGAN_ERR_SHAPE;

@@ -66,6 +66,13 @@ int dcgan_last_device_error(void) {
   return v;
 }
 
+int dcgan_copy_error_flag(int* host_dst, cudaStream_t stream) {
+  int* flag = dcgan::error_flag_ptr();
+  if (!flag || !host_dst) return DCGAN_ERR_DRIVER;
+  return cudaMemcpyAsync(host_dst, flag, sizeof(int), cudaMemcpyDeviceToHost, stream) == cudaSuccess
+             ? 0 : DCGAN_ERR_LAUNCH;
+}
+
 void dcgan_set_mn_desc_variant(int v) { cudaMemcpyToSymbol(dcgan::g_mn_desc_variant, &v, sizeof(int)); }
 
 }  // extern "C"

@@ -41,9 +41,11 @@ IMAGE_NUM = 107766 * 3
 NUM_EXAMPLES_PER_EPOCH_FOR_TRAIN = 107766  # image_input.py:14
 
 
-def steps_per_epoch(batch_size: int = 64) -> int:
-    """``step_per_epoch = image_num / batch_size`` under Python-2 integer division = 5051."""
-    return IMAGE_NUM // batch_size
+def steps_per_epoch(batch_size: int = 64, train_size: float = float("inf")) -> int:
+    """``step_per_epoch = image_num / batch_size`` under Python-2 integer division = 5051.  A finite
+    ``--train_size`` (declared but never read by the reference, image_train.py:14) caps the image count."""
+    n = IMAGE_NUM if train_size == float("inf") else max(int(min(IMAGE_NUM, train_size)), batch_size)
+    return n // batch_size
 
 
 WIDE_128 = ModelConfig(output_size=128, gf_dim=128, df_dim=128)

@@ -196,6 +196,16 @@ class DCGANEngine:
         self.split_d_forward = self.wgrad_overlap and os.environ.get("DCGAN_SPLIT_D_FORWARD", "0") != "0"
         self.side = torch.cuda.Stream(self.device)
         self._side_used = False
+        # split-K scratch of the implicit-GEMM kernels (arrival counters + partial tiles): the chain and the side
+        # stream run concurrently, so each gets its own (ops/_lib.set_workspace is per host thread)
+        ws_bytes = 64 * 1024 * 1024 + 65536
+        self._ws_main = torch.zeros(ws_bytes, dtype=torch.uint8, device=dev)
+        self._ws_side = torch.zeros(ws_bytes, dtype=torch.uint8, device=dev)
+        # set by callers that run a forward pass on ONE rank only (the chief's sample-time evaluation): cross-replica
+        # batch-norm statistics are a collective and must not be entered alone
+        self._local_bn_only = False
+        # 1.0 freezes the EMA shadows for a pass (second D pass of the alternating update)
+        self._ema_decay_override: Optional[float] = None
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self.refresh_compute_weights()
 
@@ -225,13 +235,17 @@ class DCGANEngine:
         if train:
             if not stats_done:
                 K.bn_stats(x2, st["sums"], G)
-            if self.comm is not None and getattr(self.comm, "sync_bn", False):
+            if self._sync_bn_active():
                 self.comm.allreduce_bn(st["sums"])
+            decay = self.cfg.bn_momentum if self._ema_decay_override is None else self._ema_decay_override
             K.bn_apply(x2, y2, st["sums"], p[f"{name}/gamma"], p[f"{name}/beta"], st["saved"], st["ema_mean"],
-                       st["ema_var"], G, st["act"], self.cfg.bn_eps, self.cfg.bn_momentum)
+                       st["ema_var"], G, st["act"], self.cfg.bn_eps, decay)
         else:
             K.bn_apply(x2, y2, st["sums"], p[f"{name}/gamma"], p[f"{name}/beta"], None, st["ema_mean"],
                        st["ema_var"], 1, st["act"], self.cfg.bn_eps, self.cfg.bn_momentum, use_ema=True)
+
+    def _sync_bn_active(self) -> bool:
+        return (self.comm is not None and getattr(self.comm, "sync_bn", False) and not self._local_bn_only)
 
     def generator_forward(self, train: bool = True) -> torch.Tensor:
         """z -> images; training mode writes into the fake half of ``d_in``."""
@@ -306,7 +320,7 @@ class DCGANEngine:
         slabs, G = st["slabs"], st["groups"]
         K.bn_bwd_reduce(da.view(-1, C), pre.view(-1, C), st["saved"], p[f"{name}/gamma"], p[f"{name}/beta"],
                         st["red"], slabs, G, st["act"])
-        if self.comm is not None and getattr(self.comm, "sync_bn", False):
+        if self._sync_bn_active():
             self.comm.allreduce_bn(st["red"])
         K.bn_bwd_apply(da.view(-1, C), pre.view(-1, C), dpre.view(-1, C), st["saved"], p[f"{name}/gamma"],
                        p[f"{name}/beta"], st["red"], g[f"{name}/gamma"], g[f"{name}/beta"], slabs, G, G, st["act"])
@@ -318,11 +332,16 @@ class DCGANEngine:
         if not self.wgrad_overlap:
             yield
             return
+        from .ops import _lib
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.device))
         self.side.wait_event(ev)
-        with torch.cuda.stream(self.side):
-            yield
+        _lib.set_workspace(self._ws_side)
+        try:
+            with torch.cuda.stream(self.side):
+                yield
+        finally:
+            _lib.set_workspace(self._ws_main)
         self._side_used = True
 
     def side_event(self) -> Optional[torch.cuda.Event]:
@@ -412,6 +431,14 @@ class DCGANEngine:
 
     def step_body(self) -> None:
         """Everything of one training iteration that runs on the device, in stream order."""
+        from .ops import _lib
+        _lib.set_workspace(self._ws_main)
+        try:
+            self._step_body()
+        finally:
+            _lib.set_workspace(None)
+
+    def _step_body(self) -> None:
         B = self.B
         # gradients are not touched before the backward pass: their memset runs beside the forward pass
         with self._off_critical_path():
@@ -458,7 +485,16 @@ class DCGANEngine:
         else:
             # D first, then G against the updated D (carpedm20-style alternation)
             self.optimizer_step("d")
-            self.discriminator_forward()
+            # The second D pass starts from clean reduction buffers: the batch-norm sums / backward reductions and
+            # the generator-side gradients that the first pass already touched all accumulate (+=).  The EMA shadows
+            # are not advanced a second time (CPUTrainer._alternating_step does the same).
+            self._scratch.zero_()
+            self.grads[:self.arena.g_end].zero_()
+            self._ema_decay_override = 1.0
+            try:
+                self.discriminator_forward()
+            finally:
+                self._ema_decay_override = None
             K.gan_loss(self.logits, self.losses[:3], self.dlogit, self.probs, None, B, 1.0, False)
             self.discriminator_backward()
             self.generator_backward()
@@ -506,6 +542,7 @@ class DCGANEngine:
             st.host_loss = [torch.empty(self.losses.numel(), dtype=self.losses.dtype).pin_memory() for _ in range(2)]
             st.host_cnt = [torch.empty(self.counters.numel(), dtype=self.counters.dtype).pin_memory()
                            for _ in range(2)]
+            st.host_err = [torch.zeros(1, dtype=torch.int32).pin_memory() for _ in range(2)]
             st.ev_in = [torch.cuda.Event() for _ in range(2)]
             st.ev_consumed = [torch.cuda.Event() for _ in range(2)]
             st.ev_out = [torch.cuda.Event() for _ in range(2)]
@@ -541,6 +578,10 @@ class DCGANEngine:
         self.run_step()
         st.host_loss[slot].copy_(self.losses, non_blocking=True)
         st.host_cnt[slot].copy_(self.counters, non_blocking=True)
+        # the sticky device error flag travels with the fetches: a timed-out peer wait makes a rank skip its
+        # shard's update, which must stop the job instead of silently desynchronising the replicas
+        from .ops import _lib
+        _lib.load().dcgan_copy_error_flag(st.host_err[slot].data_ptr(), _lib.stream_handle())
         st.ev_out[slot].record(main)
         st.n += 1
         return st.n - 1
@@ -553,6 +594,11 @@ class DCGANEngine:
             raise ValueError(f"ticket {ticket} is no longer held (last submitted: {st.n - 1})")
         slot = ticket & 1
         st.ev_out[slot].synchronize()
+        err = int(st.host_err[slot][0])
+        if err != 0:
+            from .ops import _lib
+            raise _lib.KernelError(f"device-side error flag = {err} after step {ticket} (1: mbarrier wait timed "
+                                   "out, 2: peer signal wait timed out): replicas may have diverged, aborting")
         l = st.host_loss[slot]
         return float(l[0]), float(l[1]), float(l[2]), int(st.host_cnt[slot][1])
 
@@ -603,15 +649,19 @@ class DCGANEngine:
             self.comm.gather_state(self)
         sd = {n: t.detach().clone() for n, t in self.params.items()}
         sd.update({n: t.detach().clone() for n, t in self.ema_named().items()})
-        sd[manifest.GLOBAL_STEP_NAME] = self.counters[1].to(torch.int32).clone()
+        async_ps = self.comm is not None and hasattr(self.comm, "shard_counters")
+        if async_ps:   # async parameter-server mode: the applies of ALL workers, counted on the shard owners
+            sd[manifest.GLOBAL_STEP_NAME] = torch.tensor(self.comm.global_step(), dtype=torch.int32)
+        else:
+            sd[manifest.GLOBAL_STEP_NAME] = self.counters[1].to(torch.int32).clone()
         m, v = A.named(A.m), A.named(A.v)
         for n in self.params:
             a, b = manifest.adam_slot_names(n)
             sd[a], sd[b] = m[n].clone(), v[n].clone()
-        t = int(self.counters[0].item())
+        t = int(self.comm.shard_counters[0].item()) if async_ps else int(self.counters[0].item())
         sd["beta1_power"] = torch.tensor(self.beta1 ** (t + 1))
         sd["beta2_power"] = torch.tensor(self.beta2 ** (t + 1))
-        sd["adam_t"] = self.counters[0].clone()
+        sd["adam_t"] = torch.tensor(t, dtype=torch.int64) if async_ps else self.counters[0].clone()
         return sd
 
     def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:

@@ -1,7 +1,12 @@
 """Command-line flags: every flag name of the reference (image_train.py:10-40) with its default,
-plus the new ones of SURVEY.md 5.6.  Flags the reference declares but never reads are live here
-where that is meaningful (``batch_size``, ``output_size``, ``c_dim``, ``sample_dir``, ``epoch``,
-``train_size``, ``log_device_placement``); the rest are accepted and reported as unused.
+plus the new ones of SURVEY.md 5.6.  Of the flags the reference declares but never reads:
+
+* live here: ``batch_size``, ``output_size``, ``c_dim`` (model / batch geometry), ``sample_dir`` (where the grids
+  go), ``train_size`` (a finite value shortens the epoch used by the log line and the sample file names,
+  ``config.steps_per_epoch``) and ``log_device_placement`` (the chief prints which rank / device holds every
+  variable, ``train.log_placement``);
+* accepted and unused, as in the reference: ``epoch`` (the loop budget is ``--max_steps`` = the reference's
+  hard-coded 1,200,000 global steps), ``image_size``, ``dataset``, ``is_train``, ``is_crop``, ``visualize``.
 """
 from __future__ import annotations
 
@@ -68,10 +73,13 @@ def define_flags() -> None:
     flags.DEFINE_integer("worker_timeout_secs", 120, "ps role: a worker that stays silent this long while others wait "
                          "for it (sync round / shutdown) is presumed dead and dropped; 0 = wait forever like "
                          "server.join() (image_train.py:62-63)")
+    flags.DEFINE_integer("peer_timeout_secs", 600, "GPU replicas: how long a rank waits for its peers' signals inside "
+                         "the fused exchange before it raises the device error flag and the job stops (the chief "
+                         "pauses between steps for checkpoints and summaries)")
     flags.DEFINE_integer("log_every", 1, "print the step line every N steps (reference: every step)")
 
 
-UNUSED_IN_REFERENCE_AND_HERE = ("image_size", "dataset", "is_train", "is_crop", "visualize")
+UNUSED_IN_REFERENCE_AND_HERE = ("epoch", "image_size", "dataset", "is_train", "is_crop", "visualize")
 
 
 def pprint_flags() -> None:

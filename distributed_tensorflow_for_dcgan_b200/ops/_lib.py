@@ -54,6 +54,7 @@ _SIGNATURES = {
     "dcgan_comm_allreduce_small": "pppiipiiis",
     "dcgan_comm_async_apply": "ppppppppiizffffis",
     "dcgan_bn_forward_static": "pppppppiiiffis",
+    "dcgan_copy_error_flag": "ps",
 }
 _KIND = {"p": c_void_p, "i": c_int, "f": c_float, "z": c_size_t, "s": c_void_p}
 
@@ -85,8 +86,11 @@ def load() -> ctypes.CDLL:
     lib.dcgan_last_device_error.restype = c_int
     lib.dcgan_set_mn_desc_variant.argtypes = [c_int]
     lib.dcgan_set_mn_desc_variant.restype = None
+    lib.dcgan_set_workspace.argtypes = [c_void_p, c_size_t]
+    lib.dcgan_set_workspace.restype = c_int
     for setter in ("dcgan_set_igemm_tuning", "dcgan_set_igemm_ksplit", "dcgan_set_wgrad_cta_target",
-                   "dcgan_set_adam_blocks"):
+                   "dcgan_set_adam_blocks", "dcgan_set_igemm_max_ctas", "dcgan_set_igemm_stage_mode",
+                   "dcgan_set_igemm_cluster"):
         getattr(lib, setter).argtypes = [c_int]
         getattr(lib, setter).restype = None
     # profiling overrides (A/B runs of bench.py without a rebuild)
@@ -94,6 +98,10 @@ def load() -> ctypes.CDLL:
         lib.dcgan_set_igemm_tuning(int(os.environ["DCGAN_IGEMM_TUNING"]))
     if os.environ.get("DCGAN_IGEMM_KSPLIT"):
         lib.dcgan_set_igemm_ksplit(int(os.environ["DCGAN_IGEMM_KSPLIT"]))
+    if os.environ.get("DCGAN_IGEMM_CLUSTER"):
+        lib.dcgan_set_igemm_cluster(int(os.environ["DCGAN_IGEMM_CLUSTER"]))
+    if os.environ.get("DCGAN_IGEMM_MAX_CTAS"):
+        lib.dcgan_set_igemm_max_ctas(int(os.environ["DCGAN_IGEMM_MAX_CTAS"]))
     if os.environ.get("DCGAN_WGRAD_CTAS"):
         lib.dcgan_set_wgrad_cta_target(int(os.environ["DCGAN_WGRAD_CTAS"]))
     if os.environ.get("DCGAN_ADAM_BLOCKS"):
@@ -147,6 +155,13 @@ def call(name: str, *args) -> None:
     if rc != 0:
         raise KernelError(f"{name} failed: {_ERR.get(rc, rc)}")
     launch_count += 1
+
+
+def set_workspace(t) -> None:
+    """Split-K scratch for the implicit-GEMM launches of this host thread (``None`` = the library default)."""
+    rc = load().dcgan_set_workspace(None if t is None else t.data_ptr(), 0 if t is None else t.numel() * t.element_size())
+    if rc != 0:
+        raise KernelError(f"dcgan_set_workspace failed: {_ERR.get(rc, rc)}")
 
 
 def last_device_error() -> int:

@@ -25,12 +25,15 @@ class AsyncPSComm:
     overlap = False
     sync_bn = False
 
-    def __init__(self, device, blocks: int = 148):
+    def __init__(self, device, blocks: int = 148, group=None):
         import torch.distributed._symmetric_memory as symm_mem
         self.symm_mem = symm_mem
         self.device, self.blocks = device, blocks
-        self.world, self.rank = dist.get_world_size(), dist.get_rank()
-        self.group = dist.group.WORLD
+        self.group = group if group is not None else dist.group.WORLD   # the worker ranks (ps tasks excluded)
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.chief = dist.get_global_rank(self.group, 0)
+        if self.group is not dist.group.WORLD and hasattr(symm_mem, "enable_symm_mem_for_group"):
+            symm_mem.enable_symm_mem_for_group(self.group.group_name)
         self.handles: Dict[str, object] = {}
 
     def _symmetric(self, name: str, numel: int, dtype) -> torch.Tensor:
@@ -47,7 +50,7 @@ class AsyncPSComm:
 
     def attach(self, engine) -> None:
         A = engine.arena
-        dist.broadcast(A.master, src=0)
+        dist.broadcast(A.master, src=self.chief, group=self.group)
         engine.refresh_compute_weights()
         self._p = _ptr_array(self.handles["master"].buffer_ptrs)
         self._b = _ptr_array(self.handles["bf16"].buffer_ptrs)
@@ -58,7 +61,16 @@ class AsyncPSComm:
         self._counter_ptrs = torch.tensor([int(p) for p in self.handles["shard_counters"].buffer_ptrs],
                                           dtype=torch.int64, device=self.device)
         torch.cuda.synchronize(self.device)
-        dist.barrier()
+        dist.barrier(group=self.group)
+
+    def seed_counters(self, engine) -> None:
+        """After a restore / the chief's broadcast: global_step and the per-shard Adam step live in the shard
+        counters in this mode, so they continue from the restored values instead of restarting at zero."""
+        adam_t, gstep = (int(v) for v in engine.counters.tolist())
+        self.shard_counters[0] = adam_t
+        self.shard_counters[1] = gstep if self.rank == 0 else 0
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
 
     def optimizer_step(self, engine, which: str = "both") -> None:
         A = engine.arena
@@ -93,4 +105,4 @@ class AsyncPSComm:
     def close(self) -> None:
         # a worker may only release its shard once nobody pushes to it any more
         torch.cuda.synchronize(self.device)
-        dist.barrier()
+        dist.barrier(group=self.group)

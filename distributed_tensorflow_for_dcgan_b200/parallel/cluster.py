@@ -10,7 +10,10 @@ variables pinned to the ps job.  Here:
   the first ps host (first worker host when there is no ps job) -- the gRPC star becomes one TCP store;
 * CPU mode: ps tasks own parameter shards and serve push/pull (parallel/ps.py);
 * GPU mode: parameter shards live in the worker GPUs' NVLink-mapped memory (parallel/fused_comm.py),
-  so a ps task has nothing to serve: it joins, waits for the workers to finish and exits.
+  so a ps task has nothing to serve.  The world group (ps + workers) is gloo; every process -- ps tasks too,
+  as non-members -- takes part in creating the NCCL sub-group of the worker ranks (``worker_group``) that
+  carries the symmetric-memory rendezvous, the initial broadcast and the barriers.  A ps task then waits at
+  two world barriers (workers started / workers finished) and exits: ``server.join()`` with a way out.
 """
 from __future__ import annotations
 
@@ -114,6 +117,23 @@ def init_process_group(role: Role, backend: str, timeout_s: int = 1800, device=N
         kwargs["device_id"] = device
     dist.init_process_group(backend, init_method=f"tcp://{host}:{port}", rank=role.rank,
                             world_size=role.world_size, timeout=datetime.timedelta(seconds=timeout_s), **kwargs)
+
+
+def worker_ranks(spec: ClusterSpec) -> List[int]:
+    """Global ranks of the worker job (ps tasks come first in the rank order)."""
+    return [spec.worker_rank(i) for i in range(spec.num_workers)]
+
+
+def worker_group(role: Role, backend: str):
+    """Process group of the worker ranks only.  COLLECTIVE over the whole world: every process of the cluster,
+    ps tasks included, must call it (non-members get ``None``).  Without ps tasks the world group is returned."""
+    import torch.distributed as dist
+    if not role.distributed:
+        return None
+    if role.cluster.num_ps == 0:
+        return dist.group.WORLD
+    g = dist.new_group(ranks=worker_ranks(role.cluster), backend=backend)
+    return None if role.is_ps else g
 
 
 def shutdown() -> None:

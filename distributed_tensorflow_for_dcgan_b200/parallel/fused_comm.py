@@ -39,14 +39,18 @@ def _ptr_array(ptrs):
 
 class FusedComm:
     def __init__(self, device, sync_bn: bool = False, overlap: bool = True, use_multicast: bool = True,
-                 blocks: int = 32, gather_in_consumer: bool = True):
+                 blocks: int = 32, gather_in_consumer: bool = True, group=None):
         import torch.distributed._symmetric_memory as symm_mem
         self.symm_mem = symm_mem
         self.device, self.sync_bn, self.overlap = device, sync_bn, overlap
-        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        # the worker ranks only: with ps tasks in the launch (CPU joiners) this is an NCCL sub-group of the world
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.chief = dist.get_global_rank(self.group, 0)
         if self.world > MAX_RANKS:
             raise ValueError(f"at most {MAX_RANKS} ranks per NVLink domain")
-        self.group = dist.group.WORLD
+        if self.group is not dist.group.WORLD and hasattr(symm_mem, "enable_symm_mem_for_group"):
+            symm_mem.enable_symm_mem_for_group(self.group.group_name)
         self.handles: Dict[str, object] = {}
         self.tensors: Dict[str, torch.Tensor] = {}
         self.use_multicast = use_multicast
@@ -83,7 +87,7 @@ class FusedComm:
 
     def attach(self, engine) -> None:
         A = engine.arena
-        dist.broadcast(A.master, src=0)  # one-time: the chief's initialisation (image_train.py:117,125)
+        dist.broadcast(A.master, src=self.chief, group=self.group)  # the chief's initialisation (image_train.py:117,125)
         engine.refresh_compute_weights()
         self._grad_ptrs = _ptr_array(self.handles["zero_region"].buffer_ptrs)
         self._bf16_ptrs = _ptr_array(self.handles["bf16"].buffer_ptrs)
@@ -101,7 +105,22 @@ class FusedComm:
         off, shape = A.offsets["g_h0_lin/Matrix"]
         self.pull_range = (off, off + shape[0] * shape[1]) if self.gather_in_consumer else (0, 0)
         torch.cuda.synchronize(self.device)
-        dist.barrier()
+        dist.barrier(group=self.group)
+
+    def set_peer_timeout(self, seconds: float) -> None:
+        """Bound of every wait for the peers' signals (about 0.7 us per poll)."""
+        polls = int(min(max(seconds, 1.0) / 0.7e-6, 2 ** 32 - 1))
+        _lib.load().dcgan_comm_set_peer_spin_limit(ctypes.c_uint(polls))
+
+    def owner_ranks(self, lo: int, hi: int):
+        """Ranks whose optimizer shard intersects the arena range [lo, hi)."""
+        out = []
+        for bucket in ("g", "d"):
+            for r in range(self.world):
+                s0, s1 = self.shard_range(bucket, r)
+                if s0 < hi and lo < s1 and r not in out:
+                    out.append(r)
+        return sorted(out)
 
     # ---- the fused optimizer step ---------------------------------------------------------------------------------
     def _launch(self, engine, which: str, blocks: int = 0) -> None:

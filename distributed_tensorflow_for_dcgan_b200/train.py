@@ -41,11 +41,14 @@ def run_ps(FLAGS, role, cfg) -> int:
     """``server.join()`` (image_train.py:62-63)."""
     use_cuda = _use_cuda(FLAGS)
     if use_cuda:
-        # GPU mode: the parameter shards live in the workers' peer-mapped HBM; nothing to serve.
+        # GPU mode: the parameter shards live in the workers' peer-mapped HBM; nothing to serve.  The ps task is a
+        # member of the gloo world only; it helps create the workers' NCCL group (collective) and then joins.
         cl.init_process_group(role, "gloo")
         import torch.distributed as dist
-        dist.barrier()   # start
+        cl.worker_group(role, "nccl")
+        dist.barrier()   # workers started
         dist.barrier()   # workers finished
+        print(f"ps {role.task_index}: joined; the workers own the parameter shards", flush=True)
         cl.shutdown()
         return 0
     from .parallel.ps import PSServer
@@ -73,25 +76,33 @@ def run_worker(FLAGS, role, cfg) -> int:
     use_cuda = _use_cuda(FLAGS)
     is_chief = role.is_chief
     batch = cfg.batch_size
-    spe = steps_per_epoch(batch)
+    spe = steps_per_epoch(batch, FLAGS.train_size)
     ps_client = None
     comm = None
     if use_cuda:
         local = int(os.environ.get("LOCAL_RANK", role.task_index % max(torch.cuda.device_count(), 1)))
         torch.cuda.set_device(local)
         device = torch.device("cuda", local)
+        wgroup = None
         if role.distributed:
+            import torch.distributed as dist
             if role.cluster.num_ps:
-                # ps joiners are CPU-only processes: rendezvous them over gloo, workers among themselves on NCCL
-                raise SystemExit("GPU mode: launch workers only (parameter shards live on the worker GPUs); "
-                                 "omit --ps_hosts or use --device=cpu for the ps plumbing path")
-            cl.init_process_group(role, "nccl", device=device)
+                # ps tasks are CPU-only joiners: the world (ps + workers) meets over gloo, the workers get an NCCL
+                # sub-group of their own for the symmetric-memory rendezvous and the initial broadcast
+                cl.init_process_group(role, "gloo")
+                wgroup = cl.worker_group(role, "nccl")
+                dist.barrier()   # pairs with run_ps: workers started
+            else:
+                cl.init_process_group(role, "nccl", device=device)
+                wgroup = dist.group.WORLD
             from .parallel.sync_dp import make_comm
             if FLAGS.sync_replicas:
-                comm = make_comm(FLAGS.comm_backend, device, sync_bn=FLAGS.sync_bn)
+                comm = make_comm(FLAGS.comm_backend, device, sync_bn=FLAGS.sync_bn, group=wgroup)
             else:
                 from .parallel.async_ps import AsyncPSComm
-                comm = AsyncPSComm(device)
+                comm = AsyncPSComm(device, group=wgroup)
+            if hasattr(comm, "set_peer_timeout"):
+                comm.set_peer_timeout(FLAGS.peer_timeout_secs)
         if FLAGS.dtype == "fp32":
             # reference-precision path: the oracle model in f32 on the GPU through PyTorch's library kernels
             # (single process only); the hand-written engine computes in bf16
@@ -140,12 +151,21 @@ def run_worker(FLAGS, role, cfg) -> int:
             # "wait for the chief to initialise" of managed_session (image_train.py:141)
             eng = trainer.engine
             for t in (eng.arena.master, eng.arena.m, eng.arena.v, eng.counters):
-                dist.broadcast(t, src=0)
+                dist.broadcast(t, src=role.cluster.worker_rank(0), group=wgroup)
             eng.refresh_compute_weights()
+            if hasattr(comm, "seed_counters"):     # async mode keeps global_step / Adam t in the shard counters
+                comm.seed_counters(eng)
 
+    if FLAGS.log_device_placement and is_chief:
+        log_placement(trainer, role, use_cuda)
     replica = 0 if FLAGS.identical_replicas else role.task_index
     images = _make_reader(FLAGS, FLAGS.data_dir, batch, cfg, FLAGS.seed + 17 * replica)
     sample_images = None
+    if is_chief:
+        # the second pipeline (image_train.py:84) is built before the loop, as in the reference graph: filling its
+        # shuffle queue inside the step loop would keep the other replicas waiting at their next exchange
+        sample_dir = FLAGS.sample_image_dir if os.path.isdir(FLAGS.sample_image_dir) else FLAGS.data_dir
+        sample_images = _make_reader(FLAGS, sample_dir, batch, cfg, FLAGS.seed + 999)
     rng = np.random.RandomState(FLAGS.seed + 1000 + replica)
     sample_z = rng.uniform(-1, 1, size=(SAMPLE_SIZE, cfg.z_dim)).astype(np.float32)  # image_train.py:77
     prefetch = None
@@ -179,9 +199,6 @@ def run_worker(FLAGS, role, cfg) -> int:
         if prefetch is not None:
             prefetch.release()
         if step % FLAGS.sample_every == 1 and is_chief:                               # image_train.py:179
-            if sample_images is None:
-                sample_dir = FLAGS.sample_image_dir if os.path.isdir(FLAGS.sample_image_dir) else FLAGS.data_dir
-                sample_images = _make_reader(FLAGS, sample_dir, batch, cfg, FLAGS.seed + 999)  # 2nd pipeline, :84
             sample_image = sample_images.dequeue_many(batch)
             grid = trainer.sample_grid(sample_z[:batch])
             d1_loss, g1_loss = trainer.evaluate_losses(sample_image, sample_z[:batch])
@@ -203,8 +220,32 @@ def run_worker(FLAGS, role, cfg) -> int:
     if role.distributed:
         if use_cuda and comm is not None and hasattr(comm, "close"):
             comm.close()
+        if use_cuda and role.cluster.num_ps:
+            import torch.distributed as dist
+            dist.barrier()   # pairs with run_ps: workers finished
         cl.shutdown()
     return 0
+
+
+def log_placement(trainer, role, use_cuda: bool) -> None:
+    """``--log_device_placement`` (image_train.py:36; the reference declares it and never reads it): one line per
+    variable with the device -- and, for sharded multi-GPU state, the ranks -- that hold it."""
+    eng = getattr(trainer, "engine", None)
+    if eng is None:
+        where = "ps shards (parallel/ps.py)" if role.cluster.num_ps else "cpu"
+        for name in trainer.params:
+            print(f"{name}: {where}")
+        return
+    comm, A = eng.comm, eng.arena
+    for name, (off, shape) in A.offsets.items():
+        n = 1
+        for d in shape:
+            n *= d
+        if comm is not None and hasattr(comm, "owner_ranks"):
+            owners = comm.owner_ranks(off, off + n)
+            print(f"{name}: {eng.device} (bf16 copy on every rank; f32 master + Adam slots on rank(s) {owners})")
+        else:
+            print(f"{name}: {eng.device}")
 
 
 def _worker_barrier(role):

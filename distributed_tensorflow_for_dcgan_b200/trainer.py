@@ -221,8 +221,13 @@ class EngineTrainer:
         e.real_f32.copy_(torch.as_tensor(real)); e.z.copy_(torch.as_tensor(z))
         e.zero_region.zero_()
         K.f32_to_bf16(e.real_f32, e.d_in[:e.B])
-        e.generator_forward(train=True)
-        e.discriminator_forward()
+        # only the chief evaluates (image_train.py:179-184): batch statistics stay local, no collective is entered
+        e._local_bn_only = True
+        try:
+            e.generator_forward(train=True)
+            e.discriminator_forward()
+        finally:
+            e._local_bn_only = False
         K.gan_loss(e.logits, e.losses, None, e.probs, None, e.B, 1.0, False)
         l = e.losses.tolist()
         return l[0] + l[1], l[2]

@@ -34,6 +34,11 @@ extern "C" {
  * 2 = peer signal wait timed out).  Synchronises the device. */
 int dcgan_last_device_error(void);
 
+/* Stream-ordered read of the same flag into pinned host memory (4 bytes; neither synchronises nor clears): a
+ * training loop fetches it with the losses of every step and stops when it is non-zero, so that a timed-out
+ * peer wait -- which makes a rank skip its shard's update -- cannot go unnoticed. */
+int dcgan_copy_error_flag(int* host_dst, cudaStream_t stream);
+
 /* Bring-up switch for the MN-major UMMA descriptor convention (0 = CuTe convention). */
 void dcgan_set_mn_desc_variant(int v);
 
@@ -42,8 +47,20 @@ void dcgan_set_mn_desc_variant(int v);
  * side-stream filter-gradient kernels); DCGAN_PDL=1 in the environment or this call turns it on. */
 void dcgan_set_pdl(int v);
 
-/* Profiling switch for the implicit-GEMM kernels: bit 0 = two CTAs per SM (default on). */
+/* Profiling switch for the implicit-GEMM kernels.  Bit 7 (128) selects the first-generation kernels (cp.async
+ * gather, csrc/igemm_sm100.cu) instead of the TMA-fed persistent ones (csrc/igemm2_sm100.cu); the other bits
+ * only act on the first generation: bit 0 = two CTAs per SM (default on). */
 void dcgan_set_igemm_tuning(int v);
+/* Second-generation kernels: cap on the persistent grid (0 = one CTA per SM), stage-ring depth (1 = shallow),
+ * CTAs per cluster that share the filter tile by TMA multicast (0 = default, 1 / 2 / 4 forced). */
+void dcgan_set_igemm_max_ctas(int v);
+void dcgan_set_igemm_stage_mode(int v);
+void dcgan_set_igemm_cluster(int v);
+/* Split-K scratch of the second-generation kernels for the calling host thread: `bytes` of device memory whose
+ * first 64 KiB are zero (arrival counters; the kernels leave them zero), at least 1 MiB + 64 KiB.  Kernels that
+ * may run concurrently (different streams) must not share a workspace.  NULL returns to the library's default
+ * buffer (48 MiB per device, allocated on first need -- not possible inside a stream capture). */
+int dcgan_set_workspace(void* ptr, size_t bytes);
 /* Split-K factor of the strided / transposed convs (a thread-block cluster shares one output tile and reduces
  * its partial accumulators through distributed shared memory): 0 = chosen per layer (default), 1/2/4 = forced.
  * Tests and profiling only. */
@@ -186,6 +203,11 @@ int dcgan_count_zeros(const void* x, unsigned long long* count, size_t n, cudaSt
 /* ---- in-kernel collectives over NVLink peer memory (csrc/comm_sm100.cu) --------------------------------
  * Replace the reference's gRPC parameter push/pull.  *_ptrs are host arrays of `world`
  * device pointers (one per rank, peer-mapped symmetric buffers); `state` is 2 local uint32 per slot. */
+
+/* Polls (about 0.7 us each) before a wait for the peers' signals gives up and raises the error flag; default 2^24
+ * (~12 s).  A training driver whose chief pauses between steps (checkpoint, sample queue) raises it.  Applies to
+ * the current device. */
+int dcgan_comm_set_peer_spin_limit(unsigned polls);
 
 /* Sync replicas: reduce-scatter of f32 gradients + average + TF-form Adam on this rank's shard of
  * [lo,hi) + all-gather of the updated bf16 parameters, in one kernel.  mc_* = NVLS multicast addresses

@@ -309,3 +309,34 @@ def test_variable_sharding_is_balanced_and_exhaustive():
     assert sorted(flat) == sorted(s.name for s in specs)
     sizes = [sum(next(x.numel for x in specs if x.name == n) for n in s) for s in shards]
     assert max(sizes) <= 3276800 + 100000  # no shard much beyond the largest single tensor
+
+
+def test_worker_group_ranks_exclude_ps_tasks():
+    """The workers' own process group (symmetric-memory rendezvous, initial broadcast) is made of the worker ranks
+    only; ps tasks come first in the rank order and stay out of it (reference launch: image_train.py:52-67)."""
+    from distributed_tensorflow_for_dcgan_b200.parallel import cluster as cl
+    spec = cl.ClusterSpec.from_flags("a:1,b:2", "c:3,d:4,e:5")
+    assert cl.worker_ranks(spec) == [2, 3, 4]
+    assert cl.worker_ranks(cl.ClusterSpec.from_flags("", "c:3,d:4")) == [0, 1]
+    solo = cl.resolve_role("", 0, "", "")
+    assert cl.worker_group(solo, "gloo") is None   # a single process has no group to build
+
+
+def test_train_size_flag_shortens_the_epoch():
+    from distributed_tensorflow_for_dcgan_b200.config import steps_per_epoch
+    assert steps_per_epoch(64) == 5051                      # image_train.py:44-48 under Python 2
+    assert steps_per_epoch(64, float("inf")) == 5051
+    assert steps_per_epoch(64, 6400) == 100
+    assert steps_per_epoch(64, 10) == 1                     # never zero: the log line divides by it
+    assert steps_per_epoch(64, 10 ** 9) == 5051
+
+
+def test_flag_docstring_matches_what_is_read():
+    """The flags module says which reference-dead flags are live; hold it to that."""
+    import inspect
+    from distributed_tensorflow_for_dcgan_b200 import flags as F, train as T
+    src = inspect.getsource(T)
+    for live in ("train_size", "log_device_placement", "sample_dir"):
+        assert f"FLAGS.{live}" in src, live
+    for unused in F.UNUSED_IN_REFERENCE_AND_HERE:
+        assert f"FLAGS.{unused}" not in src, unused
