@@ -43,7 +43,8 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "ddp", "reference"])
     ap.add_argument("--batch", type=int, default=64, help="images per GPU (reference: 64, hard-coded)")
     ap.add_argument("--comm", default="fused", choices=["fused", "nccl"], help="multi-GPU gradient path")
-    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="ours: launch the kernels eagerly.  ddp: eager PyTorch + the DDP wrapper (the round-1 bar)")
     ap.add_argument("--wide", action="store_true", help="128x128, ngf=ndf=128 (BASELINE.json config 3)")
     ap.add_argument("--sync-bn", action="store_true")
     ap.add_argument("--mode", default="sync", choices=["sync", "async"],
@@ -135,6 +136,59 @@ def reference_arm(args):
     return 0
 
 
+def multi_gpu_check(eng, comm, dist, torch, rank, world):
+    """Driver-visible multi-GPU numerics, outside every timed region (N > 1, fused backend):
+    (a) every rank holds bit-identical bf16 parameters after the timed steps;
+    (b) one optimizer step through the fused reduce-scatter + Adam + all-gather kernel and one through
+        NCCL all-reduce + the single-GPU Adam kernel, from identical state and rank-dependent gradients, agree."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as Kn
+    A = eng.arena
+    torch.cuda.synchronize()
+    dist.barrier()
+    # ---- (a) replicas in lock-step ------------------------------------------------------------------------
+    lo, hi = getattr(comm, "pull_range", (0, 0))
+    shadow = A.bf16.view(torch.int16).to(torch.int64)
+    if hi > lo:   # gathered by its consumer at the next forward pass: only the owners' copies are current
+        shadow = torch.cat([shadow[:lo], shadow[hi:]])
+    mine = torch.stack([shadow.sum(), (shadow * (torch.arange(shadow.numel(), device=shadow.device) % 8191)).sum()])
+    allv = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(allv, mine)
+    identical = all(bool((v == allv[0]).all()) for v in allv)
+    # ---- (b) fused step vs NCCL + Adam --------------------------------------------------------------------
+    keep = dict(master=A.master.clone(), m=A.m.clone(), v=A.v.clone(), bf16=A.bf16.clone(), cnt=eng.counters.clone())
+    gen = torch.Generator(device=A.master.device).manual_seed(4321 + rank)
+    grads = torch.randn(A.padded, device=A.master.device, generator=gen) * 1e-2
+    eng.grads.copy_(grads)
+    torch.cuda.synchronize(); dist.barrier()
+    comm.optimizer_step(eng, "both")
+    torch.cuda.synchronize(); dist.barrier()
+    fused_master, fused_bf16 = A.master.clone(), A.bf16.clone()
+    A.master.copy_(keep["master"]); A.m.copy_(keep["m"]); A.v.copy_(keep["v"]); A.bf16.copy_(keep["bf16"])
+    ref_g = grads.clone()
+    dist.all_reduce(ref_g)
+    Kn.adam(A.master, ref_g, A.m, A.v, A.bf16, eng.counters, eng.lr, eng.beta1, eng.beta2, eng.eps, 1.0 / world)
+    torch.cuda.synchronize()
+    worst = 0.0
+    for bucket in ("g", "d"):
+        s0, s1 = comm.shard_range(bucket, comm.rank)      # the f32 master is current on its owner only
+        if s1 > s0:
+            d = (fused_master[s0:s1] - A.master[s0:s1]).abs().max().item()
+            worst = max(worst, d / max(A.master[s0:s1].abs().max().item(), 1e-12))
+    fb, rb = fused_bf16.float(), A.bf16.float()
+    if hi > lo:
+        fb = torch.cat([fb[:lo], fb[hi:]]); rb = torch.cat([rb[:lo], rb[hi:]])
+    bf_diff = (fb - rb).abs().max().item()
+    # back to the state the benchmark left
+    A.master.copy_(keep["master"]); A.m.copy_(keep["m"]); A.v.copy_(keep["v"]); A.bf16.copy_(keep["bf16"])
+    eng.counters.copy_(keep["cnt"])
+    t = torch.tensor([worst, bf_diff, 0.0 if identical else 1.0], device=A.master.device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    worst, bf_diff, bad = t.tolist()
+    ok = bad == 0.0 and worst < 1e-5 and bf_diff < 1e-2
+    return {"ranks_bit_identical": bad == 0.0, "fused_vs_nccl_adam_max_rel_err": worst,
+            "bf16_param_max_abs_diff": bf_diff, "multicast": getattr(comm, "mc_grad", None) is not None, "ok": ok}
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -215,10 +269,29 @@ def main():
             parallelism += "-syncbn"
     else:
         from baseline.ddp_dcgan import BaselineTrainer
+        use_graph = not args.no_graph
+        if use_graph and world > 1:
+            os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")  # NCCL collectives inside a capture
         tr = BaselineTrainer(dev, world=world, batch=B, s=S, gf=cfg.gf_dim, df=cfg.df_dim, z_dim=cfg.z_dim,
-                             sync_bn=args.sync_bn)
+                             sync_bn=args.sync_bn, graph=use_graph)
         d_real = torch.empty(B, 3, S, S, device=dev).contiguous(memory_format=torch.channels_last)
         d_z = torch.empty(B, cfg.z_dim, device=dev)
+        if use_graph:
+            # the whole step (both backward passes, the all-reduces, both Adams) as one CUDA graph; every rank
+            # must agree on whether the capture worked, or the collectives would no longer pair up
+            d_real.uniform_(-1, 1); d_z.uniform_(-1, 1)
+            ok = 1
+            try:
+                tr.capture(d_real, d_z)
+            except Exception as e:   # pragma: no cover - depends on the torch / NCCL build
+                print(f"rank {rank}: baseline graph capture failed ({type(e).__name__}: {e})", file=sys.stderr)
+                ok = 0
+            if world > 1:
+                flag = torch.tensor([ok], device=dev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                ok = int(flag.item())
+            if not ok:
+                raise SystemExit("baseline graph capture failed; rerun with --no-graph for the eager DDP bar")
         stage_nhwc = torch.empty(B, S, S, 3, device=dev)
         last = {}
 
@@ -288,9 +361,13 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms = t.tolist()
+    mg_check = None
     if args.impl == "ours":
         from distributed_tensorflow_for_dcgan_b200.ops import kernels as Kn
         Kn.check_device_error()
+        if world > 1 and args.mode == "sync" and args.comm == "fused":
+            mg_check = multi_gpu_check(eng, comm, dist, torch, rank, world)
+            Kn.check_device_error()
 
     if rank == 0:
         gb = B * world
@@ -314,7 +391,7 @@ def main():
             "impl": args.impl,
             "config": {"model": f"DCGAN {S}x{S} ngf={cfg.gf_dim} ndf={cfg.df_dim} z={cfg.z_dim}",
                        "global_batch": gb, "batch_per_gpu": B, "seq_len": None, "parallelism": parallelism,
-                       "update_mode": "simultaneous", "replica_mode": args.mode, "cuda_graph": (args.impl == "ours" and use_graph),
+                       "update_mode": "simultaneous", "replica_mode": args.mode, "cuda_graph": bool(use_graph),
                        "l2": "flushed between timed steps (256 MiB write outside the event pairs)",
                        "step_ms_min_med_max": [round(min(per_step), 4), round(statistics.median(per_step), 4),
                                                round(max(per_step), 4)]},
@@ -324,9 +401,13 @@ def main():
             "gpu_launches": launches_per_step * K_steps if args.impl == "ours" else 0,
             "launches_per_step": launches_per_step,
         }
+        if mg_check is not None:
+            line["multi_gpu_check"] = mg_check
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    if mg_check is not None and not mg_check["ok"]:
+        return 3   # a rank diverged or the fused exchange disagrees with NCCL + Adam: the number does not count
     return 0
 
 

@@ -49,35 +49,52 @@ __device__ __forceinline__ void zero_patch(__nv_bfloat16* patch) {
 
 constexpr int kPatchWordsPerThread = 15;  // 5 rows * 384 words / 128 threads (the 1x128 tile)
 
-__device__ __forceinline__ void fetch_patch(const __nv_bfloat16* __restrict__ x, uint32_t (&v)[kPatchWordsPerThread],
-                                            int n, int oy0, int H, int W, const TileGeom& g) {
-  const int iy0 = 2 * oy0 - 1;
+// Word i = threadIdx.x + k*128 of a tile's patch: rows of one image are contiguous in memory, so the source is
+// simply word i after the first patch row and only the row bounds need checking; the destination (row pitch
+// differs from the image pitch) needs i / words_per_row, which depends on the thread alone and is computed once
+// per kernel (PatchMap) instead of per tile -- ncu showed these kernels bound by instruction issue, ~900 of the
+// ~1900 instructions per warp and tile being these divisions.
+struct PatchMap {
+  int dst[kPatchWordsPerThread];  // element index of the word's low half in the smem patch, -1 = beyond the patch
+};
+__device__ __forceinline__ PatchMap make_patch_map(int W, const TileGeom& g) {
+  PatchMap m;
   const int words_per_row = (3 * W) >> 1;       // 32-bit words of one image row (W even)
   const int total = g.patch_h * words_per_row;  // <= 11 * 96 = 1056, 7 * 192 = 1344, 5 * 384 = 1920
 #pragma unroll
   for (int k = 0; k < kPatchWordsPerThread; ++k) {
     const int i = threadIdx.x + k * kTcThreads;
-    v[k] = 0u;
-    if (i < total) {
-      const int r = i / words_per_row, wcol = i - r * words_per_row;
-      const int iy = iy0 + r;
-      if ((unsigned)iy < (unsigned)H)
-        v[k] = __ldg(reinterpret_cast<const uint32_t*>(x + ((size_t)n * H + iy) * W * 3) + wcol);
-    }
-  }
-}
-
-__device__ __forceinline__ void commit_patch(__nv_bfloat16* patch, const uint32_t (&v)[kPatchWordsPerThread], int W,
-                                             const TileGeom& g) {
-  const int words_per_row = (3 * W) >> 1;
-  const int total = g.patch_h * words_per_row;
-#pragma unroll
-  for (int k = 0; k < kPatchWordsPerThread; ++k) {
-    const int i = threadIdx.x + k * kTcThreads;
+    m.dst[k] = -1;
     if (i < total) {
       const int r = i / words_per_row, wcol = i - r * words_per_row;
       // pixel 0 sits at element 3 of the patch row (element 0..2 = pixel -1): odd offset -> two 16-bit stores
-      unsigned short* dst = reinterpret_cast<unsigned short*>(patch) + r * g.patch_pitch + 3 + 2 * wcol;
+      m.dst[k] = r * g.patch_pitch + 3 + 2 * wcol;
+    }
+  }
+  return m;
+}
+
+__device__ __forceinline__ void fetch_patch(const __nv_bfloat16* __restrict__ x, uint32_t (&v)[kPatchWordsPerThread],
+                                            int n, int oy0, int H, int W, const TileGeom& g) {
+  const int iy0 = 2 * oy0 - 1;
+  const int words_per_row = (3 * W) >> 1;
+  const int lo = (iy0 < 0 ? -iy0 : 0) * words_per_row;                              // rows above the image
+  const int hi = (g.patch_h < H - iy0 ? g.patch_h : H - iy0) * words_per_row;      // rows below it / patch end
+  const long first = ((long)n * H + iy0) * words_per_row;                          // word index of patch row 0
+  const uint32_t* xw = reinterpret_cast<const uint32_t*>(x);
+#pragma unroll
+  for (int k = 0; k < kPatchWordsPerThread; ++k) {
+    const int i = threadIdx.x + k * kTcThreads;
+    v[k] = (i >= lo && i < hi) ? __ldg(xw + (first + i)) : 0u;
+  }
+}
+
+__device__ __forceinline__ void commit_patch(__nv_bfloat16* patch, const uint32_t (&v)[kPatchWordsPerThread],
+                                             const PatchMap& m) {
+#pragma unroll
+  for (int k = 0; k < kPatchWordsPerThread; ++k) {
+    if (m.dst[k] >= 0) {
+      unsigned short* dst = reinterpret_cast<unsigned short*>(patch) + m.dst[k];
       dst[0] = (unsigned short)(v[k] & 0xffffu);
       dst[1] = (unsigned short)(v[k] >> 16);
     }
@@ -169,6 +186,7 @@ c3_fprop_tc_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict_
   const int tiles_per_img = oH * oW / 128;
   const int tiles = N * tiles_per_img;
   uint32_t phase = 0;
+  const PatchMap pmap = make_patch_map(W, g);
   uint32_t pv[kPatchWordsPerThread];  // the next tile's patch, in flight while this tile computes
   if ((int)blockIdx.x < tiles) {
     const int n = blockIdx.x / tiles_per_img;
@@ -180,7 +198,7 @@ c3_fprop_tc_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict_
   for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
     const int n = tile / tiles_per_img;
     const int oy0 = (tile - n * tiles_per_img) * g.rows_per_tile;
-    commit_patch(patch, pv, W, g);
+    commit_patch(patch, pv, pmap);
     __syncthreads();
     {
       const int nt = tile + gridDim.x;
@@ -271,6 +289,7 @@ c3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ x3, const __nv_bfloat16* __
   const int tiles = N * tiles_per_img;
   uint32_t phase = 0;
   bool any = false, ok = true;
+  const PatchMap pmap = make_patch_map(W, g);
   uint32_t pv[kPatchWordsPerThread];  // next tile's patch and dy row, fetched while this tile's MMAs run
   uint4 yv[8];
   auto fetch = [&](int tile) {
@@ -290,7 +309,7 @@ c3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ x3, const __nv_bfloat16* __
     // dy rows of this tile: pixel t -> 128 contiguous bytes, swizzled into the B tile
 #pragma unroll
     for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(b_tile + swz(t, j)) = yv[j];
-    commit_patch(patch, pv, W, g);
+    commit_patch(patch, pv, pmap);
     __syncthreads();
     if (tile + (int)gridDim.x < tiles) fetch(tile + gridDim.x);
     build_im2col_row(a_tiles, patch, t, g);

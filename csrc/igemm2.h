@@ -29,6 +29,22 @@ struct Igemm2Params {
   int oH, oW;             // F/T output spatial dims
   float* stats;           // F/T optional: [groups][2][Cn] += per-channel (sum, sum of squares), pre-activation
   int stat_group_rows;    // rows per statistics group (multiple of 128)
+  // optional: batch-norm backward reductions of the layer BELOW, fused into this data-gradient's epilogue.  The tile
+  // just computed is da (gradient w.r.t. that layer's activation); with its saved pre-activation the epilogue forms
+  // dy = da * act'(gamma * xhat + beta) and accumulates red[slab][0][c] += sum dy, red[slab][1][c] += sum dy * xhat
+  // (what dcgan_bn_bwd_reduce computes in a pass of its own).  stat_group_rows then holds the rows per slab.
+  const void* bn_pre;     // bf16 [stat_groups * slab_out_rows][Cn], the layer's pre-activations
+  const float* bn_saved;  // [stat_groups][2][Cn] (mean, rstd)
+  const float* bn_gamma;
+  const float* bn_beta;
+  float* bn_red;          // [slabs][2][Cn], zeroed by the caller
+  int bn_slab_out_rows;   // output rows (pixels) per slab
+  int bn_stat_groups;     // slab g uses the statistics / pre-activations of group min(g, bn_stat_groups - 1)
+  int bn_act;             // the layer's activation (ReLU / LeakyReLU)
+  // third-generation transposed conv (igemm3_sm100.cu)
+  int halo;               // X tiles carry two halo rows; the vertical shift is a descriptor offset
+  int halo_row_bytes;     // W * 128: one image row of the X tile
+  int x_tile_bytes;       // bytes of one X tile (TMA transaction size)
   float* partials;        // split-K scratch: [tile][slice][BLOCK_N / 4][128] float4
   int* counters;          // split-K arrival counters per tile (zero between launches)
   int* err_flag;          // sticky device error flag (csrc/runtime.cu)
@@ -36,14 +52,44 @@ struct Igemm2Params {
 };
 
 // Strided (transposed = 0) or transposed (1) 5x5 / stride-2 conv; see dcgan_conv_fprop* / dcgan_conv_tconv*.
+struct BnRedArgs {  // see Igemm2Params::bn_*
+  const void* pre;
+  const float* saved;
+  const float* gamma;
+  const float* beta;
+  float* red;
+  int slabs, stat_groups, act;
+};
 int igemm2_conv(int transposed, const void* x, const void* w, const float* bias, void* out, int NB, int H, int W,
                 int Cin, int Cout, int act, int block_n, int b_mn, float* stats, int stat_groups,
-                cudaStream_t stream);
+                cudaStream_t stream, const BnRedArgs* bnred = nullptr);
 // Filter gradient; see dcgan_conv_wgrad.
 int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd, int splits,
                  int block_n, cudaStream_t stream);
 // (tile width, K slices) for `tiles_bn64` 64-wide tiles of `kb_per_tile` k-blocks on the persistent grid
 void igemm2_plan(long tiles_bn64, double kb_per_tile, int Cn, int min_kb, int force_bn, int* block_n, int* ksplit);
+
+// Transposed conv with the four output parities fused in one CTA (igemm3_sm100.cu); same contract as
+// igemm2_conv(transposed = 1, ...).  Returns DCGAN_ERR_SHAPE for shapes it does not take (caller falls back).
+int igemm3_tconv(const void* x, const void* w, const float* bias, void* out, int NB, int H, int W, int Cin, int Cout,
+                 int act, int block_n, float* stats, int stat_groups, cudaStream_t stream, const BnRedArgs* bnred);
+
+// Strided conv with halo tiles (TensorFlow filter layout only); DCGAN_ERR_SHAPE when the layer's tiles are not whole
+// image rows (caller falls back to igemm2_conv).
+int igemm3_fconv(const void* x, const void* w_kn, const float* bias, void* out, int NB, int H, int W, int Cin, int Cout,
+                 int act, int block_n, float* stats, int stat_groups, cudaStream_t stream, const BnRedArgs* bnred);
+
+// helpers of igemm2_sm100.cu shared with igemm3_sm100.cu
+struct CUtensorMap_st;
+int igemm2_tmap_nhwc(const void* ptr, int N, int H, int W, int C, int bw, int bh, int bn, int stride, void* out_map);
+int igemm2_tmap_2d(const void* ptr, unsigned long long rows, unsigned long long cols, unsigned box_r, unsigned box_c,
+                   void* out_map);
+bool igemm2_pixel_box(int rows, int rH, int rW, int* bw, int* bh, int* bn);
+int igemm2_attach_scratch(Igemm2Params* p, long tiles, int cols_per_tile);
+int igemm2_num_sms();
+int igemm2_max_ctas();
+int igemm2_cluster_pref();
+int igemm2_forced_ksplit();
 
 void igemm2_set_max_ctas(int v);
 void igemm2_set_ksplit(int v);

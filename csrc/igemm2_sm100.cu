@@ -305,7 +305,8 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
     const int et = tid - 64;  // 0..127
     const int q = warp & 3;   // TMEM lane quadrant this warp may read
     const int row_in_tile = q * 32 + lane;
-    const bool do_stats = (MODE != MODE_W) && p.stats != nullptr;
+    const bool do_bnred = (MODE != MODE_W) && p.bn_red != nullptr;
+    const bool do_stats = (MODE != MODE_W) && (p.stats != nullptr || do_bnred);
     int ti = 0;
     bool ok = true;
     for (int u = first_group; u < p.total_groups && ok; u += group_step, ++ti) {
@@ -377,15 +378,24 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
         const int R = wi.m0 + row_in_tile;
         const bool valid = R < p.rows_total;
         __nv_bfloat16* orow = nullptr;
+        const __nv_bfloat16* prow = nullptr;  // fused batch-norm backward: this row of the saved pre-activations
+        int sg = 0;
         if (valid) {
+          size_t Ro;  // output pixel, row-major over the output tensor
           if (MODE == MODE_F) {
-            orow = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)R * p.Cn + wi.n0;
+            Ro = (size_t)R;
           } else {
             const int qw = R & (rW - 1);
             const int qh = (R >> p.rW_log2) & (rH - 1);
             const int n = R >> (p.rW_log2 + p.rH_log2);
-            orow = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                   ((size_t)((n * p.oH + 2 * qh + wi.ph) * p.oW + 2 * qw + wi.pw)) * p.Cn + wi.n0;
+            Ro = (size_t)((n * p.oH + 2 * qh + wi.ph) * p.oW + 2 * qw + wi.pw);
+          }
+          orow = reinterpret_cast<__nv_bfloat16*>(p.out) + Ro * p.Cn + wi.n0;
+          if (do_bnred) {
+            const int g = wi.m0 / p.stat_group_rows;  // slab of this tile (tiles never straddle slabs)
+            sg = min(g, p.bn_stat_groups - 1);
+            prow = reinterpret_cast<const __nv_bfloat16*>(p.bn_pre) +
+                   (Ro - (size_t)(g - sg) * p.bn_slab_out_rows) * p.Cn + wi.n0;
           }
         }
         float* ssm = stat_smem + a * (8 * BLOCK_N);
@@ -412,10 +422,45 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
           }
           if (do_stats) {  // batch-norm moments of this tile, reduced over the warp's 32 rows
             float sq[32];
+            if (do_bnred) {
+              // dy = da * act'(gamma * xhat + beta) and dy * xhat instead of (x, x^2)
+              uint4 pv[4];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              f[j] = valid ? f[j] : 0.f;
-              sq[j] = f[j] * f[j];
+              for (int j = 0; j < 4; ++j)
+                pv[j] = valid ? __ldg(reinterpret_cast<const uint4*>(prow + c) + j) : make_uint4(0, 0, 0, 0);
+              const uint32_t* pw32 = reinterpret_cast<const uint32_t*>(pv);
+              const float* mean = p.bn_saved + (size_t)sg * 2 * p.Cn + wi.n0 + c;
+              const float* rstd = mean + p.Cn;
+              const float* gm = p.bn_gamma + wi.n0 + c;
+              const float* bt = p.bn_beta + wi.n0 + c;
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                const float4 m4 = __ldg(reinterpret_cast<const float4*>(mean + j));
+                const float4 r4 = __ldg(reinterpret_cast<const float4*>(rstd + j));
+                const float4 g4 = __ldg(reinterpret_cast<const float4*>(gm + j));
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bt + j));
+                const float2 p01 = unpack_bf16x2(pw32[j >> 1]);
+                const float2 p23 = unpack_bf16x2(pw32[(j >> 1) + 1]);
+                const float pe[4] = {p01.x, p01.y, p23.x, p23.y};
+                const float me[4] = {m4.x, m4.y, m4.z, m4.w}, re[4] = {r4.x, r4.y, r4.z, r4.w};
+                const float ge[4] = {g4.x, g4.y, g4.z, g4.w}, be[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float xh = (pe[e] - me[e]) * re[e];
+                  const float y = ge[e] * xh + be[e];
+                  const float slope = (p.bn_act == kActRelu) ? (y > 0.f ? 1.f : 0.f)
+                                                             : (p.bn_act == kActLrelu ? (y > 0.f ? 1.f : 0.2f) : 1.f);
+                  const float dy = valid ? f[j + e] * slope : 0.f;
+                  f[j + e] = dy;
+                  sq[j + e] = dy * xh;
+                }
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                f[j] = valid ? f[j] : 0.f;
+                sq[j] = f[j] * f[j];
+              }
             }
             const float s1 = warp_transpose_reduce32(f);
             const float s2 = warp_transpose_reduce32(sq);
@@ -430,7 +475,7 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
         }
         if (do_stats) {
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          float* gs = p.stats + (size_t)(wi.m0 / p.stat_group_rows) * 2 * p.Cn + wi.n0;
+          float* gs = (do_bnred ? p.bn_red : p.stats) + (size_t)(wi.m0 / p.stat_group_rows) * 2 * p.Cn + wi.n0;
           // (a tile that only pads the last cluster group has no rows and no statistics group)
           for (int i = et; i < BLOCK_N && wi.m0 < p.rows_total; i += kEpiThreads) {
             float t1 = 0.f, t2 = 0.f;
@@ -682,6 +727,19 @@ int dispatch2(int block_n, const CUtensorMap& tg, const CUtensorMap& td, const I
 
 }  // namespace
 
+int igemm2_num_sms() { return num_sms(); }
+int igemm2_max_ctas() { return g_max_ctas; }
+int igemm2_cluster_pref() { return g_cluster; }
+int igemm2_forced_ksplit() { return g_force_ksplit2; }
+int igemm2_tmap_nhwc(const void* ptr, int N, int H, int W, int C, int bw, int bh, int bn, int stride, void* out_map) {
+  return tmap_nhwc(ptr, N, H, W, C, bw, bh, bn, stride, reinterpret_cast<CUtensorMap*>(out_map));
+}
+int igemm2_tmap_2d(const void* ptr, unsigned long long rows, unsigned long long cols, unsigned box_r, unsigned box_c,
+                   void* out_map) {
+  return tmap_2d(ptr, rows, cols, box_r, box_c, reinterpret_cast<CUtensorMap*>(out_map));
+}
+bool igemm2_pixel_box(int rows, int rH, int rW, int* bw, int* bh, int* bn) { return pixel_box(rows, rH, rW, bw, bh, bn); }
+
 void igemm2_set_max_ctas(int v) { g_max_ctas = v > 0 ? v : 0; }
 void igemm2_set_ksplit(int v) { g_force_ksplit2 = (v >= 1 && v <= 16) ? v : 0; }
 void igemm2_set_stage_mode(int v) { g_stage_override = v; }
@@ -741,6 +799,8 @@ static int ilog2_exact(int v) {
   return ((1 << l) == v) ? l : -1;
 }
 
+static int attach_scratch(Igemm2Params* p, long tiles, int block_n);
+int igemm2_attach_scratch(Igemm2Params* p, long tiles, int cols_per_tile) { return attach_scratch(p, tiles, cols_per_tile); }
 static int attach_scratch(Igemm2Params* p, long tiles, int block_n) {
   p->partials = nullptr;
   p->counters = nullptr;
@@ -757,8 +817,9 @@ static int attach_scratch(Igemm2Params* p, long tiles, int block_n) {
 
 int igemm2_conv(int transposed, const void* x, const void* w, const float* bias, void* out, int NB, int H, int W,
                 int Cin, int Cout, int act, int block_n, int b_mn, float* stats, int stat_groups,
-                cudaStream_t stream) {
+                cudaStream_t stream, const BnRedArgs* bnred) {
   if (Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
+  if (bnred != nullptr && (stats != nullptr || bias != nullptr || act != 0)) return DCGAN_ERR_SHAPE;
   if (!transposed && ((H & 1) || (W & 1))) return DCGAN_ERR_SHAPE;
   if (transposed && b_mn) return DCGAN_ERR_SHAPE;
   const int rH = transposed ? H : H / 2, rW = transposed ? W : W / 2;
@@ -780,6 +841,14 @@ int igemm2_conv(int transposed, const void* x, const void* w, const float* bias,
     if (stat_groups < 1 || p.rows_total % stat_groups || (p.rows_total / stat_groups) % kBlockM) return DCGAN_ERR_SHAPE;
     p.stats = stats;
     p.stat_group_rows = p.rows_total / stat_groups;
+  }
+  if (bnred != nullptr) {
+    // slabs are groups of whole images; every 128-row tile must lie inside one slab
+    if (bnred->slabs < 1 || NB % bnred->slabs || ((NB / bnred->slabs) * rH * rW) % kBlockM) return DCGAN_ERR_SHAPE;
+    p.bn_pre = bnred->pre; p.bn_saved = bnred->saved; p.bn_gamma = bnred->gamma; p.bn_beta = bnred->beta;
+    p.bn_red = bnred->red; p.bn_stat_groups = bnred->stat_groups; p.bn_act = bnred->act;
+    p.stat_group_rows = (NB / bnred->slabs) * rH * rW;
+    p.bn_slab_out_rows = (NB / bnred->slabs) * p.oH * p.oW;
   }
   const int cpt = Cin / 64;
   const int mt = (p.rows_total + kBlockM - 1) / kBlockM;

@@ -904,6 +904,7 @@ void dcgan_set_igemm_stage_mode(int v) { igemm2_set_stage_mode(v); }
 void dcgan_set_igemm_cluster(int v) { igemm2_set_cluster(v); }
 int dcgan_set_workspace(void* ptr, size_t bytes) { return igemm2_set_workspace(ptr, bytes); }
 static inline bool use_v2() { return (g_igemm_tuning & 128) == 0; }
+static inline bool use_v3() { return (g_igemm_tuning & 256) == 0; }  // bit 8: per-parity igemm2 transposed conv
 void dcgan_set_wgrad_cta_target(int v) { g_wgrad_cta_target = v > 0 ? v : 148; }
 
 // Host-only view of the launch plan of a strided (transposed = 0) or transposed (1) conv: tile width, split-K
@@ -931,8 +932,14 @@ int dcgan_debug_plan_conv(int transposed, int NB, int H, int W, int Cin, int Cou
 static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                            int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream,
                            float* stats = nullptr, int stat_groups = 1) {
-  if (use_v2())
+  if (use_v2()) {
+    if (use_v3() && b_mn) {  // halo tiles: 10 instead of 25 input tiles per channel chunk
+      const int rc3 = igemm3_fconv(x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n, stats, stat_groups, stream,
+                                   nullptr);
+      if (rc3 != DCGAN_ERR_SHAPE) return rc3;
+    }
     return igemm2_conv(0, x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n, b_mn, stats, stat_groups, stream);
+  }
   if ((H & 1) || (W & 1) || Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
   if ((long)NB * H * W * Cin >= (1L << 31)) return DCGAN_ERR_SHAPE;  // the gather uses 32-bit element offsets
   const int oH = H / 2, oW = W / 2;
@@ -986,9 +993,15 @@ int dcgan_conv_fprop_kn_stats(const void* x, const void* w_kn, const float* bias
 static int conv_tconv_impl(const void* x, const void* w_nk, const float* bias, void* out, int NB, int H, int W,
                            int Cin, int Cout, int act, int block_n, cudaStream_t stream, float* stats,
                            int stat_groups) {
-  if (use_v2())
+  if (use_v2()) {
+    if (use_v3()) {  // parity-fused kernel (9 or 3.75 shifted input tiles per chunk instead of 25)
+      const int rc3 = igemm3_tconv(x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n, stats, stat_groups, stream,
+                                   nullptr);
+      if (rc3 != DCGAN_ERR_SHAPE) return rc3;
+    }
     return igemm2_conv(1, x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n < 0 ? 0 : block_n, 0, stats,
                        stat_groups, stream);
+  }
   if (Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
   if ((long)NB * H * W * Cin >= (1L << 31)) return DCGAN_ERR_SHAPE;  // the gather uses 32-bit element offsets
   const int lh = ilog2_exact(H), lw = ilog2_exact(W);
@@ -1043,6 +1056,33 @@ int dcgan_conv_tconv_stats(const void* x, const void* w_nk, const float* bias, v
                            int stat_groups, int NB, int H, int W, int Cin, int Cout, int block_n,
                            cudaStream_t stream) {
   return conv_tconv_impl(x, w_nk, bias, out, NB, H, W, Cin, Cout, 0, block_n, stream, stats, stat_groups);
+}
+
+// Data-gradient convs whose epilogue also forms the batch-norm backward reductions of the layer they feed
+// (second-generation kernels only; see Igemm2Params::bn_*).
+int dcgan_conv_tconv_bnred(const void* x, const void* w_nk, void* out, const void* pre, const float* saved,
+                           const float* gamma, const float* beta, float* red, int slabs, int stat_groups, int bn_act,
+                           int NB, int H, int W, int Cin, int Cout, int block_n, cudaStream_t stream) {
+  if (!use_v2()) return DCGAN_ERR_SHAPE;
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act};
+  if (use_v3()) {
+    const int rc3 = igemm3_tconv(x, w_nk, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, nullptr, 1, stream, &a);
+    if (rc3 != DCGAN_ERR_SHAPE) return rc3;
+  }
+  return igemm2_conv(1, x, w_nk, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 0, nullptr, 1, stream, &a);
+}
+
+int dcgan_conv_fprop_kn_bnred(const void* x, const void* w_kn, void* out, const void* pre, const float* saved,
+                              const float* gamma, const float* beta, float* red, int slabs, int stat_groups,
+                              int bn_act, int NB, int H, int W, int Cin, int Cout, int block_n,
+                              cudaStream_t stream) {
+  if (!use_v2()) return DCGAN_ERR_SHAPE;
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act};
+  if (use_v3()) {
+    const int rc3 = igemm3_fconv(x, w_kn, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, nullptr, 1, stream, &a);
+    if (rc3 != DCGAN_ERR_SHAPE) return rc3;
+  }
+  return igemm2_conv(0, x, w_kn, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 1, nullptr, 1, stream, &a);
 }
 
 int dcgan_conv_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd,

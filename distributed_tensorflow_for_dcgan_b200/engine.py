@@ -191,6 +191,8 @@ class DCGANEngine:
         # stream next to the data-gradient chain, filling the SMs that the small grids leave idle
         self.wgrad_overlap = os.environ.get("DCGAN_WGRAD_OVERLAP", "1") != "0"
         self.fuse_head_loss = os.environ.get("DCGAN_FUSE_HEAD_LOSS", "1") != "0"
+        self.fuse_bn_bwd = (os.environ.get("DCGAN_FUSE_BN_BWD", "1") != "0"
+                            and (int(os.environ.get("DCGAN_IGEMM_TUNING", "1")) & 128) == 0)
         # measured: 0.876 -> 0.815 ms/step on one GPU, 0.958 -> 0.905 on two (profiles/README.md)
         self.prioritize_main = os.environ.get("DCGAN_MAIN_PRIORITY", "1") != "0"
         self.split_d_forward = self.wgrad_overlap and os.environ.get("DCGAN_SPLIT_D_FORWARD", "0") != "0"
@@ -313,13 +315,29 @@ class DCGANEngine:
     # ------------------------------------------------------------------------------------------------
     # backward
     # ------------------------------------------------------------------------------------------------
-    def _bn_bwd(self, name, da, pre, dpre):
+    def _bnred_fusable(self, name, da, tile_rows_per_image) -> bool:
+        """The data-gradient conv that produces ``da`` can form this layer's backward reductions in its epilogue
+        when every 128-row tile of that conv lies in one slab (``DCGAN_FUSE_BN_BWD=0`` turns the fusion off)."""
+        if not self.fuse_bn_bwd:
+            return False
+        imgs_per_slab = da.shape[0] // self.bn[name]["slabs"]
+        return (imgs_per_slab * tile_rows_per_image) % 128 == 0
+
+    def _dgrad_bnred(self, name, x, w, da, pre, transposed):
+        """dgrad conv writing ``da`` + the batch-norm backward reductions of layer ``name`` in one launch."""
+        st = self.bn[name]
+        p = self.params
+        K.conv_dgrad_bnred(x, w, da, pre, st["saved"], p[f"{name}/gamma"], p[f"{name}/beta"], st["red"],
+                           st["slabs"], st["groups"], st["act"], transposed)
+
+    def _bn_bwd(self, name, da, pre, dpre, reduce_done=False):
         st = self.bn[name]
         C = st["C"]
         p, g = self.params, self.grad_views
         slabs, G = st["slabs"], st["groups"]
-        K.bn_bwd_reduce(da.view(-1, C), pre.view(-1, C), st["saved"], p[f"{name}/gamma"], p[f"{name}/beta"],
-                        st["red"], slabs, G, st["act"])
+        if not reduce_done:
+            K.bn_bwd_reduce(da.view(-1, C), pre.view(-1, C), st["saved"], p[f"{name}/gamma"], p[f"{name}/beta"],
+                            st["red"], slabs, G, st["act"])
         if self._sync_bn_active():
             self.comm.allreduce_bn(st["red"])
         K.bn_bwd_apply(da.view(-1, C), pre.view(-1, C), dpre.view(-1, C), st["saved"], p[f"{name}/gamma"],
@@ -370,13 +388,21 @@ class DCGANEngine:
         else:
             K.head_bwd(self.d_act[3].view(2 * B, -1), p["d_h3_lin/Matrix"], self.dlogit,
                        self.dd_act[3].view(3 * B, -1), g["d_h3_lin/Matrix"], g["d_h3_lin/bias"], B)
+        red_done = False   # d_bn3's upstream gradient comes from the head kernel, not from a conv
         for i in (3, 2, 1):
-            self._bn_bwd(f"d_bn{i}", self.dd_act[i], self.d_pre[i], self.dd_pre[i])
+            self._bn_bwd(f"d_bn{i}", self.dd_act[i], self.d_pre[i], self.dd_pre[i], reduce_done=red_done)
             ci, co = self.d_ch[i], self.d_ch[i + 1]
             with self._off_critical_path():
                 K.conv_wgrad(self.d_act[i - 1], self.dd_pre[i][:2 * B], g[f"d_h{i}_conv/w"].view(25, ci, co))
-            K.conv_tconv(self.dd_pre[i], self.w_native[f"d_h{i}_conv/w"].view(25, ci, co), None,
-                         out=self.dd_act[i - 1])
+            w = self.w_native[f"d_h{i}_conv/w"].view(25, ci, co)
+            # the data gradient lands in dd_act[i-1]; for i > 1 that is the input of d_bn{i-1}'s backward pass,
+            # whose two reductions the conv's epilogue forms on the fly
+            red_done = i > 1 and self._bnred_fusable(f"d_bn{i - 1}", self.dd_act[i - 1],
+                                                     self.d_sz[i + 1] * self.d_sz[i + 1])
+            if red_done:
+                self._dgrad_bnred(f"d_bn{i - 1}", self.dd_pre[i], w, self.dd_act[i - 1], self.d_pre[i - 1], True)
+            else:
+                K.conv_tconv(self.dd_pre[i], w, None, out=self.dd_act[i - 1])
         C0 = self.d_ch[1]
         K.act_bwd(self.dd_act[0].view(-1, C0), self.d_act[0].view(-1, C0), self.dd_pre[0].view(-1, C0),
                   g["d_h0_conv/biases"], "lrelu", bias_rows=2 * B * self.d_sz[1] * self.d_sz[1])
@@ -392,13 +418,19 @@ class DCGANEngine:
         with self._off_critical_path():
             K.c3_wgrad(self.dimg, self.g_act[3], g["g_h4/w"])
         K.c3_fprop(self.dimg, p["g_h4/w"], None, out=self.dg_act[3])
+        red_done = False   # g_bn3's upstream gradient comes from the 3-channel kernel
         for i in (3, 2, 1):
-            self._bn_bwd(f"g_bn{i}", self.dg_act[i], self.g_pre[i], self.dg_pre[i])
+            self._bn_bwd(f"g_bn{i}", self.dg_act[i], self.g_pre[i], self.dg_pre[i], reduce_done=red_done)
             co, ci = self.g_ch[i], self.g_ch[i - 1]
             with self._off_critical_path():
                 K.conv_wgrad(self.dg_pre[i], self.g_act[i - 1], g[f"g_h{i}/w"].view(25, co, ci))
-            K.conv_fprop_kn(self.dg_pre[i], self.w_native[f"g_h{i}/w"].view(25, co, ci), None, out=self.dg_act[i - 1])
-        self._bn_bwd("g_bn0", self.dg_act[0], self.g_pre[0], self.dg_pre[0])
+            w = self.w_native[f"g_h{i}/w"].view(25, co, ci)
+            red_done = self._bnred_fusable(f"g_bn{i - 1}", self.dg_act[i - 1], self.g_sz[i - 1] * self.g_sz[i - 1])
+            if red_done:
+                self._dgrad_bnred(f"g_bn{i - 1}", self.dg_pre[i], w, self.dg_act[i - 1], self.g_pre[i - 1], False)
+            else:
+                K.conv_fprop_kn(self.dg_pre[i], w, None, out=self.dg_act[i - 1])
+        self._bn_bwd("g_bn0", self.dg_act[0], self.g_pre[0], self.dg_pre[0], reduce_done=red_done)
         K.lin_wgrad(self.z, self.dg_pre[0].view(B, -1), g["g_h0_lin/Matrix"], g["g_h0_lin/bias"])
 
     # ------------------------------------------------------------------------------------------------

@@ -24,6 +24,8 @@ _SIGNATURES = {
     "dcgan_conv_fprop_kn_stats": "pppppiiiiiiis",
     "dcgan_conv_tconv_stats": "pppppiiiiiiis",
     "dcgan_conv_wgrad": "pppiiiiiiis",
+    "dcgan_conv_tconv_bnred": "ppppppppiiiiiiiiis",
+    "dcgan_conv_fprop_kn_bnred": "ppppppppiiiiiiiiis",
     "dcgan_c3_fprop": "ppppiiiiis",
     "dcgan_c3_tconv": "ppppppiiiiiis",
     "dcgan_c3_wgrad": "pppiiiis",

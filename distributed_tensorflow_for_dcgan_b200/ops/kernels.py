@@ -64,6 +64,17 @@ def conv_tconv_stats(x, w_nk, bias, out, stats, groups, block_n=0):
     return out
 
 
+def conv_dgrad_bnred(x, w, out, pre, saved, gamma, beta, red, slabs, stat_groups, act, transposed, block_n=0):
+    """Data-gradient conv (transposed: w [25,Cout,Cin]; strided: w [25,Cin,Cout]) whose epilogue also accumulates
+    the batch-norm backward reductions ``red [slabs,2,Cout]`` of the layer that ``out`` is the activation gradient
+    of (``pre`` / ``saved`` / ``gamma`` / ``beta`` are that layer's)."""
+    N, H, W, Cin = x.shape
+    Cout = w.shape[1] if transposed else w.shape[2]
+    call("dcgan_conv_tconv_bnred" if transposed else "dcgan_conv_fprop_kn_bnred", ptr(x), ptr(w), ptr(out), ptr(pre),
+         ptr(saved), ptr(gamma), ptr(beta), ptr(red), slabs, stat_groups, ACT[act], N, H, W, Cin, Cout, block_n)
+    return out
+
+
 def conv_wgrad(big, small, dw, splits=0, block_n=0):
     """dw[25,Cg,Cd] (f32, +=) from big [N,2Hs,2Ws,Cg] and small [N,Hs,Ws,Cd]."""
     N, Hs, Ws, Cd = small.shape

@@ -49,7 +49,8 @@ void dcgan_set_pdl(int v);
 
 /* Profiling switch for the implicit-GEMM kernels.  Bit 7 (128) selects the first-generation kernels (cp.async
  * gather, csrc/igemm_sm100.cu) instead of the TMA-fed persistent ones (csrc/igemm2_sm100.cu); the other bits
- * only act on the first generation: bit 0 = two CTAs per SM (default on). */
+ * only act on the first generation: bit 0 = two CTAs per SM (default on).  Bit 8 (256) runs the transposed conv as
+ * four per-parity GEMMs (igemm2) instead of the parity-fused kernel with halo rows (csrc/igemm3_sm100.cu). */
 void dcgan_set_igemm_tuning(int v);
 /* Second-generation kernels: cap on the persistent grid (0 = one CTA per SM), stage-ring depth (1 = shallow),
  * CTAs per cluster that share the filter tile by TMA multicast (0 = default, 1 / 2 / 4 forced). */
@@ -109,8 +110,23 @@ int dcgan_conv_tconv_stats(const void* x, const void* w_nk, const float* bias, v
                            int stat_groups, int NB, int H, int W, int Cin, int Cout, int block_n,
                            cudaStream_t stream);
 
-/* Weight gradient of either layer kind: dw[25][Cg][Cd] (f32, accumulated with atomics -- zero it
- * first) += sum over pixels of big[NB,2Hs,2Ws,Cg] (gathered at 2q+k-1) * small[NB,Hs,Ws,Cd].
+/* Data-gradient convs (no bias, no activation) that also accumulate, in their epilogue, the batch-norm backward
+ * reductions of the layer whose activation gradient they produce: with pre = that layer's saved pre-activations
+ * [stat_groups * rows][Cout] and saved = its (mean, rstd) [stat_groups][2][Cout],
+ *   dy = out * act'(gamma * xhat + beta),  red[slab][0][c] += sum dy,  red[slab][1][c] += sum dy * xhat
+ * -- the result of dcgan_bn_bwd_reduce without its extra pass over out and pre (autodiff of the reference's
+ * batch_norm, distriubted_model.py:15-52).  The NB images are `slabs` equal groups; slab g reads the statistics
+ * of group min(g, stat_groups - 1); (NB / slabs) images must fill whole 128-row tiles. */
+int dcgan_conv_tconv_bnred(const void* x, const void* w_nk, void* out, const void* pre, const float* saved,
+                           const float* gamma, const float* beta, float* red, int slabs, int stat_groups, int bn_act,
+                           int NB, int H, int W, int Cin, int Cout, int block_n, cudaStream_t stream);
+int dcgan_conv_fprop_kn_bnred(const void* x, const void* w_kn, void* out, const void* pre, const float* saved,
+                              const float* gamma, const float* beta, float* red, int slabs, int stat_groups,
+                              int bn_act, int NB, int H, int W, int Cin, int Cout, int block_n,
+                              cudaStream_t stream);
+
+/* Weight gradient of either layer kind: dw[25][Cg][Cd] (f32, += -- zero it first; the second-generation kernels add each element once, split-K partials are
+ * summed in a fixed order, so the result is reproducible bit for bit) += sum over pixels of big[NB,2Hs,2Ws,Cg] (gathered at 2q+k-1) * small[NB,Hs,Ws,Cd].
  * conv2d:  big = layer input, small = output gradient  -> dw is HWIO.
  * deconv:  big = output gradient, small = layer input  -> dw is [kh,kw,Cout,Cin].
  * (autodiff of reference image_train.py:109-112).  splits <= 0 picks a split-K factor. */

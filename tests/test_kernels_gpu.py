@@ -401,3 +401,79 @@ def test_cluster_split_k_matches_single_cta(cuda_lib):
     xp = torch.nn.functional.pad(x.float().permute(0, 3, 1, 2), (1, 2, 1, 2))
     ref = torch.nn.functional.conv2d(xp, w_kn.float().view(5, 5, 256, 128).permute(3, 2, 0, 1), stride=2)
     _close(outs[4][0], ref.permute(0, 2, 3, 1), rel=2e-2, name="split-K 4 vs torch conv2d")
+
+
+@pytest.mark.parametrize("transposed", [True, False])
+def test_dgrad_epilogue_forms_bn_backward_reductions(cuda_lib, transposed):
+    """The data-gradient conv's epilogue accumulates sum(dy) and sum(dy * xhat) of the batch-norm layer below
+    (dy = da * act'(gamma * xhat + beta)) -- checked against plain fp32 PyTorch: conv(-transpose) for da, then the
+    two reductions, per slab, with slab 2 reading the statistics of group 1 (the discriminator's g_loss slab)."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    slabs, groups = (3, 2) if transposed else (1, 1)
+    B = 8
+    N = slabs * B
+    if transposed:   # da [N, 16, 16, 64] from x [N, 8, 8, 128]
+        H, Cin, Cout, oH = 8, 128, 64, 16
+        x = _rand((N, H, H, Cin), 0.5)
+        w = _rand((25, Cout, Cin), 0.05)                                   # [tap][Cout][Cin]
+        wt = w.float().view(5, 5, Cout, Cin).permute(3, 2, 0, 1)           # conv_transpose2d weight [Cin, Cout, kh, kw]
+        full = torch.nn.functional.conv_transpose2d(x.float().permute(0, 3, 1, 2), wt, stride=2)
+        da_ref = full[:, :, 1:1 + 2 * H, 1:1 + 2 * H].permute(0, 2, 3, 1).contiguous()
+        act = "lrelu"
+    else:            # da [N, 8, 8, 128] from x [N, 16, 16, 64]
+        H, Cin, Cout, oH = 16, 64, 128, 8
+        x = _rand((N, H, H, Cin), 0.5)
+        w = _rand((25, Cin, Cout), 0.05)                                   # TensorFlow layout [tap][Cin][Cout]
+        xp = torch.nn.functional.pad(x.float().permute(0, 3, 1, 2), (1, 2, 1, 2))
+        da_ref = torch.nn.functional.conv2d(xp, w.float().view(5, 5, Cin, Cout).permute(3, 2, 0, 1), stride=2)
+        da_ref = da_ref.permute(0, 2, 3, 1).contiguous()
+        act = "relu"
+    pre = _rand((groups * B, oH, oH, Cout))
+    gamma = 1 + 0.1 * torch.randn(Cout, device="cuda")
+    beta = 0.1 * torch.randn(Cout, device="cuda")
+    saved = torch.empty(groups, 2, Cout, device="cuda")
+    pf = pre.float().view(groups, -1, Cout)
+    saved[:, 0] = pf.mean(1)
+    saved[:, 1] = (pf.var(1, unbiased=False) + 1e-5).rsqrt()
+    red = torch.zeros(slabs, 2, Cout, device="cuda")
+    da = torch.empty(N, oH, oH, Cout, device="cuda", dtype=torch.bfloat16)
+    K.conv_dgrad_bnred(x, w, da, pre, saved, gamma, beta, red, slabs, groups, act, transposed)
+    K.check_device_error()
+    _close(da, da_ref, name="data gradient")
+    exp = torch.zeros_like(red)
+    for g in range(slabs):
+        sg = min(g, groups - 1)
+        xh = (pf[sg] - saved[sg, 0]) * saved[sg, 1]
+        y = gamma * xh + beta
+        slope = (y > 0).float() if act == "relu" else torch.where(y > 0, 1.0, 0.2)
+        dy = da_ref[g * B:(g + 1) * B].reshape(-1, Cout) * slope
+        exp[g, 0] = dy.sum(0)
+        exp[g, 1] = (dy * xh).sum(0)
+    _close(red, exp, rel=5e-3, name="fused bn backward reductions")
+    # and the stand-alone reduction kernel, fed the bf16 data gradient, agrees with the fused epilogue
+    red2 = torch.zeros_like(red)
+    K.bn_bwd_reduce(da.view(-1, Cout), pre.view(-1, Cout), saved, gamma, beta, red2, slabs, groups, act)
+    _close(red, red2, rel=5e-3, name="fused vs stand-alone reduction")
+
+
+def test_filter_gradient_is_reproducible(cuda_lib):
+    """Split-K partial tiles are summed in slice order by the slice that arrives last, so two runs of the filter
+    gradient agree bit for bit (the first-generation kernel accumulated with f32 atomics)."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    big, small = _rand((32, 16, 16, 64)), _rand((32, 8, 8, 128))
+    outs = []
+    for _ in range(3):
+        dw = torch.zeros(25, 64, 128, device="cuda")
+        K.conv_wgrad(big, small, dw, splits=5)
+        outs.append(dw.clone())
+    K.check_device_error()
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    x = _rand((16, 8, 8, 256), 0.5)
+    w_kn = _rand((25, 256, 128), 0.05)
+    try:
+        cuda_lib.dcgan_set_igemm_ksplit(4)
+        a = K.conv_fprop_kn(x, w_kn, None, block_n=64)
+        b = K.conv_fprop_kn(x, w_kn, None, block_n=64)
+    finally:
+        cuda_lib.dcgan_set_igemm_ksplit(0)
+    assert torch.equal(a, b)
