@@ -14,7 +14,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(ROOT, "csrc")
 PKG = os.path.join(ROOT, "distributed_tensorflow_for_dcgan_b200")
 LIB = os.path.join(PKG, "lib", "libdcgan_b200.so")
-SOURCES = ["igemm_sm100.cu", "igemm2_sm100.cu", "igemm3_sm100.cu", "runtime.cu", "bn_act.cu", "heads_optim.cu", "conv_c3.cu", "conv_c3_tc.cu", "comm_sm100.cu"]
+SOURCES = ["igemm_sm100.cu", "igemm2_sm100.cu", "runtime.cu", "bn_act.cu", "heads_optim.cu", "conv_c3.cu", "conv_c3_tc.cu", "comm_sm100.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "igemm2.h"),

@@ -135,17 +135,6 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m
       : "memory");
 }
 
-// 2-D tiled load delivered to the same shared-memory offset of every CTA in `cta_mask` (thread-block cluster);
-// each destination CTA's mbarrier at the same offset receives the complete_tx.
-__device__ __forceinline__ void tma_load_2d_mc(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1,
-                                               uint16_t cta_mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(smem_dst)),
-      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(cta_mask)
-      : "memory");
-}
-
 // ---------------------------------------------------------------------------------------------
 // tcgen05 / TMEM
 // ---------------------------------------------------------------------------------------------
@@ -178,20 +167,30 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// One lane of a converged warp.  The MMA / TMA issuing warps run their loops with all 32 lanes (uniform control flow
+// lets the compiler keep ring state, addresses and descriptors in uniform registers, which is what UTCHMMA / UTMALDG
+// take their operands from); only the issuing instructions are predicated on the elected lane.  A lone lane under
+// `if (lane == 0)` measured ~550 cycles of R2UR conversions and dependent integer chains per 4-MMA ring slot.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+  return pred != 0;
+}
+// SWIZZLE_128B shared-memory descriptor in two words: the high word is constant per operand kind, the low word
+// carries the start address (and the leading byte offset) and is what advances from MMA to MMA.
+__host__ __device__ constexpr uint32_t smem_desc_hi_sw128(uint32_t sbo_bytes) {
+  return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
+}
+__device__ __forceinline__ uint32_t smem_desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+__device__ __forceinline__ uint64_t smem_desc_join(uint32_t hi, uint32_t lo) { return ((uint64_t)hi << 32) | lo; }
+
 // all previously issued MMAs of this thread arrive on `bar` when they retire
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                    smem_u32(bar))
                : "memory");
-}
-// same, arriving on the barrier at this shared-memory offset in every CTA of `cta_mask` (cluster multicast):
-// a smem slot filled by multicast TMA is free only when every consumer in the cluster has released it
-__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t cta_mask) {
-  asm volatile(
-      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-          smem_u32(bar)),
-      "h"(cta_mask)
-      : "memory");
 }
 // 32 lanes x 32 consecutive columns (one f32 each) -> 32 registers per thread
 __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32]) {

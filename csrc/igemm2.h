@@ -18,9 +18,7 @@ struct Igemm2Params {
   int num_kb;            // F: 25 * gC / 64.  W: pixels / 64.  T: derived per parity class
   int m_tiles, n_tiles;  // tile grid (T: per parity class; W: per filter tap)
   int ksplit;            // K slices per tile
-  int cluster;           // CTAs per thread-block cluster: consecutive M tiles that share (multicast) the filter tile
-  int m_groups;          // ceil(m_tiles / cluster)
-  int total_groups;      // work groups (one per cluster and iteration): tiles / cluster * ksplit
+  int total_groups;      // work items of the static schedule: tiles * ksplit
   int b_mn;              // F: filter is [25][Ck][Cn] (TensorFlow layout) -> MN-major B operand
   // epilogue
   void* out;              // F/T: bf16 NHWC.  W: f32 [25][Cn][Cd]
@@ -41,10 +39,6 @@ struct Igemm2Params {
   int bn_slab_out_rows;   // output rows (pixels) per slab
   int bn_stat_groups;     // slab g uses the statistics / pre-activations of group min(g, bn_stat_groups - 1)
   int bn_act;             // the layer's activation (ReLU / LeakyReLU)
-  // third-generation transposed conv (igemm3_sm100.cu)
-  int halo;               // X tiles carry two halo rows; the vertical shift is a descriptor offset
-  int halo_row_bytes;     // W * 128: one image row of the X tile
-  int x_tile_bytes;       // bytes of one X tile (TMA transaction size)
   float* partials;        // split-K scratch: [tile][slice][BLOCK_N / 4][128] float4
   int* counters;          // split-K arrival counters per tile (zero between launches)
   int* err_flag;          // sticky device error flag (csrc/runtime.cu)
@@ -69,16 +63,6 @@ int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, 
 // (tile width, K slices) for `tiles_bn64` 64-wide tiles of `kb_per_tile` k-blocks on the persistent grid
 void igemm2_plan(long tiles_bn64, double kb_per_tile, int Cn, int min_kb, int force_bn, int* block_n, int* ksplit);
 
-// Transposed conv with the four output parities fused in one CTA (igemm3_sm100.cu); same contract as
-// igemm2_conv(transposed = 1, ...).  Returns DCGAN_ERR_SHAPE for shapes it does not take (caller falls back).
-int igemm3_tconv(const void* x, const void* w, const float* bias, void* out, int NB, int H, int W, int Cin, int Cout,
-                 int act, int block_n, float* stats, int stat_groups, cudaStream_t stream, const BnRedArgs* bnred);
-
-// Strided conv with halo tiles (TensorFlow filter layout only); DCGAN_ERR_SHAPE when the layer's tiles are not whole
-// image rows (caller falls back to igemm2_conv).
-int igemm3_fconv(const void* x, const void* w_kn, const float* bias, void* out, int NB, int H, int W, int Cin, int Cout,
-                 int act, int block_n, float* stats, int stat_groups, cudaStream_t stream, const BnRedArgs* bnred);
-
 // helpers of igemm2_sm100.cu shared with igemm3_sm100.cu
 struct CUtensorMap_st;
 int igemm2_tmap_nhwc(const void* ptr, int N, int H, int W, int C, int bw, int bh, int bn, int stride, void* out_map);
@@ -88,13 +72,11 @@ bool igemm2_pixel_box(int rows, int rH, int rW, int* bw, int* bh, int* bn);
 int igemm2_attach_scratch(Igemm2Params* p, long tiles, int cols_per_tile);
 int igemm2_num_sms();
 int igemm2_max_ctas();
-int igemm2_cluster_pref();
 int igemm2_forced_ksplit();
 
 void igemm2_set_max_ctas(int v);
 void igemm2_set_ksplit(int v);
 void igemm2_set_stage_mode(int v);
-void igemm2_set_cluster(int v);
 int igemm2_set_workspace(void* ptr, size_t bytes);
 
 }  // namespace dcgan

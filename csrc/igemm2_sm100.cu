@@ -62,11 +62,9 @@ struct WorkItem {
   int tap;       // W: filter tap
 };
 
-// Work item of cluster rank `r` in work group `u`.  A group is `p.cluster` tiles that differ only in their
-// M tile (consecutive M tiles): they walk the same K range against the same filter tile, which is therefore
-// fetched from L2 once per cluster and multicast (F/T).  W runs with clusters of one.
+// Work item `u` of the static schedule (tile x K slice).
 template <int MODE, int BLOCK_N>
-__device__ __forceinline__ WorkItem decode_work(int u, int r, const Igemm2Params& p) {
+__device__ __forceinline__ WorkItem decode_work(int u, const Igemm2Params& p) {
   WorkItem it;
   it.ks = u % p.ksplit;
   const int t = u / p.ksplit;
@@ -81,21 +79,17 @@ __device__ __forceinline__ WorkItem decode_work(int u, int r, const Igemm2Params
     it.m0 = (q / p.n_tiles) * kBlockM;
     total_kb = p.num_kb;
   } else if (MODE == MODE_F) {
-    const int mt = (t % p.m_groups) * p.cluster + r;  // neighbouring clusters share the filter tile as well
-    const int nt = t / p.m_groups;
-    it.m0 = mt * kBlockM;
-    it.n0 = nt * BLOCK_N;
-    it.tile = nt * (p.m_groups * p.cluster) + mt;
+    it.m0 = (t % p.m_tiles) * kBlockM;  // neighbouring CTAs share the filter tile (L2)
+    it.n0 = (t / p.m_tiles) * BLOCK_N;
+    it.tile = t;
     total_kb = p.num_kb;
   } else {
-    const int per_class = p.m_groups * p.n_tiles;
+    const int per_class = p.m_tiles * p.n_tiles;
     const int rank = t / per_class;  // 0: 3x3 taps, 1: 3x2, 2: 2x3, 3: 2x2 -- the long K loops are scheduled first
     const int q = t - rank * per_class;
-    const int mt = (q % p.m_groups) * p.cluster + r;
-    const int nt = q / p.m_groups;
-    it.m0 = mt * kBlockM;
-    it.n0 = nt * BLOCK_N;
-    it.tile = (rank * p.n_tiles + nt) * (p.m_groups * p.cluster) + mt;
+    it.m0 = (q % p.m_tiles) * kBlockM;
+    it.n0 = (q / p.m_tiles) * BLOCK_N;
+    it.tile = t;
     it.ph = 1 - (rank >> 1);
     it.pw = 1 - (rank & 1);
     total_kb = (it.ph ? 3 : 2) * (it.pw ? 3 : 2) * (p.gC / kBlockK);
@@ -103,17 +97,6 @@ __device__ __forceinline__ WorkItem decode_work(int u, int r, const Igemm2Params
   it.kb0 = (it.ks * total_kb) / p.ksplit;
   it.nkb = ((it.ks + 1) * total_kb) / p.ksplit - it.kb0;
   return it;
-}
-
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-// every thread of every CTA in the cluster takes part (non-.aligned forms: callers may be diverged)
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
 }
 
 __device__ __forceinline__ float4 ldcg_f4(const float4* p) {
@@ -126,8 +109,8 @@ __device__ __forceinline__ void stcg_f4(float4* p, float4 v) {
                : "memory");
 }
 
-template <int MODE, int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int MODE, int BLOCK_N, int STAGES, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
 igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 4-D NHWC activation tensor
               const __grid_constant__ CUtensorMap tmap_d,  // dense operand: 2-D (filter, or W: the small activation)
               const Igemm2Params p) {
@@ -148,15 +131,12 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
   const int warp = tid >> 5;
   const int lane = tid & 31;
 
-  const int csize = p.cluster;                                  // CTAs that share (multicast) the filter tile
-  const int crank = (csize > 1) ? (int)cluster_ctarank() : 0;
-  const uint16_t cmask = (uint16_t)((1u << csize) - 1u);
-  const int first_group = blockIdx.x / csize;                   // clusters are consecutive in x
-  const int group_step = gridDim.x / csize;
+  const int first_group = blockIdx.x;
+  const int group_step = gridDim.x;
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], csize);  // every consumer of the cluster releases the slot (multicast B)
+      mbar_init(&empty_bar[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull_bar[a], 1);
@@ -174,7 +154,6 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
   }
   tc_fence_before();
   __syncthreads();
-  if (csize > 1) cluster_sync_all();  // peers' barriers are initialised before anything is multicast at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   pdl_wait();  // set-up above overlaps the previous kernel's tail; global memory is touched from here on
@@ -184,12 +163,13 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
 
   if (warp == 0) {
     // =================================== TMA producer ==========================================
-    if (lane == 0) {
+    // all 32 lanes walk the schedule (uniform control flow); the elected lane arms the barrier and issues the copies
+    {
       int s = 0;
       uint32_t phase = 0;
       bool ok = true;
       for (int u = first_group; u < p.total_groups && ok; u += group_step) {
-        const WorkItem wi = decode_work<MODE, BLOCK_N>(u, crank, p);
+        const WorkItem wi = decode_work<MODE, BLOCK_N>(u, p);
         // origin of the tile's pixel box (F/T); the box always starts at column 0
         const int img0 = wi.m0 >> (p.rW_log2 + p.rH_log2);
         const int h0 = (wi.m0 >> p.rW_log2) & (rH - 1);
@@ -207,6 +187,7 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
           if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
           uint8_t* sA = smem + s * L::kStageBytes;
           uint8_t* sB = sA + kATileBytes;
+          if (elect_one()) {
           mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
           if (MODE == MODE_W) {
             const int px0 = (wi.kb0 + kb) * kBlockK;
@@ -229,53 +210,41 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
               const int kw = wi.pw ? 2 * tb : 2 * tb + 1;
               tap = kh * 5 + kw;
             }
-            if (csize == 1) {
-              if (p.b_mn) {  // TensorFlow layout [tap][Ck][Cn]: 64(k) x 64(n) boxes, one per 64 output channels
+            if (p.b_mn) {  // TensorFlow layout [tap][Ck][Cn]: 64(k) x 64(n) boxes, one per 64 output channels
 #pragma unroll
-                for (int j = 0; j < BLOCK_N / 64; ++j)
-                  tma_load_2d(sB + j * 8192, &tmap_d, &full_bar[s], wi.n0 + 64 * j, tap * p.gC + cc * kBlockK);
-              } else {
-                tma_load_2d(sB, &tmap_d, &full_bar[s], cc * kBlockK, tap * p.Cn + wi.n0);
-              }
+              for (int j = 0; j < BLOCK_N / 64; ++j)
+                tma_load_2d(sB + j * 8192, &tmap_d, &full_bar[s], wi.n0 + 64 * j, tap * p.gC + cc * kBlockK);
             } else {
-              // this CTA fetches 1/csize of the filter tile and the TMA unit delivers it to every CTA of the cluster
-              if (p.b_mn) {  // slice of the k rows of every 64 x 64 box
-                const int kr = 64 / csize;
-#pragma unroll
-                for (int j = 0; j < BLOCK_N / 64; ++j)
-                  tma_load_2d_mc(sB + j * 8192 + crank * kr * 128, &tmap_d, &full_bar[s], wi.n0 + 64 * j,
-                                 tap * p.gC + cc * kBlockK + crank * kr, cmask);
-              } else {       // slice of the output-channel rows
-                const int nr = BLOCK_N / csize;
-                tma_load_2d_mc(sB + crank * nr * 128, &tmap_d, &full_bar[s], cc * kBlockK,
-                               tap * p.Cn + wi.n0 + crank * nr, cmask);
-              }
+              tma_load_2d(sB, &tmap_d, &full_bar[s], cc * kBlockK, tap * p.Cn + wi.n0);
             }
-            if (++cc == cpt) { cc = 0; if (++tb == nb) { tb = 0; ++ta; } }
           }
+          }
+          __syncwarp();
+          if (MODE != MODE_W) { if (++cc == cpt) { cc = 0; if (++tb == nb) { tb = 0; ++ta; } } }
           if (++s == STAGES) { s = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // =================================== MMA issuer ============================================
-    if (lane == 0) {
+    // all 32 lanes walk the schedule; the tcgen05 instructions run on the elected lane
+    {
       constexpr bool kMN = (MODE == MODE_W);
       const bool b_mn = kMN || (p.b_mn != 0);
       const uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, kMN, b_mn);
       const bool swap = (kMN || b_mn) && (*p.mn_variant != 0);
       const uint32_t lbo = kMN ? (swap ? 1024u : 8192u) : 16u;
-      const uint32_t sbo = kMN ? (swap ? 8192u : 1024u) : 1024u;
-      const uint32_t kstep = kMN ? 2048u : 32u;  // bytes per UMMA_K = 16 step
+      const uint32_t hi_a = smem_desc_hi_sw128(kMN ? (swap ? 8192u : 1024u) : 1024u);
+      const uint32_t kstep = (kMN ? 2048u : 32u) >> 4;  // descriptor address units per UMMA_K = 16 step
       const uint32_t lbo_b = b_mn ? (swap ? 1024u : 8192u) : 16u;
-      const uint32_t sbo_b = b_mn ? (swap ? 8192u : 1024u) : 1024u;
-      const uint32_t kstep_b = b_mn ? 2048u : 32u;
+      const uint32_t hi_b = smem_desc_hi_sw128(b_mn ? (swap ? 8192u : 1024u) : 1024u);
+      const uint32_t kstep_b = (b_mn ? 2048u : 32u) >> 4;
       int s = 0;
       uint32_t phase = 0;
       int ti = 0;
       bool ok = true;
       for (int u = first_group; u < p.total_groups && ok; u += group_step, ++ti) {
-        const WorkItem wi = decode_work<MODE, BLOCK_N>(u, crank, p);
+        const WorkItem wi = decode_work<MODE, BLOCK_N>(u, p);
         const int a = ti & 1;
         // the epilogue must have drained this accumulator (two tiles ago)
         if (!mbar_wait(&tempty_bar[a], ((ti >> 1) & 1) ^ 1, abort_flag, p.err_flag)) break;
@@ -285,19 +254,22 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
           if (!mbar_wait(&full_bar[s], phase, abort_flag, p.err_flag)) { ok = false; break; }
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
-          const uint32_t b_addr = a_addr + kATileBytes;
+          const uint32_t a_lo = smem_desc_lo(a_addr, lbo);
+          const uint32_t b_lo = smem_desc_lo(a_addr + kATileBytes, lbo_b);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k) {
-            const uint64_t da = make_smem_desc_sw128(a_addr + k * kstep, lbo, sbo);
-            const uint64_t db = make_smem_desc_sw128(b_addr + k * kstep_b, lbo_b, sbo_b);
-            umma_bf16(tacc, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < kBlockK / 16; ++k)
+              umma_bf16(tacc, smem_desc_join(hi_a, a_lo + k * kstep), smem_desc_join(hi_b, b_lo + k * kstep_b), idesc,
+                        (kb | k) != 0 ? 1u : 0u);
+            umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs retire
           }
-          // frees the smem slot once these MMAs retire -- in every CTA of the cluster, whose producers all write it
-          if (csize == 1) umma_commit(&empty_bar[s]);
-          else umma_commit_mc(&empty_bar[s], cmask);
+          __syncwarp();
           if (++s == STAGES) { s = 0; phase ^= 1; }
         }
-        if (ok) umma_commit(&tfull_bar[a]);  // accumulator complete
+        if (ok) {
+          if (elect_one()) umma_commit(&tfull_bar[a]);  // accumulator complete
+          __syncwarp();
+        }
       }
     }
   } else {
@@ -310,7 +282,7 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
     int ti = 0;
     bool ok = true;
     for (int u = first_group; u < p.total_groups && ok; u += group_step, ++ti) {
-      const WorkItem wi = decode_work<MODE, BLOCK_N>(u, crank, p);
+      const WorkItem wi = decode_work<MODE, BLOCK_N>(u, p);
       const int a = ti & 1;
       if (!mbar_wait(&tfull_bar[a], (ti >> 1) & 1, abort_flag, p.err_flag)) { ok = false; break; }
       tc_fence_after();
@@ -476,7 +448,6 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
         if (do_stats) {
           asm volatile("bar.sync 1, 128;" ::: "memory");
           float* gs = (do_bnred ? p.bn_red : p.stats) + (size_t)(wi.m0 / p.stat_group_rows) * 2 * p.Cn + wi.n0;
-          // (a tile that only pads the last cluster group has no rows and no statistics group)
           for (int i = et; i < BLOCK_N && wi.m0 < p.rows_total; i += kEpiThreads) {
             float t1 = 0.f, t2 = 0.f;
 #pragma unroll
@@ -512,7 +483,6 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
   // ---- teardown ---------------------------------------------------------------------------------
   tc_fence_before();
   __syncthreads();
-  if (csize > 1) cluster_sync_all();  // no CTA leaves while a peer may still multicast into it or signal its barriers
   if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
@@ -668,12 +638,15 @@ int num_sms() {
 int g_max_ctas = 0;        // 0 = one CTA per SM
 int g_force_ksplit2 = 0;   // 0 = chosen per layer
 int g_stage_override = 0;  // 0 = deepest ring that fits
-int g_cluster = 0;         // 0 = chosen per layer; 1, 2, 4 = forced
 
-template <int MODE, int BLOCK_N, int STAGES>
-int launch2(const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p, int grid, cudaStream_t stream) {
+// MINB = CTAs per SM the configuration is built for.  A single MMA-issuing warp spends ~450 cycles of control flow
+// (barrier wait, fences, descriptor set-up, commit) per ring slot, more than the tensor work of a slot for tiles of
+// 64 or 128 columns (128 / 256 cycles), so those run two CTAs per SM -- two independent issue streams -- with half
+// the ring depth each; 256-column tiles (512 cycles per slot, all of TMEM) run one.
+template <int MODE, int BLOCK_N, int STAGES, int MINB>
+int launch2(const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p, cudaStream_t stream) {
   using L = Smem2<BLOCK_N, STAGES>;
-  auto kern = igemm2_kernel<MODE, BLOCK_N, STAGES>;
+  auto kern = igemm2_kernel<MODE, BLOCK_N, STAGES, MINB>;
   static bool attr_done[64] = {false};  // per instantiation and device
   const int dev = current_device();
   if (dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
@@ -682,45 +655,19 @@ int launch2(const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p,
       return DCGAN_ERR_LAUNCH;
     attr_done[dev] = true;
   }
-  if (p.cluster > 1) {
-    // persistent clusters: never launch more than can be resident at once (a cluster that waits for a free GPC
-    // slot would only start when the whole first wave has finished)
-    static int max_clusters[64][9] = {{0}};
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = L::kTotal;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = p.cluster;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    if (max_clusters[dev][p.cluster] == 0) {
-      int n = 0;
-      cfg.gridDim = dim3(num_sms() / p.cluster * p.cluster);
-      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) { cudaGetLastError(); n = 1; }
-      max_clusters[dev][p.cluster] = n;
-    }
-    int clusters = grid / p.cluster;
-    if (clusters > max_clusters[dev][p.cluster]) clusters = max_clusters[dev][p.cluster];
-    cfg.gridDim = dim3(clusters * p.cluster);
-    return cudaLaunchKernelEx(&cfg, kern, tg, td, p) == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
-  }
+  const int ctas = g_max_ctas > 0 ? g_max_ctas : num_sms() * MINB;
+  const int grid = p.total_groups < ctas ? p.total_groups : ctas;
   launch_k(kern, dim3(grid), dim3(kThreads), L::kTotal, stream, tg, td, p);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 
 template <int MODE>
-int dispatch2(int block_n, const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p, int grid,
-              cudaStream_t st) {
-  const bool shallow = g_stage_override == 1;  // half-depth rings (two CTAs of different kernels can share an SM)
+int dispatch2(int block_n, const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p, cudaStream_t st) {
+  const bool deep = g_stage_override == 2;  // one CTA per SM with the deepest ring that fits (A/B runs)
   switch (block_n) {
-    case 64: return shallow ? launch2<MODE, 64, 4>(tg, td, p, grid, st) : launch2<MODE, 64, 8>(tg, td, p, grid, st);
-    case 128: return shallow ? launch2<MODE, 128, 3>(tg, td, p, grid, st) : launch2<MODE, 128, 6>(tg, td, p, grid, st);
-    case 256: return launch2<MODE, 256, 4>(tg, td, p, grid, st);
+    case 64: return deep ? launch2<MODE, 64, 8, 1>(tg, td, p, st) : launch2<MODE, 64, 4, 2>(tg, td, p, st);
+    case 128: return deep ? launch2<MODE, 128, 6, 1>(tg, td, p, st) : launch2<MODE, 128, 3, 2>(tg, td, p, st);
+    case 256: return launch2<MODE, 256, 4, 1>(tg, td, p, st);
     default: return DCGAN_ERR_SHAPE;
   }
 }
@@ -729,7 +676,6 @@ int dispatch2(int block_n, const CUtensorMap& tg, const CUtensorMap& td, const I
 
 int igemm2_num_sms() { return num_sms(); }
 int igemm2_max_ctas() { return g_max_ctas; }
-int igemm2_cluster_pref() { return g_cluster; }
 int igemm2_forced_ksplit() { return g_force_ksplit2; }
 int igemm2_tmap_nhwc(const void* ptr, int N, int H, int W, int C, int bw, int bh, int bn, int stride, void* out_map) {
   return tmap_nhwc(ptr, N, H, W, C, bw, bh, bn, stride, reinterpret_cast<CUtensorMap*>(out_map));
@@ -743,7 +689,6 @@ bool igemm2_pixel_box(int rows, int rH, int rW, int* bw, int* bh, int* bn) { ret
 void igemm2_set_max_ctas(int v) { g_max_ctas = v > 0 ? v : 0; }
 void igemm2_set_ksplit(int v) { g_force_ksplit2 = (v >= 1 && v <= 16) ? v : 0; }
 void igemm2_set_stage_mode(int v) { g_stage_override = v; }
-void igemm2_set_cluster(int v) { g_cluster = (v == 1 || v == 2 || v == 4) ? v : 0; }
 
 int igemm2_set_workspace(void* ptr, size_t bytes) {
   if (ptr != nullptr && bytes < kCounterBytes + (1u << 20)) return DCGAN_ERR_LIMIT;
@@ -756,6 +701,7 @@ int igemm2_set_workspace(void* ptr, size_t bytes) {
 // (128 x bn x 64 MACs at 8192 MACs per cycle and SM) and its bytes from L2 at the per-SM share of the fabric;
 // a work item adds a fixed cost (epilogue tail, scheduling) plus the partial-tile traffic when K is split.
 static double plan_cost(long tiles, double kb_per_tile, int bn, int ks, int ctas) {
+  if (bn <= 128) ctas *= 2;  // two CTAs per SM (see launch2)
   const double kBytesPerCycle = 36.0;  // measured-order L2 -> SM rate per SM with every SM loading
   const double t_kb = fmax(2.0 * bn, (kATileBytes + bn * 128.0) / kBytesPerCycle);
   const double part = (ks > 1) ? (128.0 * bn * 4.0 * 2.0) / kBytesPerCycle + 1500.0 : 0.0;
@@ -862,28 +808,17 @@ int igemm2_conv(int transposed, const void* x, const void* w, const float* bias,
   p.ksplit = ks;
   p.m_tiles = mt;
   p.n_tiles = Cout / block_n;
-  // CTAs of a cluster take consecutive M tiles and share the filter tile through TMA multicast
-  int cl = g_cluster > 0 ? g_cluster : 2;
-  while (cl > 1 && cl > mt) cl >>= 1;
-  p.cluster = cl;
-  p.m_groups = (mt + cl - 1) / cl;
-  const long tiles = (long)p.m_groups * cl * p.n_tiles * classes;  // including the tiles that pad the last group
+  const long tiles = (long)mt * p.n_tiles * classes;
   int rc = attach_scratch(&p, tiles, block_n);
   if (rc) return rc;
-  p.total_groups = (int)((long)p.m_groups * p.n_tiles * classes * p.ksplit);
+  p.total_groups = (int)(tiles * p.ksplit);
   CUtensorMap tg, td;
   rc = tmap_nhwc(x, NB, H, W, Cin, bw, bh, bn_img, transposed ? 1 : 2, &tg);
   if (rc) return rc;
-  rc = b_mn ? tmap_2d(w, (uint64_t)25 * Cin, Cout, 64 / cl, 64, &td)
-            : tmap_2d(w, (uint64_t)25 * Cout, Cin, block_n / cl, 64, &td);
+  rc = b_mn ? tmap_2d(w, (uint64_t)25 * Cin, Cout, 64, 64, &td)
+            : tmap_2d(w, (uint64_t)25 * Cout, Cin, block_n, 64, &td);
   if (rc) return rc;
-  int ctas = g_max_ctas > 0 ? g_max_ctas : num_sms();
-  if (ctas < cl) ctas = cl;
-  ctas = ctas / cl * cl;
-  const long want = (long)p.total_groups * cl;
-  const int grid = want < ctas ? (int)want : ctas;
-  return transposed ? dispatch2<MODE_T>(block_n, tg, td, p, grid, stream)
-                    : dispatch2<MODE_F>(block_n, tg, td, p, grid, stream);
+  return transposed ? dispatch2<MODE_T>(block_n, tg, td, p, stream) : dispatch2<MODE_F>(block_n, tg, td, p, stream);
 }
 
 int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd, int splits,
@@ -918,8 +853,6 @@ int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, 
   p.ksplit = ks;
   p.m_tiles = Cd / kBlockM;
   p.n_tiles = Cg / block_n;
-  p.cluster = 1;
-  p.m_groups = p.m_tiles;
   const long tiles = (long)25 * p.m_tiles * p.n_tiles;
   int rc = attach_scratch(&p, tiles, block_n);
   if (rc) return rc;
@@ -929,9 +862,7 @@ int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, 
   if (rc) return rc;
   rc = tmap_2d(small, (uint64_t)rows, Cd, 64, 64, &td);
   if (rc) return rc;
-  const int ctas = g_max_ctas > 0 ? g_max_ctas : num_sms();
-  const int grid = p.total_groups < ctas ? p.total_groups : ctas;
-  return dispatch2<MODE_W>(block_n, tg, td, p, grid, stream);
+  return dispatch2<MODE_W>(block_n, tg, td, p, stream);
 }
 
 }  // namespace dcgan

@@ -901,10 +901,8 @@ void dcgan_set_igemm_ksplit(int v) {
 }
 void dcgan_set_igemm_max_ctas(int v) { igemm2_set_max_ctas(v); }
 void dcgan_set_igemm_stage_mode(int v) { igemm2_set_stage_mode(v); }
-void dcgan_set_igemm_cluster(int v) { igemm2_set_cluster(v); }
 int dcgan_set_workspace(void* ptr, size_t bytes) { return igemm2_set_workspace(ptr, bytes); }
 static inline bool use_v2() { return (g_igemm_tuning & 128) == 0; }
-static inline bool use_v3() { return (g_igemm_tuning & 256) == 0; }  // bit 8: per-parity igemm2 transposed conv
 void dcgan_set_wgrad_cta_target(int v) { g_wgrad_cta_target = v > 0 ? v : 148; }
 
 // Host-only view of the launch plan of a strided (transposed = 0) or transposed (1) conv: tile width, split-K
@@ -933,11 +931,6 @@ static int conv_fprop_impl(const void* x, const void* w_nk, const float* bias, v
                            int Cin, int Cout, int act, int block_n, int b_mn, cudaStream_t stream,
                            float* stats = nullptr, int stat_groups = 1) {
   if (use_v2()) {
-    if (use_v3() && b_mn) {  // halo tiles: 10 instead of 25 input tiles per channel chunk
-      const int rc3 = igemm3_fconv(x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n, stats, stat_groups, stream,
-                                   nullptr);
-      if (rc3 != DCGAN_ERR_SHAPE) return rc3;
-    }
     return igemm2_conv(0, x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n, b_mn, stats, stat_groups, stream);
   }
   if ((H & 1) || (W & 1) || Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
@@ -994,11 +987,6 @@ static int conv_tconv_impl(const void* x, const void* w_nk, const float* bias, v
                            int Cin, int Cout, int act, int block_n, cudaStream_t stream, float* stats,
                            int stat_groups) {
   if (use_v2()) {
-    if (use_v3()) {  // parity-fused kernel (9 or 3.75 shifted input tiles per chunk instead of 25)
-      const int rc3 = igemm3_tconv(x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n, stats, stat_groups, stream,
-                                   nullptr);
-      if (rc3 != DCGAN_ERR_SHAPE) return rc3;
-    }
     return igemm2_conv(1, x, w_nk, bias, out, NB, H, W, Cin, Cout, act, block_n < 0 ? 0 : block_n, 0, stats,
                        stat_groups, stream);
   }
@@ -1065,10 +1053,6 @@ int dcgan_conv_tconv_bnred(const void* x, const void* w_nk, void* out, const voi
                            int NB, int H, int W, int Cin, int Cout, int block_n, cudaStream_t stream) {
   if (!use_v2()) return DCGAN_ERR_SHAPE;
   BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act};
-  if (use_v3()) {
-    const int rc3 = igemm3_tconv(x, w_nk, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, nullptr, 1, stream, &a);
-    if (rc3 != DCGAN_ERR_SHAPE) return rc3;
-  }
   return igemm2_conv(1, x, w_nk, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 0, nullptr, 1, stream, &a);
 }
 
@@ -1078,10 +1062,6 @@ int dcgan_conv_fprop_kn_bnred(const void* x, const void* w_kn, void* out, const 
                               cudaStream_t stream) {
   if (!use_v2()) return DCGAN_ERR_SHAPE;
   BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act};
-  if (use_v3()) {
-    const int rc3 = igemm3_fconv(x, w_kn, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, nullptr, 1, stream, &a);
-    if (rc3 != DCGAN_ERR_SHAPE) return rc3;
-  }
   return igemm2_conv(0, x, w_kn, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 1, nullptr, 1, stream, &a);
 }
 

@@ -13,7 +13,6 @@
 
 extern "C" void dcgan_set_igemm_max_ctas(int v);
 extern "C" void dcgan_set_igemm_stage_mode(int v);
-extern "C" void dcgan_set_igemm_cluster(int v);
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(2); } } while (0)
 
@@ -255,30 +254,13 @@ static void time_layers(bool sweep) {
     dcgan_set_igemm_tuning(1 | 128);
     const float t_old = time_us([&] { rc |= run(0, 0); }, 20);
     dcgan_set_igemm_tuning(1);
-    float t_cl[3] = {0, 0, 0};
-    const int cls[3] = {1, 2, 4};
-    for (int ci = 0; ci < 3; ++ci) {
-      dcgan_set_igemm_cluster(cls[ci]);
-      t_cl[ci] = time_us([&] { rc |= run(0, 0); }, 20);
-    }
-    dcgan_set_igemm_cluster(0);
     const float t_new = time_us([&] { rc |= run(0, 0); }, 20);
+    dcgan_set_igemm_stage_mode(2);  // one CTA per SM, deepest ring
+    const float t_deep = time_us([&] { rc |= run(0, 0); }, 20);
+    dcgan_set_igemm_stage_mode(0);
     const double fl = layer_flops(l);
-    printf("[TIME] %s  gen1 %7.1f us (%6.1f TF/s)   gen2 %7.1f us (%6.1f TF/s)   x%.2f   cluster 1/2/4: %.1f / %.1f / %.1f us  rc=%d err=%d\n", l.name, t_old,
-           fl / t_old * 1e-6, t_new, fl / t_new * 1e-6, t_old / t_new, t_cl[0], t_cl[1], t_cl[2], rc, dcgan_last_device_error());
-    if (l.kind == 0) {
-      dcgan_set_igemm_tuning(1 | 256);
-      const float t_pp = time_us([&] { rc |= run(0, 0); }, 20);
-      dcgan_set_igemm_tuning(1);
-      printf("        igemm2 (no halo) %.1f us rc=%d err=%d\n", t_pp, rc, dcgan_last_device_error());
-    }
-    if (l.kind == 1) {
-      dcgan_set_igemm_tuning(1 | 256);
-      const float t_pp = time_us([&] { rc |= run(0, 0); }, 20);
-      dcgan_set_igemm_tuning(1);
-      const float t_128 = (l.Cout % 128 == 0) ? time_us([&] { rc |= run(128, 0); }, 20) : 0.f;
-      printf("        per-parity igemm2 %.1f us; parity-fused bn=128 %.1f us rc=%d err=%d\n", t_pp, t_128, rc, dcgan_last_device_error());
-    }
+    printf("[TIME] %s  gen1 %7.1f us (%6.1f TF/s)   gen2 %7.1f us (%6.1f TF/s)   x%.2f   gen2 with one CTA per SM: %.1f us  rc=%d err=%d\n",
+           l.name, t_old, fl / t_old * 1e-6, t_new, fl / t_new * 1e-6, t_old / t_new, t_deep, rc, dcgan_last_device_error());
     tot_old += t_old; tot_new += t_new;
     if (sweep) {
       const int nch = (l.kind == 2) ? l.Cin : l.Cout;
@@ -317,20 +299,16 @@ int main(int argc, char** argv) {
     fails += test_tconv(2, 4, 4, 128, 128, 128, 1, false);
     fails += test_tconv(1, 8, 8, 64, 256, 256, 1, false);
     fails += test_tconv(2, 8, 8, 64, 128, 0, 1, true);
-    // strided conv with halo tiles (output tiles of whole image rows: oH * oW >= 128)
+    // output tiles of whole image rows (oH * oW >= 128)
     fails += test_fprop(2, 32, 32, 64, 128, 0, 1, 1, false);
     fails += test_fprop(1, 32, 32, 128, 64, 64, 1, 1, false);
     fails += test_fprop(1, 64, 64, 64, 64, 0, 1, 3, false);     // oW = 32: 4-row tiles
     fails += test_fprop(4, 32, 32, 64, 128, 0, 1, 1, true);
-    // parity-fused kernel with halo rows (tiles of whole image rows: H * W >= 128)
+    // input tiles of whole image rows (H * W >= 128)
     fails += test_tconv(2, 16, 16, 64, 64, 64, 1, false);
     fails += test_tconv(1, 16, 16, 128, 128, 128, 1, false);
     fails += test_tconv(1, 32, 32, 64, 64, 64, 1, false);
     fails += test_tconv(3, 16, 16, 128, 64, 0, 1, true);
-    dcgan_set_igemm_tuning(1 | 256);  // the per-parity igemm2 path stays available
-    fails += test_tconv(2, 16, 16, 64, 64, 64, 1, false);
-    fails += test_tconv(2, 8, 8, 64, 128, 0, 1, true);
-    dcgan_set_igemm_tuning(1);
     for (int ks : {2, 3, 5, 8}) {  // ordered split-K through the scratch buffer
       dcgan_set_igemm_ksplit(ks);
       fails += test_fprop(2, 16, 16, 64, 64, 64, 0, 1, false);
@@ -338,27 +316,10 @@ int main(int argc, char** argv) {
       fails += test_fprop(2, 16, 16, 128, 128, 128, 1, 1, false);
       fails += test_tconv(2, 8, 8, 128, 64, 64, 1, false);
       fails += test_tconv(2, 4, 4, 128, 128, 128, 1, false);
-      fails += test_tconv(1, 16, 16, 256, 64, 64, 1, false);   // halo + split over channel chunks
+      fails += test_tconv(1, 16, 16, 256, 64, 64, 1, false);
       fails += test_fprop(4, 16, 16, 64, 128, 0, 1, 1, true);
     }
     dcgan_set_igemm_ksplit(0);
-    for (int cl : {1, 4}) {  // (2 is the default) filter tile multicast across a thread-block cluster
-      dcgan_set_igemm_cluster(cl);
-      fails += test_fprop(2, 16, 16, 128, 128, 64, 0, 1, false);
-      fails += test_fprop(2, 16, 16, 128, 128, 128, 1, 1, false);
-      fails += test_fprop(1, 4, 8, 64, 64, 64, 0, 1, false);
-      fails += test_fprop(3, 16, 16, 64, 128, 64, 1, 1, false);   // 3 M tiles: the last group is padded
-      fails += test_tconv(3, 8, 8, 64, 128, 128, 1, false);
-      fails += test_tconv(3, 16, 16, 64, 64, 64, 1, false);     // halo, 6 M tiles
-      fails += test_fprop(3, 32, 32, 64, 128, 0, 1, 1, false);  // strided halo, 6 M tiles
-      fails += test_tconv(3, 16, 16, 128, 64, 0, 1, true);
-      fails += test_fprop(4, 16, 16, 64, 128, 0, 1, 1, true);
-      dcgan_set_igemm_ksplit(3);
-      fails += test_fprop(3, 16, 16, 64, 128, 64, 1, 1, false);
-      fails += test_tconv(3, 8, 8, 128, 128, 64, 1, false);
-      dcgan_set_igemm_ksplit(0);
-    }
-    dcgan_set_igemm_cluster(0);
     fails += test_wgrad(2, 8, 8, 64, 128, 1, 64, 1, 1);
     fails += test_wgrad(2, 8, 8, 128, 128, 2, 128, 1, 2);
     fails += test_wgrad(4, 4, 4, 256, 256, 1, 256, 1, 1);
@@ -371,7 +332,7 @@ int main(int argc, char** argv) {
     fails += test_wgrad(2, 8, 8, 128, 128, 3, 64, 1, 2);
     fails += test_fprop(4, 16, 16, 64, 128, 64, 1, 1, true);
     dcgan_set_igemm_max_ctas(0);
-    dcgan_set_igemm_stage_mode(1);  // shallow rings
+    dcgan_set_igemm_stage_mode(2);  // one CTA per SM, deep rings
     fails += test_fprop(2, 16, 16, 128, 128, 128, 1, 1, false);
     fails += test_tconv(2, 8, 8, 64, 64, 64, 1, false);
     dcgan_set_igemm_stage_mode(0);

@@ -91,8 +91,7 @@ def load() -> ctypes.CDLL:
     lib.dcgan_set_workspace.argtypes = [c_void_p, c_size_t]
     lib.dcgan_set_workspace.restype = c_int
     for setter in ("dcgan_set_igemm_tuning", "dcgan_set_igemm_ksplit", "dcgan_set_wgrad_cta_target",
-                   "dcgan_set_adam_blocks", "dcgan_set_igemm_max_ctas", "dcgan_set_igemm_stage_mode",
-                   "dcgan_set_igemm_cluster"):
+                   "dcgan_set_adam_blocks", "dcgan_set_igemm_max_ctas", "dcgan_set_igemm_stage_mode"):
         getattr(lib, setter).argtypes = [c_int]
         getattr(lib, setter).restype = None
     # profiling overrides (A/B runs of bench.py without a rebuild)
@@ -100,8 +99,8 @@ def load() -> ctypes.CDLL:
         lib.dcgan_set_igemm_tuning(int(os.environ["DCGAN_IGEMM_TUNING"]))
     if os.environ.get("DCGAN_IGEMM_KSPLIT"):
         lib.dcgan_set_igemm_ksplit(int(os.environ["DCGAN_IGEMM_KSPLIT"]))
-    if os.environ.get("DCGAN_IGEMM_CLUSTER"):
-        lib.dcgan_set_igemm_cluster(int(os.environ["DCGAN_IGEMM_CLUSTER"]))
+    if os.environ.get("DCGAN_IGEMM_STAGE_MODE"):
+        lib.dcgan_set_igemm_stage_mode(int(os.environ["DCGAN_IGEMM_STAGE_MODE"]))
     if os.environ.get("DCGAN_IGEMM_MAX_CTAS"):
         lib.dcgan_set_igemm_max_ctas(int(os.environ["DCGAN_IGEMM_MAX_CTAS"]))
     if os.environ.get("DCGAN_WGRAD_CTAS"):

@@ -49,14 +49,12 @@ void dcgan_set_pdl(int v);
 
 /* Profiling switch for the implicit-GEMM kernels.  Bit 7 (128) selects the first-generation kernels (cp.async
  * gather, csrc/igemm_sm100.cu) instead of the TMA-fed persistent ones (csrc/igemm2_sm100.cu); the other bits
- * only act on the first generation: bit 0 = two CTAs per SM (default on).  Bit 8 (256) runs the transposed conv as
- * four per-parity GEMMs (igemm2) instead of the parity-fused kernel with halo rows (csrc/igemm3_sm100.cu). */
+ * only act on the first generation: bit 0 = two CTAs per SM (default on). */
 void dcgan_set_igemm_tuning(int v);
-/* Second-generation kernels: cap on the persistent grid (0 = one CTA per SM), stage-ring depth (1 = shallow),
- * CTAs per cluster that share the filter tile by TMA multicast (0 = default, 1 / 2 / 4 forced). */
+/* Second-generation kernels: cap on the persistent grid (0 = every CTA slot of the device), ring configuration
+ * (0 = default: two CTAs per SM for tiles of 64 / 128 columns; 2 = one CTA per SM with the deepest ring). */
 void dcgan_set_igemm_max_ctas(int v);
 void dcgan_set_igemm_stage_mode(int v);
-void dcgan_set_igemm_cluster(int v);
 /* Split-K scratch of the second-generation kernels for the calling host thread: `bytes` of device memory whose
  * first 64 KiB are zero (arrival counters; the kernels leave them zero), at least 1 MiB + 64 KiB.  Kernels that
  * may run concurrently (different streams) must not share a workspace.  NULL returns to the library's default
