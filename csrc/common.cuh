@@ -280,13 +280,33 @@ __device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32]) {
 
 enum Act : int { kActNone = 0, kActRelu = 1, kActLrelu = 2, kActTanh = 3, kActSigmoid = 4 };
 
+// Per-element activation.  Written for a loop-invariant `act`: identity costs one (uniform) branch, ReLU / LeakyReLU
+// are branch-free.  The earlier form -- a switch evaluated per element -- cost four compare-and-branch pairs per
+// element on the identity path; in the conv epilogues that was ~11 k cycles per 128x128 tile, as much as the tile's
+// main loop (profiles/README.md).  Hot loops should still prefer apply_act_chunk below.
 __device__ __forceinline__ float apply_act(float x, int act) {
-  switch (act) {
-    case kActRelu: return fmaxf(x, 0.f);
-    case kActLrelu: return fmaxf(x, 0.2f * x);
-    case kActTanh: return tanhf(x);
-    case kActSigmoid: return 1.f / (1.f + __expf(-x));
-    default: return x;
+  if (act == kActNone) return x;
+  if (act >= kActTanh) return act == kActTanh ? tanhf(x) : 1.f / (1.f + __expf(-x));
+  const float r = fmaxf(x, 0.f), l = fmaxf(x, 0.2f * x);
+  return act == kActRelu ? r : l;
+}
+
+// Activation of a register chunk with the kind selected ONCE (warp-uniform branch outside the element loop).
+template <int N>
+__device__ __forceinline__ void apply_act_chunk(float (&f)[N], int act) {
+  if (act == kActNone) return;
+  if (act == kActRelu) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) f[j] = fmaxf(f[j], 0.f);
+  } else if (act == kActLrelu) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) f[j] = fmaxf(f[j], 0.2f * f[j]);
+  } else if (act == kActTanh) {
+#pragma unroll
+    for (int j = 0; j < N; ++j) f[j] = tanhf(f[j]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < N; ++j) f[j] = 1.f / (1.f + __expf(-f[j]));
   }
 }
 

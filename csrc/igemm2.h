@@ -39,6 +39,7 @@ struct Igemm2Params {
   int bn_slab_out_rows;   // output rows (pixels) per slab
   int bn_stat_groups;     // slab g uses the statistics / pre-activations of group min(g, bn_stat_groups - 1)
   int bn_act;             // the layer's activation (ReLU / LeakyReLU)
+  long long* dbg;         // bring-up only (-DIGEMM2_TIMING): per-CTA cycle counters [CTA][16]
   float* partials;        // split-K scratch: [tile][slice][BLOCK_N / 4][128] float4
   int* counters;          // split-K arrival counters per tile (zero between launches)
   int* err_flag;          // sticky device error flag (csrc/runtime.cu)
@@ -74,6 +75,7 @@ int igemm2_num_sms();
 int igemm2_max_ctas();
 int igemm2_forced_ksplit();
 
+void igemm2_set_debug(long long* ptr);
 void igemm2_set_max_ctas(int v);
 void igemm2_set_ksplit(int v);
 void igemm2_set_stage_mode(int v);

@@ -39,7 +39,25 @@ namespace {
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;
 constexpr int kATileBytes = kBlockM * kBlockK * 2;  // 16 KiB
-constexpr int kThreads = 192;                       // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+// Bulk tensor loads issued by ONE warp are processed one after the other (~285 ns each whatever their size; chip-wide
+// 8.2 TB/s with one issuing warp per CTA, 16.3 with two, 19.4 with four -- profiles/tma_issue_microbench.log), so the
+// ring slots are dealt to kNumProducers producer warps.  A slot always belongs to the same warp (slot % kNumProducers):
+// its waits on that slot's barrier then come in phase order (a warp that skipped a phase could not tell "two phases
+// done" from "none" by parity).
+#ifndef IGEMM2_PRODUCERS
+#define IGEMM2_PRODUCERS 1  // measured: a second producer warp gains nothing once two CTAs share an SM
+#endif
+constexpr int kNumProducers = IGEMM2_PRODUCERS;
+// -DIGEMM2_TIMING: per-role cycle counters written to Igemm2Params::dbg ([CTA][16] long long), bring-up only
+#ifdef IGEMM2_TIMING
+#define T_NOW() clock64()
+#define T_ADD(var, t0) (var) += clock64() - (t0)
+#else
+#define T_NOW() 0ll
+#define T_ADD(var, t0) ((void)0)
+#endif
+constexpr int kMmaWarp = kNumProducers;             // warps [0, P) TMA producers, warp P MMA, then 4 epilogue warps
+constexpr int kThreads = (kNumProducers + 5) * 32;
 constexpr int kEpiThreads = 128;
 
 template <int BLOCK_N, int STAGES>
@@ -48,8 +66,9 @@ struct Smem2 {
   static constexpr int kStageBytes = kATileBytes + kBTileBytes;
   static constexpr int kBarOffset = STAGES * kStageBytes;  // full[STAGES], empty[STAGES], tfull[2], tempty[2]
   static constexpr int kMiscOffset = kBarOffset + 256;     // tmem base, abort flag, split-K "last" flag
-  static constexpr int kStatOffset = kMiscOffset + 64;     // [2 accumulators][4 warps][2][BLOCK_N] f32
-  static constexpr int kTotal = kStatOffset + 16 * BLOCK_N * 4 + 1024;  // + slack for the 1024-byte alignment
+  static constexpr int kStatOffset = kMiscOffset + 64;     // [4 warps][2][BLOCK_N] f32 epilogue column sums
+  static constexpr int kStoreOffset = kStatOffset + 8 * BLOCK_N * 4;  // [4 warps][32 rows][64 B] output staging
+  static constexpr int kTotal = kStoreOffset + 8192 + 1024;           // + slack for the 1024-byte alignment
   static_assert(2 * STAGES + 4 <= 32, "barrier block is 256 bytes");
 };
 
@@ -126,6 +145,7 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
   volatile int* last_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 2);
   float* stat_smem = reinterpret_cast<float*>(smem + L::kStatOffset);
+  uint4* store_smem = reinterpret_cast<uint4*>(smem + L::kStoreOffset);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -148,7 +168,7 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
     tma_prefetch_desc(&tmap_g);
     tma_prefetch_desc(&tmap_d);
   }
-  if (warp == 1) {
+  if (warp == kMmaWarp) {
     tmem_alloc(tmem_ptr_smem, 2 * BLOCK_N);
     tmem_relinquish();
   }
@@ -161,13 +181,15 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
   const int cpt = p.gC / kBlockK;  // F/T: 64-channel chunks per filter tap
   const int rW = 1 << p.rW_log2, rH = 1 << p.rH_log2;
 
-  if (warp == 0) {
+  if (warp < kNumProducers) {
     // =================================== TMA producer ==========================================
     // all 32 lanes walk the schedule (uniform control flow); the elected lane arms the barrier and issues the copies
     {
       int s = 0;
       uint32_t phase = 0;
       bool ok = true;
+      long long tp_wait = 0, tp_n = 0;
+      const long long tp_begin = T_NOW();
       for (int u = first_group; u < p.total_groups && ok; u += group_step) {
         const WorkItem wi = decode_work<MODE, BLOCK_N>(u, p);
         // origin of the tile's pixel box (F/T); the box always starts at column 0
@@ -184,10 +206,13 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
         }
         const int kh_w = wi.tap / 5, kw_w = wi.tap - 5 * (wi.tap / 5);
         for (int kb = 0; kb < wi.nkb; ++kb) {
-          if (!mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+          const bool mine = (s % kNumProducers) == warp;  // every warp walks the whole sequence, fills its own slots
+          const long long tw0 = T_NOW();
+          if (mine && !mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
+          T_ADD(tp_wait, tw0); ++tp_n;
           uint8_t* sA = smem + s * L::kStageBytes;
           uint8_t* sB = sA + kATileBytes;
-          if (elect_one()) {
+          if (mine && elect_one()) {
           mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
           if (MODE == MODE_W) {
             const int px0 = (wi.kb0 + kb) * kBlockK;
@@ -224,8 +249,14 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
           if (++s == STAGES) { s = 0; phase ^= 1; }
         }
       }
+#ifdef IGEMM2_TIMING
+      if (p.dbg != nullptr && warp == 0 && lane == 0) {
+        long long* d = p.dbg + (size_t)blockIdx.x * 16;
+        d[0] = clock64() - tp_begin; d[1] = tp_wait; d[2] = tp_n;
+      }
+#endif
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     // =================================== MMA issuer ============================================
     // all 32 lanes walk the schedule; the tcgen05 instructions run on the elected lane
     {
@@ -243,15 +274,21 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
       uint32_t phase = 0;
       int ti = 0;
       bool ok = true;
+      long long tm_full = 0, tm_tmem = 0, tm_n = 0;
+      const long long tm_begin = T_NOW();
       for (int u = first_group; u < p.total_groups && ok; u += group_step, ++ti) {
         const WorkItem wi = decode_work<MODE, BLOCK_N>(u, p);
         const int a = ti & 1;
         // the epilogue must have drained this accumulator (two tiles ago)
+        const long long tt0 = T_NOW();
         if (!mbar_wait(&tempty_bar[a], ((ti >> 1) & 1) ^ 1, abort_flag, p.err_flag)) break;
+        T_ADD(tm_tmem, tt0);
         tc_fence_after();
         const uint32_t tacc = tmem_base + (uint32_t)(a * BLOCK_N);
         for (int kb = 0; kb < wi.nkb; ++kb) {
+          const long long tf0 = T_NOW();
           if (!mbar_wait(&full_bar[s], phase, abort_flag, p.err_flag)) { ok = false; break; }
+          T_ADD(tm_full, tf0); ++tm_n;
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
           const uint32_t a_lo = smem_desc_lo(a_addr, lbo);
@@ -271,20 +308,30 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
           __syncwarp();
         }
       }
+#ifdef IGEMM2_TIMING
+      if (p.dbg != nullptr && lane == 0) {
+        long long* d = p.dbg + (size_t)blockIdx.x * 16;
+        d[3] = clock64() - tm_begin; d[4] = tm_full; d[5] = tm_n; d[6] = tm_tmem; d[7] = ti;
+      }
+#endif
     }
   } else {
     // =================================== epilogue warps ========================================
-    const int et = tid - 64;  // 0..127
+    const int et = tid - (kMmaWarp + 1) * 32;  // 0..127
     const int q = warp & 3;   // TMEM lane quadrant this warp may read
     const int row_in_tile = q * 32 + lane;
     const bool do_bnred = (MODE != MODE_W) && p.bn_red != nullptr;
     const bool do_stats = (MODE != MODE_W) && (p.stats != nullptr || do_bnred);
     int ti = 0;
     bool ok = true;
+    long long te_wait = 0, te_ld = 0, te_st = 0;
+    const long long te_begin = T_NOW();
     for (int u = first_group; u < p.total_groups && ok; u += group_step, ++ti) {
       const WorkItem wi = decode_work<MODE, BLOCK_N>(u, p);
       const int a = ti & 1;
+      const long long te0 = T_NOW();
       if (!mbar_wait(&tfull_bar[a], (ti >> 1) & 1, abort_flag, p.err_flag)) { ok = false; break; }
+      T_ADD(te_wait, te0);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t)(a * BLOCK_N) + ((uint32_t)(q * 32) << 16);
 
@@ -349,7 +396,6 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
       if (MODE != MODE_W) {
         const int R = wi.m0 + row_in_tile;
         const bool valid = R < p.rows_total;
-        __nv_bfloat16* orow = nullptr;
         const __nv_bfloat16* prow = nullptr;  // fused batch-norm backward: this row of the saved pre-activations
         int sg = 0;
         if (valid) {
@@ -362,7 +408,6 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
             const int n = R >> (p.rW_log2 + p.rH_log2);
             Ro = (size_t)((n * p.oH + 2 * qh + wi.ph) * p.oW + 2 * qw + wi.pw);
           }
-          orow = reinterpret_cast<__nv_bfloat16*>(p.out) + Ro * p.Cn + wi.n0;
           if (do_bnred) {
             const int g = wi.m0 / p.stat_group_rows;  // slab of this tile (tiles never straddle slabs)
             sg = min(g, p.bn_stat_groups - 1);
@@ -370,11 +415,37 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
                    (Ro - (size_t)(g - sg) * p.bn_slab_out_rows) * p.Cn + wi.n0;
           }
         }
-        float* ssm = stat_smem + a * (8 * BLOCK_N);
+        float* ssm = stat_smem;
+        // Output rows leave through a per-warp staging area: a lane holds 64 bytes of ITS row per 32-column chunk,
+        // and storing them directly is four 16-byte stores per lane to 32 different lines (half-sector writes; measured
+        // 13-16 k cycles per 128x128 tile, as much as the tile's main loop).  Instead the chunk is transposed through
+        // shared memory and every store instruction writes whole 64-byte row segments of 8 rows.
+        uint4* stg = store_smem + (size_t)q * 128;  // [32 rows][4 x 16 B], 16-byte pieces XOR-swizzled by (row >> 1)
+        __nv_bfloat16* srow[4];                       // rows 8 * i + lane / 4 of this warp's 32: piece lane % 4
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int Rr = wi.m0 + q * 32 + 8 * i + (lane >> 2);
+          srow[i] = nullptr;
+          if (Rr < p.rows_total) {
+            size_t Ror;
+            if (MODE == MODE_F) {
+              Ror = (size_t)Rr;
+            } else {
+              const int qw = Rr & (rW - 1);
+              const int qh = (Rr >> p.rW_log2) & (rH - 1);
+              const int n = Rr >> (p.rW_log2 + p.rH_log2);
+              Ror = (size_t)((n * p.oH + 2 * qh + wi.ph) * p.oW + 2 * qw + wi.pw);
+            }
+            srow[i] = reinterpret_cast<__nv_bfloat16*>(p.out) + Ror * p.Cn + wi.n0 + (lane & 3) * 8;
+          }
+        }
+        if (do_stats) asm volatile("bar.sync 1, 128;" ::: "memory");  // the previous tile's sums have been flushed
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N; c += 32) {
           float f[32];
+          const long long tl0 = T_NOW();
           load_chunk(c, f);
+          T_ADD(te_ld, tl0);
           if (p.bias != nullptr) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
@@ -382,16 +453,28 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
               f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
             }
           }
-          if (valid) {
+          const long long ts0 = T_NOW();
+          {
             uint32_t packed[16];
+            // kind selected once per chunk, not per element; the entry points that fuse batch-norm moments or
+            // backward reductions have no activation, so `f` still holds the pre-activation values they need
+            apply_act_chunk(f, p.act);
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              packed[j] = pack_bf16x2(apply_act(f[2 * j], p.act), apply_act(f[2 * j + 1], p.act));
-            uint4* dst = reinterpret_cast<uint4*>(orow + c);
+            for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
+            __syncwarp();  // the previous chunk has been read out of the staging area
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-              dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+              stg[lane * 4 + (j ^ ((lane >> 1) & 3))] =
+                  make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int r = 8 * i + (lane >> 2);
+              const uint4 v = stg[r * 4 + ((lane & 3) ^ ((r >> 1) & 3))];
+              if (srow[i] != nullptr) *reinterpret_cast<uint4*>(srow[i] + c) = v;
+            }
           }
+          T_ADD(te_st, ts0);
           if (do_stats) {  // batch-norm moments of this tile, reduced over the warp's 32 rows
             float sq[32];
             if (do_bnred) {
@@ -458,8 +541,6 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
             atomicAdd(gs + i, t1);
             atomicAdd(gs + p.Cn + i, t2);
           }
-          // the other statistics buffer is used by the next tile; this one is rewritten two tiles from now,
-          // after every thread has passed the next tile's barrier
         }
       } else {
         // dW[tap][n0 + col][m0 + row] += acc: one writer per element (split-K slices were summed in order above)
@@ -478,12 +559,18 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
         }
       }
     }
+#ifdef IGEMM2_TIMING
+    if (warp == kMmaWarp + 1 && lane == 0 && p.dbg != nullptr) {
+      long long* d = p.dbg + (size_t)blockIdx.x * 16;
+      d[8] = clock64() - te_begin; d[9] = te_wait; d[10] = te_ld; d[11] = te_st;
+    }
+#endif
   }
 
   // ---- teardown ---------------------------------------------------------------------------------
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 2 * BLOCK_N);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
 // =================================================================================================
@@ -686,6 +773,8 @@ int igemm2_tmap_2d(const void* ptr, unsigned long long rows, unsigned long long 
 }
 bool igemm2_pixel_box(int rows, int rH, int rW, int* bw, int* bh, int* bn) { return pixel_box(rows, rH, rW, bw, bh, bn); }
 
+static long long* g_dbg = nullptr;
+void igemm2_set_debug(long long* ptr) { g_dbg = ptr; }
 void igemm2_set_max_ctas(int v) { g_max_ctas = v > 0 ? v : 0; }
 void igemm2_set_ksplit(int v) { g_force_ksplit2 = (v >= 1 && v <= 16) ? v : 0; }
 void igemm2_set_stage_mode(int v) { g_stage_override = v; }
@@ -781,6 +870,7 @@ int igemm2_conv(int transposed, const void* x, const void* w, const float* bias,
   p.rows_total = NB * rH * rW;
   p.gC = Cin; p.Cn = Cout; p.Cd = 0;
   p.b_mn = b_mn;
+  p.dbg = g_dbg;
   p.out = out; p.bias = bias; p.act = act;
   p.oH = transposed ? 2 * H : rH; p.oW = transposed ? 2 * W : rW;
   if (stats != nullptr) {
@@ -839,6 +929,7 @@ int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, 
   p.rows_total = rows;
   p.gC = Cg; p.Cn = Cg; p.Cd = Cd;
   p.num_kb = total_kb;
+  p.dbg = g_dbg;
   p.out = dw;
   int ks;
   if (block_n <= 0 && splits > 0) block_n = (Cg % 256 == 0) ? 256 : (Cg % 128 == 0 ? 128 : 64);

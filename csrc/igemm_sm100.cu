@@ -451,8 +451,10 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
         if (valid) {
           uint32_t packed[16];
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
+          for (int j = 0; j < 16; ++j) {
+            // (p.act is 0 whenever the moments below are wanted: the *_stats entry points have no activation)
             packed[j] = pack_bf16x2(apply_act(f[2 * j], p.act), apply_act(f[2 * j + 1], p.act));
+          }
           uint4* dst = reinterpret_cast<uint4*>(orow + c);
 #pragma unroll
           for (int j = 0; j < 4; ++j)
@@ -686,8 +688,10 @@ igemm_t4_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
         if (valid) {
           uint32_t packed[16];
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
+          for (int j = 0; j < 16; ++j) {
+            // (p.act is 0 whenever the moments below are wanted: the *_stats entry points have no activation)
             packed[j] = pack_bf16x2(apply_act(f[2 * j], p.act), apply_act(f[2 * j + 1], p.act));
+          }
           uint4* dst = reinterpret_cast<uint4*>(orow + c);
 #pragma unroll
           for (int j = 0; j < 4; ++j)
@@ -901,6 +905,7 @@ void dcgan_set_igemm_ksplit(int v) {
 }
 void dcgan_set_igemm_max_ctas(int v) { igemm2_set_max_ctas(v); }
 void dcgan_set_igemm_stage_mode(int v) { igemm2_set_stage_mode(v); }
+void dcgan_set_igemm_debug(long long* ptr) { igemm2_set_debug(ptr); }
 int dcgan_set_workspace(void* ptr, size_t bytes) { return igemm2_set_workspace(ptr, bytes); }
 static inline bool use_v2() { return (g_igemm_tuning & 128) == 0; }
 void dcgan_set_wgrad_cta_target(int v) { g_wgrad_cta_target = v > 0 ? v : 148; }

@@ -13,6 +13,7 @@
 
 extern "C" void dcgan_set_igemm_max_ctas(int v);
 extern "C" void dcgan_set_igemm_stage_mode(int v);
+extern "C" void dcgan_set_igemm_debug(long long* ptr);
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(2); } } while (0)
 
@@ -261,6 +262,20 @@ static void time_layers(bool sweep) {
     const double fl = layer_flops(l);
     printf("[TIME] %s  gen1 %7.1f us (%6.1f TF/s)   gen2 %7.1f us (%6.1f TF/s)   x%.2f   gen2 with one CTA per SM: %.1f us  rc=%d err=%d\n",
            l.name, t_old, fl / t_old * 1e-6, t_new, fl / t_new * 1e-6, t_old / t_new, t_deep, rc, dcgan_last_device_error());
+#ifdef IGEMM2_TIMING
+    {  // per-role cycle counters of one launch (bring-up builds only)
+      long long* dbg; CK(cudaMalloc(&dbg, 296 * 16 * 8)); CK(cudaMemset(dbg, 0, 296 * 16 * 8));
+      dcgan_set_igemm_debug(dbg);
+      rc |= run(0, 0);
+      CK(cudaDeviceSynchronize());
+      dcgan_set_igemm_debug(nullptr);
+      std::vector<long long> h(296 * 16); CK(cudaMemcpy(h.data(), dbg, h.size() * 8, cudaMemcpyDeviceToHost));
+      for (int b : {0, 1, 150})
+        printf("        [cta %3d] producer: %lld cyc, waits %lld (%lld slots) | mma: %lld cyc, wait full %lld (%lld slots), wait tmem %lld, %lld tiles | epilogue: %lld cyc, wait %lld, tmem/scratch loads %lld, stores %lld\n",
+               b, h[b * 16], h[b * 16 + 1], h[b * 16 + 2], h[b * 16 + 3], h[b * 16 + 4], h[b * 16 + 5], h[b * 16 + 6], h[b * 16 + 7], h[b * 16 + 8], h[b * 16 + 9], h[b * 16 + 10], h[b * 16 + 11]);
+      cudaFree(dbg);
+    }
+#endif
     tot_old += t_old; tot_new += t_new;
     if (sweep) {
       const int nch = (l.kind == 2) ? l.Cin : l.Cout;
