@@ -9,9 +9,11 @@
 // statistics for the two calls, so every kernel takes a group count and treats
 // group g = contiguous slab of rows_per_group rows.  The backward kernels take a third slab (the
 // g_loss gradient through D(fake)) that shares the statistics of slab 1 (stat_group map).
+#include <atomic>
 #include <cstdio>
 
 #include "common.cuh"
+#include "bn_tail.cuh"
 #include "../include/dcgan_b200.h"
 
 namespace dcgan {
@@ -47,13 +49,9 @@ __device__ __forceinline__ void block_colsum_to_global(float* part, const float 
 // forward statistics: sums[g][0][c] += sum x, sums[g][1][c] += sum x^2   (zeroed by the caller)
 // grid = (row_chunks, groups); thread t handles 8 channels (t % (C/8)) of rows t/(C/8)+k*R
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBnThreads)
-bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, int rows_per_group, int C,
-                int rows_per_block) {
-  pdl_launch_dependents();
-  pdl_wait();
-  __shared__ __align__(16) float part[2 * 8 * kBnThreads];
-  const int g = blockIdx.y;
+__device__ __forceinline__ void bn_stats_body(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums,
+                                              int rows_per_group, int C, int rows_per_block, int g, int chunk,
+                                              float* part) {
   const int cvec = C >> 3;
   const int lanes = kBnThreads / cvec;  // rows processed in parallel (C <= 2048)
   const int cv = threadIdx.x % cvec;
@@ -63,7 +61,7 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
   float (&ss)[8] = acc[1];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
-  const int r0 = blockIdx.x * rows_per_block;
+  const int r0 = chunk * rows_per_block;
   const int r1 = min(r0 + rows_per_block, rows_per_group);
   if (rl < lanes) {
     const __nv_bfloat16* base = x + ((size_t)g * rows_per_group) * C + cv * 8;
@@ -79,6 +77,15 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
     }
   }
   block_colsum_to_global<2>(part, acc, rl < lanes, rl, cv, lanes, C, sums + (size_t)g * 2 * C);
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, int rows_per_group, int C,
+                int rows_per_block) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ __align__(16) float part[2 * 8 * kBnThreads];
+  bn_stats_body(x, sums, rows_per_group, C, rows_per_block, blockIdx.y, blockIdx.x, part);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -171,15 +178,12 @@ __device__ __forceinline__ float act_grad(float y, int act) {
   return 1.f;
 }
 
-__global__ void __launch_bounds__(kBnThreads, 2)
-bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ pre,
-                     const float* __restrict__ saved, const float* __restrict__ gamma,
-                     const float* __restrict__ beta, float* __restrict__ red_out, int rows_per_group, int C,
-                     int n_stat_groups, int act, int rows_per_block) {
-  pdl_launch_dependents();
-  pdl_wait();
-  __shared__ __align__(16) float part[2 * 8 * kBnThreads];
-  const int g = blockIdx.y;
+__device__ __forceinline__ void bn_bwd_reduce_body(const __nv_bfloat16* __restrict__ da,
+                                                   const __nv_bfloat16* __restrict__ pre,
+                                                   const float* __restrict__ saved, const float* __restrict__ gamma,
+                                                   const float* __restrict__ beta, float* __restrict__ red_out,
+                                                   int rows_per_group, int C, int n_stat_groups, int act,
+                                                   int rows_per_block, int g, int chunk, float* part) {
   const int sg = min(g, n_stat_groups - 1);
   const int cvec = C >> 3;
   const int lanes = kBnThreads / cvec;
@@ -199,7 +203,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* 
       rstd[j] = saved[((size_t)sg * 2 + 1) * C + c];
       gm[j] = gamma[c]; bt[j] = beta[c];
     }
-    const int r0 = blockIdx.x * rows_per_block;
+    const int r0 = chunk * rows_per_block;
     const int r1 = min(r0 + rows_per_block, rows_per_group);
     const __nv_bfloat16* dab = da + ((size_t)g * rows_per_group) * C + cv * 8;
     const __nv_bfloat16* prb = pre + ((size_t)sg * rows_per_group) * C + cv * 8;
@@ -234,6 +238,53 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* 
     }
   }
   block_colsum_to_global<2>(part, acc, rl < lanes, rl, cv, lanes, C, red_out + (size_t)g * 2 * C);
+}
+
+__global__ void __launch_bounds__(kBnThreads, 2)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ pre,
+                     const float* __restrict__ saved, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, float* __restrict__ red_out, int rows_per_group, int C,
+                     int n_stat_groups, int act, int rows_per_block) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ __align__(16) float part[2 * 8 * kBnThreads];
+  bn_bwd_reduce_body(da, pre, saved, gamma, beta, red_out, rows_per_group, C, n_stat_groups, act, rows_per_block,
+                     blockIdx.y, blockIdx.x, part);
+}
+
+// ---------------------------------------------------------------------------------------------
+// One-launch variants for the layers whose producer is not an implicit-GEMM conv (which would carry the batch norm
+// in its own tail, csrc/igemm2_sm100.cu): statistics (or backward reductions) by row chunks, a grid-wide barrier,
+// then the elementwise pass by the whole grid.  1-D grid of groups * chunks CTAs, all resident (host checks).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBnThreads)
+bn_forward_fused_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, float* sums,
+                        const float* __restrict__ gamma, const float* __restrict__ beta, float* saved,
+                        float* ema_mean, float* ema_var, int groups, int rows_per_group, int C, float eps, float decay,
+                        int act, int rows_per_block, int chunks, int* barrier, int* err_flag) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ __align__(16) float part[2 * 8 * kBnThreads];
+  bn_stats_body(x, sums, rows_per_group, C, rows_per_block, blockIdx.x / chunks, blockIdx.x % chunks, part);
+  grid_barrier(barrier, err_flag);
+  bn_fwd_apply_grid<kBnThreads>(x, y, sums, gamma, beta, saved, ema_mean, ema_var, groups, rows_per_group, C, eps,
+                                decay, act);
+}
+
+__global__ void __launch_bounds__(kBnThreads)
+bn_backward_fused_kernel(const __nv_bfloat16* __restrict__ da, const __nv_bfloat16* __restrict__ pre,
+                         __nv_bfloat16* __restrict__ dpre, const float* __restrict__ saved,
+                         const float* __restrict__ gamma, const float* __restrict__ beta, float* red, float* dgamma,
+                         float* dbeta, int slabs, int n_stat_groups, int param_slabs, int rows_per_group, int C,
+                         int act, int rows_per_block, int chunks, int* barrier, int* err_flag) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ __align__(16) float part[2 * 8 * kBnThreads];
+  bn_bwd_reduce_body(da, pre, saved, gamma, beta, red, rows_per_group, C, n_stat_groups, act, rows_per_block,
+                     blockIdx.x / chunks, blockIdx.x % chunks, part);
+  grid_barrier(barrier, err_flag);
+  bn_bwd_apply_grid<kBnThreads>(da, pre, dpre, saved, gamma, beta, red, dgamma, dbeta, slabs, n_stat_groups,
+                                param_slabs, rows_per_group, C, act);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -388,6 +439,33 @@ static int pick_rows_per_block(int rows, int C, int groups) {
   return rpb;
 }
 
+// resident CTA capacity of a kernel on the current device (the grid barrier needs the whole grid resident)
+template <typename K>
+static int resident_ctas(K kern, int* cache) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  if (cache[dev] == 0) {
+    int per_sm = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kBnThreads, 0) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      return 0;
+    cache[dev] = per_sm * sms;
+  }
+  return cache[dev];
+}
+
+static int fused_chunks(int rows_per_group, int C, int groups, int capacity, int* rpb) {
+  *rpb = pick_rows_per_block(rows_per_group, C, groups);
+  int chunks = (rows_per_group + *rpb - 1) / *rpb;
+  if (chunks * groups > capacity) {
+    chunks = capacity / groups;
+    if (chunks < 1) return 0;
+    *rpb = (rows_per_group + chunks - 1) / chunks;
+    chunks = (rows_per_group + *rpb - 1) / *rpb;
+  }
+  return chunks;
+}
+
 }  // namespace dcgan
 
 using namespace dcgan;
@@ -440,6 +518,41 @@ int dcgan_bn_bwd_apply(const void* da, const void* pre, void* dpre, const float*
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 
+int dcgan_bn_forward_fused(const void* x, void* y, float* sums, const float* gamma, const float* beta, float* saved,
+                           float* ema_mean, float* ema_var, int* barrier, int groups, int rows_per_group, int C,
+                           float eps, float decay, int act, cudaStream_t st) {
+  if (C % 8 || C / 8 > kBnThreads || groups < 1 || barrier == nullptr) return DCGAN_ERR_SHAPE;
+  static int cache[64] = {0};
+  const int cap = resident_ctas(bn_forward_fused_kernel, cache);
+  int rpb;
+  const int chunks = fused_chunks(rows_per_group, C, groups, cap, &rpb);
+  if (chunks < 1) return DCGAN_ERR_LAUNCH;
+  int* err = error_flag_ptr();
+  if (!err) return DCGAN_ERR_DRIVER;
+  launch_k(bn_forward_fused_kernel, dim3(groups * chunks), dim3(kBnThreads), 0, st,
+           reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, saved,
+           ema_mean, ema_var, groups, rows_per_group, C, eps, decay, act, rpb, chunks, barrier, err);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
+int dcgan_bn_backward_fused(const void* da, const void* pre, void* dpre, const float* saved, const float* gamma,
+                            const float* beta, float* red, float* dgamma, float* dbeta, int* barrier, int groups,
+                            int stat_groups, int param_groups, int rows_per_group, int C, int act, cudaStream_t st) {
+  if (C % 8 || C / 8 > kBnThreads || groups < 1 || barrier == nullptr) return DCGAN_ERR_SHAPE;
+  static int cache[64] = {0};
+  const int cap = resident_ctas(bn_backward_fused_kernel, cache);
+  int rpb;
+  const int chunks = fused_chunks(rows_per_group, C, groups, cap, &rpb);
+  if (chunks < 1) return DCGAN_ERR_LAUNCH;
+  int* err = error_flag_ptr();
+  if (!err) return DCGAN_ERR_DRIVER;
+  launch_k(bn_backward_fused_kernel, dim3(groups * chunks), dim3(kBnThreads), 0, st,
+           reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(pre),
+           reinterpret_cast<__nv_bfloat16*>(dpre), saved, gamma, beta, red, dgamma, dbeta, groups, stat_groups,
+           param_groups, rows_per_group, C, act, rpb, chunks, barrier, err);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
 int dcgan_act_bwd(const void* da, const void* a, void* dpre, float* dbias, int rows, int a_rows, int C, int act,
                   int bias_rows, cudaStream_t st) {
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
@@ -483,18 +596,20 @@ static __device__ __align__(256) float g_static_bn_sums[kStaticBnFloats];
 
 static float* static_bn_scratch_for_current_device(cudaError_t* err) {
   constexpr int kMaxDev = 64;
-  static float* per_device[kMaxDev] = {nullptr};
+  // Filled on first use per device.  Host threads may race to fill a slot: they all store the same address (the
+  // symbol's address on that device never changes), and the atomic keeps the store / load well defined.
+  static std::atomic<float*> per_device[kMaxDev];
   int dev = -1;
   *err = cudaGetDevice(&dev);
   if (*err != cudaSuccess) return nullptr;
   if (dev < 0 || dev >= kMaxDev) { *err = cudaErrorInvalidDevice; return nullptr; }
-  if (per_device[dev] == nullptr) {
-    float* ptr = nullptr;
+  float* ptr = per_device[dev].load(std::memory_order_acquire);
+  if (ptr == nullptr) {
     *err = cudaGetSymbolAddress((void**)&ptr, g_static_bn_sums);
     if (*err != cudaSuccess) return nullptr;
-    per_device[dev] = ptr;
+    per_device[dev].store(ptr, std::memory_order_release);
   }
-  return per_device[dev];
+  return ptr;
 }
 
 }  // namespace dcgan

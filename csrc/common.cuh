@@ -53,6 +53,7 @@ enum DeviceError : int {
   kErrNone = 0,
   kErrMbarTimeout = 1,
   kErrPeerTimeout = 2,
+  kErrGridBarrierTimeout = 3,
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -308,6 +309,39 @@ __device__ __forceinline__ void apply_act_chunk(float (&f)[N], int act) {
 #pragma unroll
     for (int j = 0; j < N; ++j) f[j] = 1.f / (1.f + __expf(-f[j]));
   }
+}
+
+// Grid-wide barrier inside one launch.  `bar` = two ints in global memory (arrivals, departures), zero before the
+// launch; the last CTA to leave zeroes them again.  Every CTA of the grid must be resident for this to complete:
+// launch at most (SMs x CTAs per SM that really fit) CTAs, and do not run two kernels that use it concurrently on one
+// device (each could hold SM slots the other is waiting for).  A kernel launched with programmatic dependent launch
+// behind this one only starts once every CTA here has started, so it cannot take those slots either.
+// Writes made by any thread of any CTA before the barrier are visible to every thread after it (global memory; read
+// them with ld.global.cg / atomics-written data likewise, since this SM's L1 may hold older lines it read earlier).
+__device__ __forceinline__ void grid_barrier(int* bar, int* err_flag) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int n = (int)(gridDim.x * gridDim.y * gridDim.z);
+    __threadfence();
+    atomicAdd(bar, 1);
+    const long long t0 = clock64();
+    int seen;
+    do {
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(bar) : "memory");
+      if (seen >= n) break;
+      __nanosleep(32);
+      if (clock64() - t0 > (4LL << 30)) {  // ~2 s: some CTA of the grid never became resident
+        if (err_flag != nullptr) atomicExch(err_flag, (int)kErrGridBarrierTimeout);
+        break;
+      }
+    } while (true);
+    if (atomicAdd(bar + 1, 1) == n - 1) {  // everybody has seen the full count
+      bar[0] = 0;
+      bar[1] = 0;
+    }
+    __threadfence();
+  }
+  __syncthreads();
 }
 
 }  // namespace dcgan

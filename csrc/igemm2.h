@@ -39,6 +39,20 @@ struct Igemm2Params {
   int bn_slab_out_rows;   // output rows (pixels) per slab
   int bn_stat_groups;     // slab g uses the statistics / pre-activations of group min(g, bn_stat_groups - 1)
   int bn_act;             // the layer's activation (ReLU / LeakyReLU)
+  // optional elementwise pass after a grid-wide barrier (every tile stored, every sum complete): the batch-norm
+  // forward apply of the layer this conv feeds (tail_kind 1; bn_gamma / bn_beta / bn_act are that layer's, `stats`
+  // its sums) or the backward apply of the layer `out` is the activation gradient of (tail_kind 2, after bn_red)
+  int tail_kind;
+  int rows_out;           // rows of `out`
+  void* tail_dst;         // 1: post-activation bf16.  2: gradient w.r.t. the pre-activation, bf16.  Shape of `out`
+  float* tail_saved;      // 1: [groups][2][Cn] (mean, rstd) kept for the backward pass
+  float* tail_ema_mean;   // 1: optional shadows [groups][Cn]
+  float* tail_ema_var;
+  float tail_eps, tail_decay;
+  float* tail_dgamma;     // 2: optional [Cn], = sum over the first tail_param_slabs slabs
+  float* tail_dbeta;
+  int tail_param_slabs;
+  int* grid_barrier;      // two ints (arrivals, departures), zero between launches
   long long* dbg;         // bring-up only (-DIGEMM2_TIMING): per-CTA cycle counters [CTA][16]
   float* partials;        // split-K scratch: [tile][slice][BLOCK_N / 4][128] float4
   int* counters;          // split-K arrival counters per tile (zero between launches)
@@ -54,17 +68,32 @@ struct BnRedArgs {  // see Igemm2Params::bn_*
   const float* beta;
   float* red;
   int slabs, stat_groups, act;
+  // optional: finish the batch-norm backward pass in the same launch (see Igemm2Params::tail_*)
+  void* dpre;
+  float* dgamma;
+  float* dbeta;
+  int param_slabs;
+};
+struct BnFwdArgs {  // batch-norm forward apply in the conv's launch; `stats` of igemm2_conv must be given
+  void* act_out;
+  const float* gamma;
+  const float* beta;
+  float* saved;
+  float* ema_mean;
+  float* ema_var;
+  float eps, decay;
+  int act;
 };
 int igemm2_conv(int transposed, const void* x, const void* w, const float* bias, void* out, int NB, int H, int W,
                 int Cin, int Cout, int act, int block_n, int b_mn, float* stats, int stat_groups,
-                cudaStream_t stream, const BnRedArgs* bnred = nullptr);
+                cudaStream_t stream, const BnRedArgs* bnred = nullptr, const BnFwdArgs* bnfwd = nullptr);
 // Filter gradient; see dcgan_conv_wgrad.
 int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd, int splits,
                  int block_n, cudaStream_t stream);
 // (tile width, K slices) for `tiles_bn64` 64-wide tiles of `kb_per_tile` k-blocks on the persistent grid
 void igemm2_plan(long tiles_bn64, double kb_per_tile, int Cn, int min_kb, int force_bn, int* block_n, int* ksplit);
 
-// helpers of igemm2_sm100.cu shared with igemm3_sm100.cu
+// helpers of igemm2_sm100.cu (also used by the bring-up harness)
 struct CUtensorMap_st;
 int igemm2_tmap_nhwc(const void* ptr, int N, int H, int W, int C, int bw, int bh, int bn, int stride, void* out_map);
 int igemm2_tmap_2d(const void* ptr, unsigned long long rows, unsigned long long cols, unsigned box_r, unsigned box_c,
@@ -78,6 +107,7 @@ int igemm2_forced_ksplit();
 void igemm2_set_debug(long long* ptr);
 void igemm2_set_max_ctas(int v);
 void igemm2_set_ksplit(int v);
+void igemm2_set_tile(int v);
 void igemm2_set_stage_mode(int v);
 int igemm2_set_workspace(void* ptr, size_t bytes);
 

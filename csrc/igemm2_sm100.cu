@@ -26,10 +26,12 @@
 #include <mutex>
 #include <unordered_map>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
 #include "igemm2.h"
+#include "bn_tail.cuh"
 #include "../include/dcgan_b200.h"
 
 namespace dcgan {
@@ -134,6 +136,10 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
               const __grid_constant__ CUtensorMap tmap_d,  // dense operand: 2-D (filter, or W: the small activation)
               const Igemm2Params p) {
   pdl_launch_dependents();
+#ifdef IGEMM2_TIMING
+  long long t_kernel_begin;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_kernel_begin));
+#endif
   using L = Smem2<BLOCK_N, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -567,10 +573,42 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
 #endif
   }
 
+#ifdef IGEMM2_TIMING
+  if (tid == 0 && p.dbg != nullptr) {  // residency probe: which SM, when (ns)
+    long long* d = p.dbg + (size_t)blockIdx.x * 16;
+    unsigned smid; long long t1;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    d[12] = smid; d[13] = t_kernel_begin; d[14] = t1;
+  }
+#endif
   // ---- teardown ---------------------------------------------------------------------------------
   tc_fence_before();
   __syncthreads();
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, 2 * BLOCK_N);
+
+  // ---- batch-norm tail ----------------------------------------------------------------------------
+  // Once every CTA has stored its tiles and flushed its column sums, the whole grid runs the elementwise pass that
+  // used to be a kernel of its own (bn_apply / bn_bwd_apply).  The launch keeps the grid within the CTAs that are
+  // resident at once (launch2), which the barrier needs.
+  if constexpr (MODE != MODE_W) {
+    if (p.tail_kind != 0) {
+      grid_barrier(p.grid_barrier, p.err_flag);
+      const int groups = p.rows_total / p.stat_group_rows;
+      if (p.tail_kind == 1) {
+        bn_fwd_apply_grid<kThreads>(reinterpret_cast<const __nv_bfloat16*>(p.out),
+                                    reinterpret_cast<__nv_bfloat16*>(p.tail_dst), p.stats, p.bn_gamma, p.bn_beta,
+                                    p.tail_saved, p.tail_ema_mean, p.tail_ema_var, groups, p.rows_out / groups, p.Cn,
+                                    p.tail_eps, p.tail_decay, p.bn_act);
+      } else {
+        bn_bwd_apply_grid<kThreads>(reinterpret_cast<const __nv_bfloat16*>(p.out),
+                                    reinterpret_cast<const __nv_bfloat16*>(p.bn_pre),
+                                    reinterpret_cast<__nv_bfloat16*>(p.tail_dst), p.bn_saved, p.bn_gamma, p.bn_beta,
+                                    p.bn_red, p.tail_dgamma, p.tail_dbeta, groups, p.bn_stat_groups,
+                                    p.tail_param_slabs, p.bn_slab_out_rows, p.Cn, p.bn_act);
+      }
+    }
+  }
 }
 
 // =================================================================================================
@@ -724,6 +762,7 @@ int num_sms() {
 
 int g_max_ctas = 0;        // 0 = one CTA per SM
 int g_force_ksplit2 = 0;   // 0 = chosen per layer
+int g_pref_bn = 0;         // 0 = cost model; 64 / 128 / 256 = tile width wherever it divides the layer
 int g_stage_override = 0;  // 0 = deepest ring that fits
 
 // MINB = CTAs per SM the configuration is built for.  A single MMA-issuing warp spends ~450 cycles of control flow
@@ -740,9 +779,20 @@ int launch2(const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p,
   if (!attr_done[dev]) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal) != cudaSuccess)
       return DCGAN_ERR_LAUNCH;
+    // all of the SM's unified memory as shared memory: MINB CTAs of this size only fit with the largest carve-out
+    // (and the occupancy query below answers for the configured preference, not for what a launch would pick)
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     attr_done[dev] = true;
   }
-  const int ctas = g_max_ctas > 0 ? g_max_ctas : num_sms() * MINB;
+  int ctas = g_max_ctas > 0 ? g_max_ctas : num_sms() * MINB;
+  // The grid barrier of the batch-norm tail needs every CTA resident.  MINB CTAs per SM fit by construction:
+  // registers through __launch_bounds__(kThreads, MINB), shared memory through the assertion below, TMEM through
+  // 2 * BLOCK_N * MINB <= 512 columns.  (cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for the MINB = 2
+  // configurations although two CTAs do run per SM -- measured with the %smid / %globaltimer probe of the
+  // IGEMM2_TIMING build, profiles/igemm2_residency_r2.log -- so it is not consulted.)
+  static_assert(MINB * (L::kTotal + 1024) <= 233472, "MINB CTAs must fit the SM's shared memory");
+  static_assert(MINB * 2 * BLOCK_N <= 512, "MINB CTAs must fit TMEM");
+  if (p.tail_kind != 0 && ctas > num_sms() * MINB) ctas = num_sms() * MINB;
   const int grid = p.total_groups < ctas ? p.total_groups : ctas;
   launch_k(kern, dim3(grid), dim3(kThreads), L::kTotal, stream, tg, td, p);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -776,6 +826,7 @@ bool igemm2_pixel_box(int rows, int rH, int rW, int* bw, int* bh, int* bn) { ret
 static long long* g_dbg = nullptr;
 void igemm2_set_debug(long long* ptr) { g_dbg = ptr; }
 void igemm2_set_max_ctas(int v) { g_max_ctas = v > 0 ? v : 0; }
+void igemm2_set_tile(int v) { g_pref_bn = (v == 64 || v == 128 || v == 256) ? v : 0; }
 void igemm2_set_ksplit(int v) { g_force_ksplit2 = (v >= 1 && v <= 16) ? v : 0; }
 void igemm2_set_stage_mode(int v) { g_stage_override = v; }
 
@@ -806,6 +857,7 @@ void igemm2_plan(long tiles_bn64, double kb_per_tile, int Cn, int min_kb, int fo
   *block_n = -1;
   *ksplit = 1;
   const int cands[3] = {256, 128, 64};
+  if (force_bn <= 0 && g_pref_bn > 0 && Cn % g_pref_bn == 0) force_bn = g_pref_bn;
   for (int i = 0; i < 3; ++i) {
     const int bn = cands[i];
     if (Cn % bn) continue;
@@ -839,12 +891,17 @@ int igemm2_attach_scratch(Igemm2Params* p, long tiles, int cols_per_tile) { retu
 static int attach_scratch(Igemm2Params* p, long tiles, int block_n) {
   p->partials = nullptr;
   p->counters = nullptr;
-  if (p->ksplit <= 1) return 0;
+  p->grid_barrier = nullptr;
+  if (p->ksplit <= 1 && p->tail_kind == 0) return 0;
   Workspace ws;
   int rc = get_workspace(&ws);
   if (rc) return rc;
+  // the last two ints of the (zero) counter region are the grid barrier of the batch-norm tail
+  const long max_tiles = (long)(kCounterBytes / 4) - 2;
+  if (p->tail_kind != 0) p->grid_barrier = reinterpret_cast<int*>(ws.ptr) + max_tiles;
+  if (p->ksplit <= 1) return 0;
   const size_t need = kCounterBytes + (size_t)tiles * p->ksplit * kBlockM * block_n * 4;
-  if (tiles > (long)(kCounterBytes / 4) || need > ws.bytes) { p->ksplit = 1; return 0; }  // too big: do not split
+  if (tiles > max_tiles || need > ws.bytes) { p->ksplit = 1; return 0; }  // too big: do not split
   p->counters = reinterpret_cast<int*>(ws.ptr);
   p->partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ws.ptr) + kCounterBytes);
   return 0;
@@ -852,9 +909,10 @@ static int attach_scratch(Igemm2Params* p, long tiles, int block_n) {
 
 int igemm2_conv(int transposed, const void* x, const void* w, const float* bias, void* out, int NB, int H, int W,
                 int Cin, int Cout, int act, int block_n, int b_mn, float* stats, int stat_groups,
-                cudaStream_t stream, const BnRedArgs* bnred) {
+                cudaStream_t stream, const BnRedArgs* bnred, const BnFwdArgs* bnfwd) {
   if (Cin % 64 || Cout % 64) return DCGAN_ERR_SHAPE;
-  if (bnred != nullptr && (stats != nullptr || bias != nullptr || act != 0)) return DCGAN_ERR_SHAPE;
+  if (bnred != nullptr && (stats != nullptr || bias != nullptr || act != 0 || bnfwd != nullptr)) return DCGAN_ERR_SHAPE;
+  if (bnfwd != nullptr && (stats == nullptr || act != 0)) return DCGAN_ERR_SHAPE;
   if (!transposed && ((H & 1) || (W & 1))) return DCGAN_ERR_SHAPE;
   if (transposed && b_mn) return DCGAN_ERR_SHAPE;
   const int rH = transposed ? H : H / 2, rW = transposed ? W : W / 2;
@@ -885,7 +943,22 @@ int igemm2_conv(int transposed, const void* x, const void* w, const float* bias,
     p.bn_red = bnred->red; p.bn_stat_groups = bnred->stat_groups; p.bn_act = bnred->act;
     p.stat_group_rows = (NB / bnred->slabs) * rH * rW;
     p.bn_slab_out_rows = (NB / bnred->slabs) * p.oH * p.oW;
+    if (bnred->dpre != nullptr) {
+      if (bnred->param_slabs < 0 || bnred->param_slabs > bnred->slabs) return DCGAN_ERR_SHAPE;
+      p.tail_kind = 2;
+      p.tail_dst = bnred->dpre;
+      p.tail_dgamma = bnred->dgamma; p.tail_dbeta = bnred->dbeta; p.tail_param_slabs = bnred->param_slabs;
+    }
   }
+  if (bnfwd != nullptr) {
+    if (NB % stat_groups) return DCGAN_ERR_SHAPE;  // groups are sets of whole images (contiguous in `out`)
+    p.tail_kind = 1;
+    p.tail_dst = bnfwd->act_out;
+    p.bn_gamma = bnfwd->gamma; p.bn_beta = bnfwd->beta; p.bn_act = bnfwd->act;
+    p.tail_saved = bnfwd->saved; p.tail_ema_mean = bnfwd->ema_mean; p.tail_ema_var = bnfwd->ema_var;
+    p.tail_eps = bnfwd->eps; p.tail_decay = bnfwd->decay;
+  }
+  p.rows_out = NB * p.oH * p.oW;
   const int cpt = Cin / 64;
   const int mt = (p.rows_total + kBlockM - 1) / kBlockM;
   const int classes = transposed ? 4 : 1;

@@ -905,6 +905,7 @@ void dcgan_set_igemm_ksplit(int v) {
 }
 void dcgan_set_igemm_max_ctas(int v) { igemm2_set_max_ctas(v); }
 void dcgan_set_igemm_stage_mode(int v) { igemm2_set_stage_mode(v); }
+void dcgan_set_igemm_tile(int v) { igemm2_set_tile(v); }
 void dcgan_set_igemm_debug(long long* ptr) { igemm2_set_debug(ptr); }
 int dcgan_set_workspace(void* ptr, size_t bytes) { return igemm2_set_workspace(ptr, bytes); }
 static inline bool use_v2() { return (g_igemm_tuning & 128) == 0; }
@@ -1057,7 +1058,7 @@ int dcgan_conv_tconv_bnred(const void* x, const void* w_nk, void* out, const voi
                            const float* gamma, const float* beta, float* red, int slabs, int stat_groups, int bn_act,
                            int NB, int H, int W, int Cin, int Cout, int block_n, cudaStream_t stream) {
   if (!use_v2()) return DCGAN_ERR_SHAPE;
-  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act};
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, nullptr, nullptr, nullptr, 0};
   return igemm2_conv(1, x, w_nk, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 0, nullptr, 1, stream, &a);
 }
 
@@ -1066,8 +1067,49 @@ int dcgan_conv_fprop_kn_bnred(const void* x, const void* w_kn, void* out, const 
                               int bn_act, int NB, int H, int W, int Cin, int Cout, int block_n,
                               cudaStream_t stream) {
   if (!use_v2()) return DCGAN_ERR_SHAPE;
-  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act};
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, nullptr, nullptr, nullptr, 0};
   return igemm2_conv(0, x, w_kn, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 1, nullptr, 1, stream, &a);
+}
+
+// The same with the rest of that layer's batch-norm backward pass in the launch: after a grid-wide barrier the CTAs
+// turn out (= da) into dpre and CTA 0 writes dgamma / dbeta (what dcgan_bn_bwd_apply does in a launch of its own).
+int dcgan_conv_tconv_bnbwd(const void* x, const void* w_nk, void* out, const void* pre, const float* saved,
+                           const float* gamma, const float* beta, float* red, void* dpre, float* dgamma, float* dbeta,
+                           int slabs, int stat_groups, int param_slabs, int bn_act, int NB, int H, int W, int Cin,
+                           int Cout, int block_n, cudaStream_t stream) {
+  if (!use_v2() || dpre == nullptr) return DCGAN_ERR_SHAPE;
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, dpre, dgamma, dbeta, param_slabs};
+  return igemm2_conv(1, x, w_nk, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 0, nullptr, 1, stream, &a);
+}
+
+int dcgan_conv_fprop_kn_bnbwd(const void* x, const void* w_kn, void* out, const void* pre, const float* saved,
+                              const float* gamma, const float* beta, float* red, void* dpre, float* dgamma,
+                              float* dbeta, int slabs, int stat_groups, int param_slabs, int bn_act, int NB, int H,
+                              int W, int Cin, int Cout, int block_n, cudaStream_t stream) {
+  if (!use_v2() || dpre == nullptr) return DCGAN_ERR_SHAPE;
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, dpre, dgamma, dbeta, param_slabs};
+  return igemm2_conv(0, x, w_kn, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 1, nullptr, 1, stream, &a);
+}
+
+// Forward conv + training-mode batch norm + activation in one launch: pre = conv(x) + bias (bf16, kept for the
+// backward pass), sums += its per-group moments, then -- after a grid-wide barrier -- act_out = act(bn(pre)), saved =
+// (mean, rstd), EMA shadows advanced (dcgan_conv_*_stats followed by dcgan_bn_apply).
+int dcgan_conv_fprop_kn_bn(const void* x, const void* w_kn, const float* bias, void* pre, void* act_out, float* sums,
+                           const float* gamma, const float* beta, float* saved, float* ema_mean, float* ema_var,
+                           int stat_groups, int NB, int H, int W, int Cin, int Cout, float eps, float decay, int bn_act,
+                           int block_n, cudaStream_t stream) {
+  if (!use_v2() || act_out == nullptr || sums == nullptr) return DCGAN_ERR_SHAPE;
+  BnFwdArgs f{act_out, gamma, beta, saved, ema_mean, ema_var, eps, decay, bn_act};
+  return igemm2_conv(0, x, w_kn, bias, pre, NB, H, W, Cin, Cout, 0, block_n, 1, sums, stat_groups, stream, nullptr, &f);
+}
+
+int dcgan_conv_tconv_bn(const void* x, const void* w_nk, const float* bias, void* pre, void* act_out, float* sums,
+                        const float* gamma, const float* beta, float* saved, float* ema_mean, float* ema_var,
+                        int stat_groups, int NB, int H, int W, int Cin, int Cout, float eps, float decay, int bn_act,
+                        int block_n, cudaStream_t stream) {
+  if (!use_v2() || act_out == nullptr || sums == nullptr) return DCGAN_ERR_SHAPE;
+  BnFwdArgs f{act_out, gamma, beta, saved, ema_mean, ema_var, eps, decay, bn_act};
+  return igemm2_conv(1, x, w_nk, bias, pre, NB, H, W, Cin, Cout, 0, block_n, 0, sums, stat_groups, stream, nullptr, &f);
 }
 
 int dcgan_conv_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, int Ws, int Cg, int Cd,

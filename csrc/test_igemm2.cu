@@ -273,6 +273,20 @@ static void time_layers(bool sweep) {
       for (int b : {0, 1, 150})
         printf("        [cta %3d] producer: %lld cyc, waits %lld (%lld slots) | mma: %lld cyc, wait full %lld (%lld slots), wait tmem %lld, %lld tiles | epilogue: %lld cyc, wait %lld, tmem/scratch loads %lld, stores %lld\n",
                b, h[b * 16], h[b * 16 + 1], h[b * 16 + 2], h[b * 16 + 3], h[b * 16 + 4], h[b * 16 + 5], h[b * 16 + 6], h[b * 16 + 7], h[b * 16 + 8], h[b * 16 + 9], h[b * 16 + 10], h[b * 16 + 11]);
+      {  // how many CTAs were resident on one SM at the same time (start / end stamps in ns)
+        int max_overlap = 0, ctas = 0;
+        for (int b = 0; b < 296; ++b) {
+          if (h[b * 16 + 14] == 0) continue;
+          ++ctas;
+          int ov = 0;
+          for (int c = 0; c < 296; ++c)
+            if (h[c * 16 + 14] != 0 && h[c * 16 + 12] == h[b * 16 + 12] && h[c * 16 + 13] < h[b * 16 + 14] &&
+                h[b * 16 + 13] < h[c * 16 + 14])
+              ++ov;
+          if (ov > max_overlap) max_overlap = ov;
+        }
+        printf("        [residency] %d CTAs, at most %d resident on one SM at a time\n", ctas, max_overlap);
+      }
       cudaFree(dbg);
     }
 #endif

@@ -173,6 +173,7 @@ class DCGANEngine:
         self.logits = torch.zeros(2 * B, **f32)
         self.probs = torch.zeros(2 * B, **f32)
         self.losses = torch.zeros(3, **f32)
+        self._losses_pass2 = torch.zeros(3, **f32)
         self.dlogit = torch.zeros(3 * B, **f32)
         self.counters = (alloc("counters", 2, torch.int64) if alloc is not None
                          else torch.zeros(2, dtype=torch.int64, device=dev))  # [adam_t, global_step]
@@ -194,6 +195,18 @@ class DCGANEngine:
         self.fuse_bn_bwd = (os.environ.get("DCGAN_FUSE_BN_BWD", "1") != "0"
                             and (int(os.environ.get("DCGAN_IGEMM_TUNING", "1")) & 128) == 0)
         # measured: 0.876 -> 0.815 ms/step on one GPU, 0.958 -> 0.905 on two (profiles/README.md)
+        # batch norm inside the producing conv's launch (grid-wide barrier + elementwise tail), and one-launch
+        # batch-norm kernels for the layers whose producer is not an implicit-GEMM conv.  All of them are issued on
+        # the main stream only: two kernels that wait on a grid barrier must not share the device.
+        # DCGAN_FUSE_BN is a bit mask for A/B runs: 1 forward conv tails, 2 backward conv tails, 4 one-launch forward
+        # batch norm (g_bn0), 8 one-launch backward batch norm (d_bn3, g_bn3); the first-generation kernels have none.
+        # Default off: measured on B200 (profiles/README.md, "batch norm inside the conv launch") every variant is
+        # slower than the separate kernels -- with programmatic dependent launch a kernel boundary costs ~1.5 us, the
+        # software grid barrier ~3 us, and the tail runs at the conv kernel's low occupancy.
+        self.fuse_bn = int(os.environ.get("DCGAN_FUSE_BN", "0"))
+        if (int(os.environ.get("DCGAN_IGEMM_TUNING", "1")) & 128) != 0:
+            self.fuse_bn &= ~3
+        self._grid_barrier = torch.zeros(2, dtype=torch.int32, device=self.device)
         self.prioritize_main = os.environ.get("DCGAN_MAIN_PRIORITY", "1") != "0"
         self.split_d_forward = self.wgrad_overlap and os.environ.get("DCGAN_SPLIT_D_FORWARD", "0") != "0"
         self.side = torch.cuda.Stream(self.device)
@@ -235,16 +248,44 @@ class DCGANEngine:
         x2, y2 = pre.view(-1, C), act_out.view(-1, C)
         p = self.params
         if train:
+            decay = self.cfg.bn_momentum if self._ema_decay_override is None else self._ema_decay_override
+            if not stats_done and self._bn_tail_ok(4):
+                K.bn_forward_fused(x2, y2, st["sums"], p[f"{name}/gamma"], p[f"{name}/beta"], st["saved"],
+                                   st["ema_mean"], st["ema_var"], self._grid_barrier, G, st["act"], self.cfg.bn_eps,
+                                   decay)
+                return
             if not stats_done:
                 K.bn_stats(x2, st["sums"], G)
             if self._sync_bn_active():
                 self.comm.allreduce_bn(st["sums"])
-            decay = self.cfg.bn_momentum if self._ema_decay_override is None else self._ema_decay_override
             K.bn_apply(x2, y2, st["sums"], p[f"{name}/gamma"], p[f"{name}/beta"], st["saved"], st["ema_mean"],
                        st["ema_var"], G, st["act"], self.cfg.bn_eps, decay)
         else:
             K.bn_apply(x2, y2, st["sums"], p[f"{name}/gamma"], p[f"{name}/beta"], None, st["ema_mean"],
                        st["ema_var"], 1, st["act"], self.cfg.bn_eps, self.cfg.bn_momentum, use_ema=True)
+
+    def _bn_tail_ok(self, kind: int) -> bool:
+        """Batch norm may be finished inside the launch that produces its input: needs purely local statistics (a
+        cross-replica reduction has to happen between the two halves) and the main stream (see ``fuse_bn``)."""
+        return ((self.fuse_bn & kind) != 0 and not self._sync_bn_active()
+                and torch.cuda.current_stream(self.device) != self.side)
+
+    def _conv_bn_fwd(self, name, x, w, bias, pre, act_out, groups, transposed) -> None:
+        """conv + batch norm (training mode) + activation: one launch when possible, else conv(+moments) and apply."""
+        st, p = self.bn[name], self.params
+        fused_stats = self._stats_fusable(name, pre)
+        if fused_stats and self._bn_tail_ok(1):
+            decay = self.cfg.bn_momentum if self._ema_decay_override is None else self._ema_decay_override
+            K.conv_bn_fwd(x, w, bias, pre, act_out, st["sums"], p[f"{name}/gamma"], p[f"{name}/beta"], st["saved"],
+                          st["ema_mean"], st["ema_var"], groups, st["act"], transposed, self.cfg.bn_eps, decay)
+            return
+        if fused_stats:
+            (K.conv_tconv_stats if transposed else K.conv_fprop_kn_stats)(x, w, bias, pre, st["sums"], groups)
+        elif transposed:
+            K.conv_tconv(x, w, bias, out=pre)
+        else:
+            K.conv_fprop_kn(x, w, bias, out=pre)
+        self._bn_fwd(name, pre, act_out, True, stats_done=fused_stats)
 
     def _sync_bn_active(self) -> bool:
         return (self.comm is not None and getattr(self.comm, "sync_bn", False) and not self._local_bn_only)
@@ -263,12 +304,11 @@ class DCGANEngine:
         self._bn_fwd("g_bn0", pre[0], act[0], train)
         for i in (1, 2, 3):
             w = self.w_native[f"g_h{i}/w"].view(25, self.g_ch[i], self.g_ch[i - 1])
-            fused = train and self._stats_fusable(f"g_bn{i}", pre[i])
-            if fused:  # batch-norm moments fall out of the conv epilogue
-                K.conv_tconv_stats(act[i - 1], w, p[f"g_h{i}/biases"], pre[i], self.bn[f"g_bn{i}"]["sums"], 1)
+            if train:  # batch-norm moments fall out of the conv epilogue, the apply pass is the launch's tail
+                self._conv_bn_fwd(f"g_bn{i}", act[i - 1], w, p[f"g_h{i}/biases"], pre[i], act[i], 1, True)
             else:
                 K.conv_tconv(act[i - 1], w, p[f"g_h{i}/biases"], out=pre[i])
-            self._bn_fwd(f"g_bn{i}", pre[i], act[i], train, stats_done=fused)
+                self._bn_fwd(f"g_bn{i}", pre[i], act[i], False)
         out = self.d_in[B:] if train else self.s_img
         K.c3_tconv(act[3], p["g_h4/w"], p["g_h4/biases"], act="tanh", out=out, w_bf16=self.w_native["g_h4/w"])
         return out
@@ -278,13 +318,8 @@ class DCGANEngine:
         K.c3_fprop(self.d_in, p["d_h0_conv/w"], p["d_h0_conv/biases"], act="lrelu", out=self.d_act[0])
         for i in (1, 2, 3):
             w = self.w_native[f"d_h{i}_conv/w"].view(25, self.d_ch[i], self.d_ch[i + 1])
-            fused = self._stats_fusable(f"d_bn{i}", self.d_pre[i])
-            if fused:
-                K.conv_fprop_kn_stats(self.d_act[i - 1], w, p[f"d_h{i}_conv/biases"], self.d_pre[i],
-                                      self.bn[f"d_bn{i}"]["sums"], 2)
-            else:
-                K.conv_fprop_kn(self.d_act[i - 1], w, p[f"d_h{i}_conv/biases"], out=self.d_pre[i])
-            self._bn_fwd(f"d_bn{i}", self.d_pre[i], self.d_act[i], stats_done=fused)
+            self._conv_bn_fwd(f"d_bn{i}", self.d_act[i - 1], w, p[f"d_h{i}_conv/biases"], self.d_pre[i],
+                              self.d_act[i], 2, False)
         K.head_fwd(self.d_act[3].view(2 * self.B, -1), p["d_h3_lin/Matrix"], p["d_h3_lin/bias"], self.logits)
 
     def discriminator_forward_half(self, h: int) -> None:
@@ -323,18 +358,32 @@ class DCGANEngine:
         imgs_per_slab = da.shape[0] // self.bn[name]["slabs"]
         return (imgs_per_slab * tile_rows_per_image) % 128 == 0
 
-    def _dgrad_bnred(self, name, x, w, da, pre, transposed):
-        """dgrad conv writing ``da`` + the batch-norm backward reductions of layer ``name`` in one launch."""
+    def _dgrad_bnred(self, name, x, w, da, pre, transposed, dpre=None) -> str:
+        """dgrad conv writing ``da`` + the batch-norm backward reductions of layer ``name`` in one launch ("red"), or
+        -- statistics local, main stream -- that layer's whole backward pass (``dpre``, dgamma, dbeta; "full")."""
         st = self.bn[name]
-        p = self.params
+        p, g = self.params, self.grad_views
+        if dpre is not None and self._bn_tail_ok(2):
+            K.conv_dgrad_bnbwd(x, w, da, pre, st["saved"], p[f"{name}/gamma"], p[f"{name}/beta"], st["red"], dpre,
+                               g[f"{name}/gamma"], g[f"{name}/beta"], st["slabs"], st["groups"], st["groups"],
+                               st["act"], transposed)
+            return "full"
         K.conv_dgrad_bnred(x, w, da, pre, st["saved"], p[f"{name}/gamma"], p[f"{name}/beta"], st["red"],
                            st["slabs"], st["groups"], st["act"], transposed)
+        return "red"
 
     def _bn_bwd(self, name, da, pre, dpre, reduce_done=False):
         st = self.bn[name]
         C = st["C"]
         p, g = self.params, self.grad_views
         slabs, G = st["slabs"], st["groups"]
+        if reduce_done == "full":   # the conv that produced ``da`` finished this layer's backward pass as well
+            return
+        if not reduce_done and self._bn_tail_ok(8):
+            K.bn_backward_fused(da.view(-1, C), pre.view(-1, C), dpre.view(-1, C), st["saved"], p[f"{name}/gamma"],
+                                p[f"{name}/beta"], st["red"], g[f"{name}/gamma"], g[f"{name}/beta"],
+                                self._grid_barrier, slabs, G, G, st["act"])
+            return
         if not reduce_done:
             K.bn_bwd_reduce(da.view(-1, C), pre.view(-1, C), st["saved"], p[f"{name}/gamma"], p[f"{name}/beta"],
                             st["red"], slabs, G, st["act"])
@@ -400,7 +449,8 @@ class DCGANEngine:
             red_done = i > 1 and self._bnred_fusable(f"d_bn{i - 1}", self.dd_act[i - 1],
                                                      self.d_sz[i + 1] * self.d_sz[i + 1])
             if red_done:
-                self._dgrad_bnred(f"d_bn{i - 1}", self.dd_pre[i], w, self.dd_act[i - 1], self.d_pre[i - 1], True)
+                red_done = self._dgrad_bnred(f"d_bn{i - 1}", self.dd_pre[i], w, self.dd_act[i - 1],
+                                             self.d_pre[i - 1], True, dpre=self.dd_pre[i - 1])
             else:
                 K.conv_tconv(self.dd_pre[i], w, None, out=self.dd_act[i - 1])
         C0 = self.d_ch[1]
@@ -427,7 +477,8 @@ class DCGANEngine:
             w = self.w_native[f"g_h{i}/w"].view(25, co, ci)
             red_done = self._bnred_fusable(f"g_bn{i - 1}", self.dg_act[i - 1], self.g_sz[i - 1] * self.g_sz[i - 1])
             if red_done:
-                self._dgrad_bnred(f"g_bn{i - 1}", self.dg_pre[i], w, self.dg_act[i - 1], self.g_pre[i - 1], False)
+                red_done = self._dgrad_bnred(f"g_bn{i - 1}", self.dg_pre[i], w, self.dg_act[i - 1],
+                                             self.g_pre[i - 1], False, dpre=self.dg_pre[i - 1])
             else:
                 K.conv_fprop_kn(self.dg_pre[i], w, None, out=self.dg_act[i - 1])
         self._bn_bwd("g_bn0", self.dg_act[0], self.g_pre[0], self.dg_pre[0], reduce_done=red_done)
@@ -527,7 +578,10 @@ class DCGANEngine:
                 self.discriminator_forward()
             finally:
                 self._ema_decay_override = None
-            K.gan_loss(self.logits, self.losses[:3], self.dlogit, self.probs, None, B, 1.0, False)
+            # d_loss_real / d_loss_fake reported for the step are those of the first pass (before D's update), g_loss
+            # the one G is trained on (against the updated D) -- CPUTrainer._alternating_step returns the same
+            K.gan_loss(self.logits, self._losses_pass2, self.dlogit, self.probs, None, B, 1.0, False)
+            self.losses[2:3].copy_(self._losses_pass2[2:3])
             self.discriminator_backward()
             self.generator_backward()
             self.optimizer_step("g")

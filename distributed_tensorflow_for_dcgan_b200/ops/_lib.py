@@ -26,6 +26,12 @@ _SIGNATURES = {
     "dcgan_conv_wgrad": "pppiiiiiiis",
     "dcgan_conv_tconv_bnred": "ppppppppiiiiiiiiis",
     "dcgan_conv_fprop_kn_bnred": "ppppppppiiiiiiiiis",
+    "dcgan_conv_tconv_bnbwd": "pppppppppppiiiiiiiiiis",
+    "dcgan_conv_fprop_kn_bnbwd": "pppppppppppiiiiiiiiiis",
+    "dcgan_conv_fprop_kn_bn": "pppppppppppiiiiiiffiis",
+    "dcgan_conv_tconv_bn": "pppppppppppiiiiiiffiis",
+    "dcgan_bn_forward_fused": "pppppppppiiiffis",
+    "dcgan_bn_backward_fused": "ppppppppppiiiiiis",
     "dcgan_c3_fprop": "ppppiiiiis",
     "dcgan_c3_tconv": "ppppppiiiiiis",
     "dcgan_c3_wgrad": "pppiiiis",
@@ -91,7 +97,8 @@ def load() -> ctypes.CDLL:
     lib.dcgan_set_workspace.argtypes = [c_void_p, c_size_t]
     lib.dcgan_set_workspace.restype = c_int
     for setter in ("dcgan_set_igemm_tuning", "dcgan_set_igemm_ksplit", "dcgan_set_wgrad_cta_target",
-                   "dcgan_set_adam_blocks", "dcgan_set_igemm_max_ctas", "dcgan_set_igemm_stage_mode"):
+                   "dcgan_set_adam_blocks", "dcgan_set_igemm_max_ctas", "dcgan_set_igemm_stage_mode",
+                   "dcgan_set_igemm_tile"):
         getattr(lib, setter).argtypes = [c_int]
         getattr(lib, setter).restype = None
     # profiling overrides (A/B runs of bench.py without a rebuild)
@@ -101,6 +108,8 @@ def load() -> ctypes.CDLL:
         lib.dcgan_set_igemm_ksplit(int(os.environ["DCGAN_IGEMM_KSPLIT"]))
     if os.environ.get("DCGAN_IGEMM_STAGE_MODE"):
         lib.dcgan_set_igemm_stage_mode(int(os.environ["DCGAN_IGEMM_STAGE_MODE"]))
+    if os.environ.get("DCGAN_IGEMM_TILE"):
+        lib.dcgan_set_igemm_tile(int(os.environ["DCGAN_IGEMM_TILE"]))
     if os.environ.get("DCGAN_IGEMM_MAX_CTAS"):
         lib.dcgan_set_igemm_max_ctas(int(os.environ["DCGAN_IGEMM_MAX_CTAS"]))
     if os.environ.get("DCGAN_WGRAD_CTAS"):

@@ -75,6 +75,32 @@ def conv_dgrad_bnred(x, w, out, pre, saved, gamma, beta, red, slabs, stat_groups
     return out
 
 
+def conv_dgrad_bnbwd(x, w, out, pre, saved, gamma, beta, red, dpre, dgamma, dbeta, slabs, stat_groups, param_slabs,
+                     act, transposed, block_n=0):
+    """``conv_dgrad_bnred`` with the rest of that layer's batch-norm backward pass in the same launch: behind a
+    grid-wide barrier the kernel turns ``out`` (= da) into ``dpre`` and writes ``dgamma`` / ``dbeta``.  Kernels of
+    this family (this, ``conv_bn_fwd``, ``bn_forward_fused``, ``bn_backward_fused``) go on ONE stream per device."""
+    N, H, W, Cin = x.shape
+    Cout = w.shape[1] if transposed else w.shape[2]
+    call("dcgan_conv_tconv_bnbwd" if transposed else "dcgan_conv_fprop_kn_bnbwd", ptr(x), ptr(w), ptr(out), ptr(pre),
+         ptr(saved), ptr(gamma), ptr(beta), ptr(red), ptr(dpre), ptr(dgamma), ptr(dbeta), slabs, stat_groups,
+         param_slabs, ACT[act], N, H, W, Cin, Cout, block_n)
+    return dpre
+
+
+def conv_bn_fwd(x, w, bias, pre, act_out, sums, gamma, beta, saved, ema_mean, ema_var, groups, act, transposed,
+                eps=1e-5, decay=0.9, block_n=0):
+    """Forward conv (transposed: w [25,Cout,Cin]; strided: w [25,Cin,Cout]) + training-mode batch norm + activation
+    in one launch: ``pre`` (bf16 conv output, kept for backward), ``sums`` [groups,2,Cout] (+=), then
+    ``act_out = act(bn(pre))``, ``saved`` = (mean, rstd) and the EMA shadows."""
+    N, H, W, Cin = x.shape
+    Cout = w.shape[1] if transposed else w.shape[2]
+    call("dcgan_conv_tconv_bn" if transposed else "dcgan_conv_fprop_kn_bn", ptr(x), ptr(w), ptr(bias), ptr(pre),
+         ptr(act_out), ptr(sums), ptr(gamma), ptr(beta), ptr(saved), ptr(ema_mean), ptr(ema_var), groups, N, H, W,
+         Cin, Cout, eps, decay, ACT[act], block_n)
+    return act_out
+
+
 def conv_wgrad(big, small, dw, splits=0, block_n=0):
     """dw[25,Cg,Cd] (f32, +=) from big [N,2Hs,2Ws,Cg] and small [N,Hs,Ws,Cd]."""
     N, Hs, Ws, Cd = small.shape
@@ -150,6 +176,24 @@ def bn_bwd_apply(da2d, pre2d, dpre2d, saved, gamma, beta, red, dgamma, dbeta, gr
     rows, C = da2d.shape[0] // groups, da2d.shape[-1]
     call("dcgan_bn_bwd_apply", ptr(da2d), ptr(pre2d), ptr(dpre2d), ptr(saved), ptr(gamma), ptr(beta), ptr(red),
          ptr(dgamma), ptr(dbeta), groups, stat_groups, param_groups, rows, C, ACT[act])
+    return dpre2d
+
+
+def bn_forward_fused(x2d, y2d, sums, gamma, beta, saved, ema_mean, ema_var, barrier, groups, act, eps=1e-5,
+                     decay=0.9):
+    """``bn_stats`` + ``bn_apply`` (training mode) in one launch; ``barrier`` = two zero int32 on the device."""
+    rows, C = x2d.shape[0] // groups, x2d.shape[-1]
+    call("dcgan_bn_forward_fused", ptr(x2d), ptr(y2d), ptr(sums), ptr(gamma), ptr(beta), ptr(saved), ptr(ema_mean),
+         ptr(ema_var), ptr(barrier), groups, rows, C, eps, decay, ACT[act])
+    return y2d
+
+
+def bn_backward_fused(da2d, pre2d, dpre2d, saved, gamma, beta, red, dgamma, dbeta, barrier, groups, stat_groups,
+                      param_groups, act):
+    """``bn_bwd_reduce`` + ``bn_bwd_apply`` in one launch."""
+    rows, C = da2d.shape[0] // groups, da2d.shape[-1]
+    call("dcgan_bn_backward_fused", ptr(da2d), ptr(pre2d), ptr(dpre2d), ptr(saved), ptr(gamma), ptr(beta), ptr(red),
+         ptr(dgamma), ptr(dbeta), ptr(barrier), groups, stat_groups, param_groups, rows, C, ACT[act])
     return dpre2d
 
 

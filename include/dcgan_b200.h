@@ -55,6 +55,10 @@ void dcgan_set_igemm_tuning(int v);
  * (0 = default: two CTAs per SM for tiles of 64 / 128 columns; 2 = one CTA per SM with the deepest ring). */
 void dcgan_set_igemm_max_ctas(int v);
 void dcgan_set_igemm_stage_mode(int v);
+/* Tile width (64 / 128 / 256 output channels) used wherever it divides the layer; 0 = the library's choice. */
+void dcgan_set_igemm_tile(int v);
+/* Bring-up only: per-CTA cycle counters [CTA][16] written by a library built with -DIGEMM2_TIMING (else ignored). */
+void dcgan_set_igemm_debug(long long* counters);
 /* Split-K scratch of the second-generation kernels for the calling host thread: `bytes` of device memory whose
  * first 64 KiB are zero (arrival counters; the kernels leave them zero), at least 1 MiB + 64 KiB.  Kernels that
  * may run concurrently (different streams) must not share a workspace.  NULL returns to the library's default
@@ -123,6 +127,34 @@ int dcgan_conv_fprop_kn_bnred(const void* x, const void* w_kn, void* out, const 
                               int bn_act, int NB, int H, int W, int Cin, int Cout, int block_n,
                               cudaStream_t stream);
 
+/* dcgan_conv_*_bnred plus the rest of that layer's batch-norm backward pass in the same launch: once every CTA has
+ * stored its tiles and added its reductions (a grid-wide barrier inside the kernel), the grid rewrites out (= da) as
+ * dpre = gamma * rstd * (dy - mean(dy) - xhat * mean(dy * xhat)) (bf16, shape of out) and CTA 0 writes dgamma / dbeta
+ * (optional) = the reductions summed over the first param_slabs slabs -- dcgan_bn_bwd_apply without its launch.
+ * Uses the calling thread's workspace (dcgan_set_workspace); two kernels of this family (these and dcgan_conv_*_bn,
+ * dcgan_bn_forward_fused, dcgan_bn_backward_fused) must not run concurrently on one device: launch them on one stream. */
+int dcgan_conv_tconv_bnbwd(const void* x, const void* w_nk, void* out, const void* pre, const float* saved,
+                           const float* gamma, const float* beta, float* red, void* dpre, float* dgamma, float* dbeta,
+                           int slabs, int stat_groups, int param_slabs, int bn_act, int NB, int H, int W, int Cin,
+                           int Cout, int block_n, cudaStream_t stream);
+int dcgan_conv_fprop_kn_bnbwd(const void* x, const void* w_kn, void* out, const void* pre, const float* saved,
+                              const float* gamma, const float* beta, float* red, void* dpre, float* dgamma,
+                              float* dbeta, int slabs, int stat_groups, int param_slabs, int bn_act, int NB, int H,
+                              int W, int Cin, int Cout, int block_n, cudaStream_t stream);
+/* Forward conv + training-mode batch norm + activation in one launch (reference: conv2d / deconv2d followed by
+ * batch_norm(train=True) and relu / lrelu, distriubted_model.py:91-121): pre = conv(x) + bias (bf16, kept for the
+ * backward pass), sums[stat_groups][2][Cout] += its moments (zero it first), then behind a grid-wide barrier
+ * act_out = act(gamma * (pre - mean) * rstd + beta), saved[stat_groups][2][Cout] = (mean, rstd), and the EMA shadows
+ * (optional, [stat_groups][Cout]) advance with `decay`.  Same restrictions as dcgan_conv_*_bnbwd. */
+int dcgan_conv_fprop_kn_bn(const void* x, const void* w_kn, const float* bias, void* pre, void* act_out, float* sums,
+                           const float* gamma, const float* beta, float* saved, float* ema_mean, float* ema_var,
+                           int stat_groups, int NB, int H, int W, int Cin, int Cout, float eps, float decay, int bn_act,
+                           int block_n, cudaStream_t stream);
+int dcgan_conv_tconv_bn(const void* x, const void* w_nk, const float* bias, void* pre, void* act_out, float* sums,
+                        const float* gamma, const float* beta, float* saved, float* ema_mean, float* ema_var,
+                        int stat_groups, int NB, int H, int W, int Cin, int Cout, float eps, float decay, int bn_act,
+                        int block_n, cudaStream_t stream);
+
 /* Weight gradient of either layer kind: dw[25][Cg][Cd] (f32, += -- zero it first; the second-generation kernels add each element once, split-K partials are
  * summed in a fixed order, so the result is reproducible bit for bit) += sum over pixels of big[NB,2Hs,2Ws,Cg] (gathered at 2q+k-1) * small[NB,Hs,Ws,Cd].
  * conv2d:  big = layer input, small = output gradient  -> dw is HWIO.
@@ -168,6 +200,17 @@ int dcgan_bn_bwd_reduce(const void* da, const void* pre, const float* saved, con
 int dcgan_bn_bwd_apply(const void* da, const void* pre, void* dpre, const float* saved, const float* gamma,
                        const float* beta, const float* red, float* dgamma, float* dbeta, int groups,
                        int stat_groups, int param_groups, int rows_per_group, int C, int act, cudaStream_t stream);
+/* dcgan_bn_stats + dcgan_bn_apply (training mode) in one launch, and dcgan_bn_bwd_reduce + dcgan_bn_bwd_apply in
+ * one launch: the statistics pass, a grid-wide barrier inside the kernel, then the elementwise pass.  For the layers
+ * whose producer is not one of the convs above (which carry the batch norm in their own launch: dcgan_conv_*_bn,
+ * dcgan_conv_*_bnbwd).  `barrier` = two ints of device memory that are zero (the kernel leaves them zero); sums / red
+ * must be zero on entry.  Not to be run concurrently with another kernel of the grid-barrier family on one device. */
+int dcgan_bn_forward_fused(const void* x, void* y, float* sums, const float* gamma, const float* beta, float* saved,
+                           float* ema_mean, float* ema_var, int* barrier, int groups, int rows_per_group, int C,
+                           float eps, float decay, int act, cudaStream_t st);
+int dcgan_bn_backward_fused(const void* da, const void* pre, void* dpre, const float* saved, const float* gamma,
+                            const float* beta, float* red, float* dgamma, float* dbeta, int* barrier, int groups,
+                            int stat_groups, int param_groups, int rows_per_group, int C, int act, cudaStream_t st);
 /* Batch-norm forward (statistics + normalise + activation) for callers that cannot allocate memory.
  * No counterpart in the reference.  Same result as dcgan_bn_stats followed by dcgan_bn_apply, but the
  * per-channel sums live in a 64 KiB array built into the library (groups*2*C <= 16384 floats, otherwise

@@ -477,3 +477,165 @@ def test_filter_gradient_is_reproducible(cuda_lib):
     finally:
         cuda_lib.dcgan_set_igemm_ksplit(0)
     assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("transposed", [True, False])
+@pytest.mark.parametrize("ksplit", [0, 3])
+def test_conv_with_batch_norm_in_its_launch(cuda_lib, transposed, ksplit):
+    """conv + training-mode batch norm + activation in one launch (grid-wide barrier, then the elementwise tail)
+    against fp32 PyTorch (conv, biased batch moments per group, affine, ReLU / LeakyReLU) and against the
+    two-launch path (conv with moments, then bn_apply), including saved statistics and the EMA shadows."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    groups = 1 if transposed else 2
+    N = 16
+    if transposed:   # [N, 8, 8, 128] -> [N, 16, 16, 64]
+        H, Cin, Cout, oH, act = 8, 128, 64, 16, "relu"
+        x = _rand((N, H, H, Cin), 0.5)
+        w = _rand((25, Cout, Cin), 0.05)
+        wt = w.float().view(5, 5, Cout, Cin).permute(3, 2, 0, 1)
+        full = torch.nn.functional.conv_transpose2d(x.float().permute(0, 3, 1, 2), wt, stride=2)
+        ref = full[:, :, 1:1 + 2 * H, 1:1 + 2 * H].permute(0, 2, 3, 1).contiguous()
+    else:            # [N, 32, 32, 64] -> [N, 16, 16, 128]
+        H, Cin, Cout, oH, act = 32, 64, 128, 16, "lrelu"
+        x = _rand((N, H, H, Cin), 0.5)
+        w = _rand((25, Cin, Cout), 0.05)
+        xp = torch.nn.functional.pad(x.float().permute(0, 3, 1, 2), (1, 2, 1, 2))
+        ref = torch.nn.functional.conv2d(xp, w.float().view(5, 5, Cin, Cout).permute(3, 2, 0, 1), stride=2)
+        ref = ref.permute(0, 2, 3, 1).contiguous()
+    bias = 0.1 * torch.randn(Cout, device="cuda")
+    gamma = 1 + 0.1 * torch.randn(Cout, device="cuda")
+    beta = 0.1 * torch.randn(Cout, device="cuda")
+    ref = ref + bias
+
+    def buffers():
+        return dict(pre=torch.empty(N, oH, oH, Cout, device="cuda", dtype=torch.bfloat16),
+                    out=torch.empty(N, oH, oH, Cout, device="cuda", dtype=torch.bfloat16),
+                    sums=torch.zeros(groups, 2, Cout, device="cuda"), saved=torch.zeros(groups, 2, Cout, device="cuda"),
+                    em=torch.zeros(groups, Cout, device="cuda"), ev=torch.ones(groups, Cout, device="cuda"))
+    a, b = buffers(), buffers()
+    try:
+        cuda_lib.dcgan_set_igemm_ksplit(ksplit)
+        K.conv_bn_fwd(x, w, bias, a["pre"], a["out"], a["sums"], gamma, beta, a["saved"], a["em"], a["ev"], groups,
+                      act, transposed, 1e-5, 0.9)
+        (K.conv_tconv_stats if transposed else K.conv_fprop_kn_stats)(x, w, bias, b["pre"], b["sums"], groups)
+    finally:
+        cuda_lib.dcgan_set_igemm_ksplit(0)
+    K.bn_apply(b["pre"].view(-1, Cout), b["out"].view(-1, Cout), b["sums"], gamma, beta, b["saved"], b["em"], b["ev"],
+               groups, act, 1e-5, 0.9)
+    K.check_device_error()
+    # the two paths run the same arithmetic on the same bf16 pre-activations
+    assert torch.equal(a["pre"], b["pre"])
+    for k in ("sums", "saved", "em", "ev"):
+        _close(a[k], b[k], rel=1e-5, name=f"one launch vs two: {k}")
+    assert (a["out"].float() - b["out"].float()).abs().max().item() <= 2e-2
+    # fp32 reference
+    rf = ref.view(groups, -1, Cout)
+    mean, var = rf.mean(1, keepdim=True), rf.var(1, unbiased=False, keepdim=True)
+    y = gamma * (rf - mean) * (var + 1e-5).rsqrt() + beta
+    y = torch.relu(y) if act == "relu" else torch.where(y > 0, y, 0.2 * y)
+    _close(a["out"], y.view(N, oH, oH, Cout), rel=3e-2, name="conv + bn + act vs fp32")
+    _close(a["saved"][:, 0], mean[:, 0], rel=2e-2, name="saved mean")
+    _close(a["em"], 0.1 * mean[:, 0], rel=2e-2, name="ema mean")
+    # the barrier words are zero again (workspace is reusable by the next launch) -- run it twice more
+    for _ in range(2):
+        c = buffers()
+        K.conv_bn_fwd(x, w, bias, c["pre"], c["out"], c["sums"], gamma, beta, c["saved"], c["em"], c["ev"], groups,
+                      act, transposed, 1e-5, 0.9)
+        # (the moments are accumulated with f32 atomics, so repeats may differ in the last bf16 digit)
+        assert (c["out"].float() - a["out"].float()).abs().max().item() <= 2e-2
+    K.check_device_error()
+
+
+@pytest.mark.parametrize("transposed", [True, False])
+def test_dgrad_with_batch_norm_backward_in_its_launch(cuda_lib, transposed):
+    """Data-gradient conv + the whole batch-norm backward pass of the layer below in one launch, against the
+    three-launch path (conv, reduce, apply) and against autograd of fp32 batch norm."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    slabs, groups = (3, 2) if transposed else (1, 1)
+    B = 8
+    N = slabs * B
+    if transposed:
+        H, Cin, Cout, oH, act = 8, 128, 64, 16, "lrelu"
+        x = _rand((N, H, H, Cin), 0.5)
+        w = _rand((25, Cout, Cin), 0.05)
+    else:
+        H, Cin, Cout, oH, act = 16, 64, 128, 8, "relu"
+        x = _rand((N, H, H, Cin), 0.5)
+        w = _rand((25, Cin, Cout), 0.05)
+    pre = _rand((groups * B, oH, oH, Cout))
+    gamma = 1 + 0.1 * torch.randn(Cout, device="cuda")
+    beta = 0.1 * torch.randn(Cout, device="cuda")
+    saved = torch.empty(groups, 2, Cout, device="cuda")
+    pf = pre.float().view(groups, -1, Cout)
+    saved[:, 0] = pf.mean(1)
+    saved[:, 1] = (pf.var(1, unbiased=False) + 1e-5).rsqrt()
+
+    def bufs():
+        return dict(da=torch.empty(N, oH, oH, Cout, device="cuda", dtype=torch.bfloat16),
+                    dpre=torch.empty(N, oH, oH, Cout, device="cuda", dtype=torch.bfloat16),
+                    red=torch.zeros(slabs, 2, Cout, device="cuda"), dg=torch.zeros(Cout, device="cuda"),
+                    db=torch.zeros(Cout, device="cuda"))
+    a, b = bufs(), bufs()
+    K.conv_dgrad_bnbwd(x, w, a["da"], pre, saved, gamma, beta, a["red"], a["dpre"], a["dg"], a["db"], slabs, groups,
+                       groups, act, transposed)
+    K.conv_dgrad_bnred(x, w, b["da"], pre, saved, gamma, beta, b["red"], slabs, groups, act, transposed)
+    K.bn_bwd_apply(b["da"].view(-1, Cout), pre.view(-1, Cout), b["dpre"].view(-1, Cout), saved, gamma, beta, b["red"],
+                   b["dg"], b["db"], slabs, groups, groups, act)
+    K.check_device_error()
+    assert torch.equal(a["da"], b["da"])
+    _close(a["red"], b["red"], rel=1e-4, name="reductions")
+    _close(a["dg"], b["dg"], rel=1e-4, name="dgamma")
+    _close(a["db"], b["db"], rel=1e-4, name="dbeta")
+    assert (a["dpre"].float() - b["dpre"].float()).abs().max().item() <= 1e-2 * b["dpre"].float().abs().max().item()
+    # autograd of fp32 batch norm fed the kernel's own (bf16) upstream gradient, slab by slab
+    for g in range(slabs):
+        sg = min(g, groups - 1)
+        xin = pf[sg].clone().requires_grad_(True)
+        mean, var = xin.mean(0), xin.var(0, unbiased=False)
+        y = gamma * (xin - mean) * (var + 1e-5).rsqrt() + beta
+        out = torch.relu(y) if act == "relu" else torch.where(y > 0, y, 0.2 * y)
+        (gx,) = torch.autograd.grad(out, xin, a["da"][g * B:(g + 1) * B].float().reshape(-1, Cout))
+        _close(a["dpre"][g * B:(g + 1) * B].reshape(-1, Cout), gx, rel=3e-2, name=f"dpre slab {g} vs autograd")
+
+
+def test_one_launch_batch_norm_kernels(cuda_lib):
+    """bn_forward_fused / bn_backward_fused (statistics, grid barrier, elementwise pass) against the two-launch
+    kernels, for the shapes of g_bn0 / d_bn3 (512 channels, few rows) and g_bn3 (64 channels, many rows)."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    barrier = torch.zeros(2, dtype=torch.int32, device="cuda")
+    for rows, C, groups, slabs, act in ((1024, 512, 1, 1, "relu"), (1024, 512, 2, 3, "lrelu"), (65536, 64, 1, 1, "relu")):
+        x = _rand((groups * rows, C))
+        gamma = 1 + 0.1 * torch.randn(C, device="cuda")
+        beta = 0.1 * torch.randn(C, device="cuda")
+        outs = []
+        for fused in (True, False):
+            y = torch.empty_like(x)
+            sums, saved = torch.zeros(groups, 2, C, device="cuda"), torch.zeros(groups, 2, C, device="cuda")
+            em, ev = torch.zeros(groups, C, device="cuda"), torch.ones(groups, C, device="cuda")
+            if fused:
+                K.bn_forward_fused(x, y, sums, gamma, beta, saved, em, ev, barrier, groups, act, 1e-5, 0.9)
+            else:
+                K.bn_stats(x, sums, groups)
+                K.bn_apply(x, y, sums, gamma, beta, saved, em, ev, groups, act, 1e-5, 0.9)
+            outs.append((y, sums, saved, em, ev))
+        for u, v in zip(outs[0][1:], outs[1][1:]):
+            _close(u, v, rel=1e-5, name="forward statistics")
+        assert (outs[0][0].float() - outs[1][0].float()).abs().max().item() <= 2e-2
+        saved = outs[1][2]
+        da = _rand((slabs * rows, C))
+        res = []
+        for fused in (True, False):
+            dpre = torch.empty_like(da)
+            red = torch.zeros(slabs, 2, C, device="cuda")
+            dg, db = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+            if fused:
+                K.bn_backward_fused(da, x, dpre, saved, gamma, beta, red, dg, db, barrier, slabs, groups, groups, act)
+            else:
+                K.bn_bwd_reduce(da, x, saved, gamma, beta, red, slabs, groups, act)
+                K.bn_bwd_apply(da, x, dpre, saved, gamma, beta, red, dg, db, slabs, groups, groups, act)
+            res.append((dpre, red, dg, db))
+        for u, v in zip(res[0][1:], res[1][1:]):
+            _close(u, v, rel=1e-4, name="backward reductions")
+        assert (res[0][0].float() - res[1][0].float()).abs().max().item() <= 1e-2 * res[1][0].float().abs().max().item()
+    assert barrier.tolist() == [0, 0]
+    K.check_device_error()
