@@ -33,7 +33,7 @@ lin_fwd_kernel(const float* __restrict__ z, const __nv_bfloat16* __restrict__ W,
   const float b0 = bias ? bias[j] : 0.f, b1 = bias ? bias[j + 1] : 0.f;
 #pragma unroll
   for (int i = 0; i < kLinTile; ++i) { acc[i][0] = b0; acc[i][1] = b1; }
-  constexpr int kBatch = 10;  // weight loads in flight per thread
+  constexpr int kBatch = 25;  // weight loads in flight per thread (the kernel is latency-bound: few, long threads)
   for (int k0 = 0; k0 < K; k0 += kBatch) {
     uint32_t wv[kBatch];
 #pragma unroll
@@ -81,7 +81,7 @@ lin_wgrad_kernel(const float* __restrict__ z, const __nv_bfloat16* __restrict__ 
 #pragma unroll
   for (int i = 0; i < kt; ++i) acc[i] = 0.f;
   float bsum = 0.f;
-  constexpr int kBatch = 8;  // gradient loads in flight per thread
+  constexpr int kBatch = 32;  // gradient loads in flight per thread
   for (int nb = 0; nb < NB; nb += kBatch) {
     __nv_bfloat16 dv[kBatch];
 #pragma unroll

@@ -108,6 +108,9 @@ void igemm2_set_debug(long long* ptr);
 void igemm2_set_max_ctas(int v);
 void igemm2_set_ksplit(int v);
 void igemm2_set_tile(int v);
+// measured plan of one layer shape (kind: MODE_F / MODE_T / MODE_W; W: H, W = the small grid, Cin = Cg, Cout = Cd);
+// block_n <= 0 forgets it
+int igemm2_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit);
 void igemm2_set_stage_mode(int v);
 int igemm2_set_workspace(void* ptr, size_t bytes);
 

@@ -880,6 +880,42 @@ void igemm2_plan(long tiles_bn64, double kb_per_tile, int Cn, int min_kb, int fo
   }
 }
 
+// Measured plans (dcgan_igemm_plan_set: the Python autotuner times the candidates of a layer shape once and records
+// the winner).  Consulted when the caller leaves tile width and split factor to the library and no global override
+// (dcgan_set_igemm_tile / _ksplit) is active.
+static std::mutex g_plan_mu;
+static std::unordered_map<uint64_t, std::pair<int, int>> g_plan_table;
+static bool plan_key(int kind, int NB, int H, int W, int Cin, int Cout, uint64_t* key) {
+  if (kind < 0 || kind > 2 || NB < 1 || NB >= (1 << 14) || H < 1 || H >= (1 << 10) || W < 1 || W >= (1 << 10) ||
+      Cin < 1 || Cin >= (1 << 13) || Cout < 1 || Cout >= (1 << 13))
+    return false;
+  *key = (uint64_t)kind | ((uint64_t)NB << 2) | ((uint64_t)H << 16) | ((uint64_t)W << 26) | ((uint64_t)Cin << 36) |
+         ((uint64_t)Cout << 49);
+  return true;
+}
+int igemm2_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit) {
+  uint64_t key;
+  if (!plan_key(kind, NB, H, W, Cin, Cout, &key)) return DCGAN_ERR_SHAPE;
+  std::lock_guard<std::mutex> lock(g_plan_mu);
+  if (block_n <= 0) {
+    g_plan_table.erase(key);
+    return 0;
+  }
+  if ((block_n != 64 && block_n != 128 && block_n != 256) || ksplit < 1 || ksplit > 16) return DCGAN_ERR_SHAPE;
+  g_plan_table[key] = std::make_pair(block_n, ksplit);
+  return 0;
+}
+static bool plan_lookup(int kind, int NB, int H, int W, int Cin, int Cout, int* block_n, int* ksplit) {
+  uint64_t key;
+  if (g_force_ksplit2 > 0 || g_pref_bn > 0 || !plan_key(kind, NB, H, W, Cin, Cout, &key)) return false;
+  std::lock_guard<std::mutex> lock(g_plan_mu);
+  auto it = g_plan_table.find(key);
+  if (it == g_plan_table.end()) return false;
+  *block_n = it->second.first;
+  *ksplit = it->second.second;
+  return true;
+}
+
 static int ilog2_exact(int v) {
   int l = 0;
   while ((1 << l) < v) ++l;
@@ -966,7 +1002,14 @@ int igemm2_conv(int transposed, const void* x, const void* w, const float* bias,
   const double avg_kb = transposed ? 6.25 * cpt : 25.0 * cpt;
   p.num_kb = transposed ? 0 : 25 * cpt;
   int ks;
-  igemm2_plan((long)mt * (Cout / 64) * classes, avg_kb, Cout, min_kb, block_n > 0 ? block_n : 0, &block_n, &ks);
+  int tuned_bn, tuned_ks;
+  if (block_n <= 0 && plan_lookup(transposed ? MODE_T : MODE_F, NB, H, W, Cin, Cout, &tuned_bn, &tuned_ks) &&
+      Cout % tuned_bn == 0 && tuned_ks <= min_kb) {
+    block_n = tuned_bn;
+    ks = tuned_ks;
+  } else {
+    igemm2_plan((long)mt * (Cout / 64) * classes, avg_kb, Cout, min_kb, block_n > 0 ? block_n : 0, &block_n, &ks);
+  }
   if (block_n <= 0 || Cout % block_n) return DCGAN_ERR_SHAPE;
   p.ksplit = ks;
   p.m_tiles = mt;
@@ -1010,8 +1053,15 @@ int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, 
     if (Cg % block_n) return DCGAN_ERR_SHAPE;
     ks = splits < total_kb ? splits : total_kb;
   } else {
-    igemm2_plan((long)25 * (Cd / kBlockM) * (Cg / 64), (double)total_kb, Cg, total_kb, block_n > 0 ? block_n : 0,
-                &block_n, &ks);
+    int tuned_bn, tuned_ks;
+    if (block_n <= 0 && plan_lookup(MODE_W, NB, Hs, Ws, Cg, Cd, &tuned_bn, &tuned_ks) && Cg % tuned_bn == 0 &&
+        tuned_ks <= total_kb) {
+      block_n = tuned_bn;
+      ks = tuned_ks;
+    } else {
+      igemm2_plan((long)25 * (Cd / kBlockM) * (Cg / 64), (double)total_kb, Cg, total_kb, block_n > 0 ? block_n : 0,
+                  &block_n, &ks);
+    }
   }
   if (block_n <= 0 || Cg % block_n) return DCGAN_ERR_SHAPE;
   p.ksplit = ks;

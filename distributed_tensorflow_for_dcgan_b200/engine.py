@@ -53,7 +53,10 @@ class ParamArena:
             for part in (True, False):
                 if not part:
                     self.f32_start[key] = off
-                for s in specs:
+                # g_h0_lin/Matrix goes last among the generator's big filters: its gradient is the last one of the
+                # step, so [g_h1/w .. g_h3/w] can be updated early (engine: generator_backward) and the final
+                # optimizer launch covers one contiguous range [g_h0_lin/Matrix, g_end)
+                for s in sorted(specs, key=lambda t: t.name == "g_h0_lin/Matrix"):
                     if self.reads_bf16(s.name) == part:
                         self.offsets[s.name] = (off, s.shape)
                         off += (s.numel + 7) // 8 * 8  # every tensor 32-byte aligned (vector loads, TMA)
@@ -207,6 +210,7 @@ class DCGANEngine:
         if (int(os.environ.get("DCGAN_IGEMM_TUNING", "1")) & 128) != 0:
             self.fuse_bn &= ~3
         self._grid_barrier = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.early_adam = os.environ.get("DCGAN_EARLY_ADAM", "1") != "0"
         self.prioritize_main = os.environ.get("DCGAN_MAIN_PRIORITY", "1") != "0"
         self.split_d_forward = self.wgrad_overlap and os.environ.get("DCGAN_SPLIT_D_FORWARD", "0") != "0"
         self.side = torch.cuda.Stream(self.device)
@@ -463,8 +467,12 @@ class DCGANEngine:
                    colsum=g["g_h4/biases"],  # g_h4's bias gradient falls out of the same pass, in f32
                    w_bf16=self.w_native["d_h0_conv/w"])
 
-    def generator_backward(self) -> None:
+    def generator_backward(self, early_adam: bool = False) -> Optional[int]:
+        """``early_adam``: the Adam update of g_h1/w .. g_h3/w (85 % of the generator's parameters) is issued on the
+        side stream as soon as the last of their gradients is done and nothing reads those filters any more, under
+        the tail of the backward pass; returns the arena offset where the remaining (final) update starts."""
         p, g, B = self.params, self.grad_views, self.B
+        adam_from = None
         with self._off_critical_path():
             K.c3_wgrad(self.dimg, self.g_act[3], g["g_h4/w"])
         K.c3_fprop(self.dimg, p["g_h4/w"], None, out=self.dg_act[3])
@@ -481,8 +489,18 @@ class DCGANEngine:
                                              self.g_pre[i - 1], False, dpre=self.dg_pre[i - 1])
             else:
                 K.conv_fprop_kn(self.dg_pre[i], w, None, out=self.dg_act[i - 1])
+        if early_adam and self.wgrad_overlap:
+            A = self.arena
+            lo, hi = A.offsets["g_h1/w"][0], A.offsets["g_h0_lin/Matrix"][0]
+            if 0 <= lo < hi:
+                # ordered after g_h1's data gradient (the last reader of these filters) and, on the side stream,
+                # after the three filter gradients
+                with self._off_critical_path():
+                    self._adam_range(lo, hi)
+                adam_from = hi
         self._bn_bwd("g_bn0", self.dg_act[0], self.g_pre[0], self.dg_pre[0], reduce_done=red_done)
         K.lin_wgrad(self.z, self.dg_pre[0].view(B, -1), g["g_h0_lin/Matrix"], g["g_h0_lin/bias"])
+        return adam_from
 
     # ------------------------------------------------------------------------------------------------
     # optimizer
@@ -559,9 +577,9 @@ class DCGANEngine:
                 A = self.arena
                 with self._off_critical_path():
                     self._adam_range(A.g_end, A.padded)
-                self.generator_backward()
+                adam_from = self.generator_backward(early_adam=self.early_adam)
                 self._join_side()
-                self._adam_range(0, A.g_end)
+                self._adam_range(adam_from or 0, A.g_end)
             else:
                 self.generator_backward()
                 self.optimizer_step("both")

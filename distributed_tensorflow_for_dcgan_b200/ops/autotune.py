@@ -1,0 +1,125 @@
+"""Measured launch plans for the implicit-GEMM conv kernels (csrc/igemm2_sm100.cu).
+
+The layers of this model are small GEMMs (a few GFLOP each): whether a 64-, 128- or 256-column tile and which
+split-K factor is fastest depends on how the tile count falls on the 148 SMs, and the analytic cost model in the
+library misses by up to 40 % on some layers (profiles/igemm2_sweep_r2.log).  The first time a layer shape is
+launched with the choice left to the library, this module times every candidate on scratch tensors of that shape
+(CUDA events, warm-up first, the launching stream) and records the winner with ``dcgan_igemm_plan_set``; later
+launches of the shape -- including the ones captured into the CUDA graph -- use it.
+
+The reference has no counterpart (TensorFlow picks cuDNN algorithms through its own autotuner, which is what
+``tf.nn.conv2d`` / ``conv2d_transpose`` in distriubted_model.py:55-88 go through).
+
+``DCGAN_AUTOTUNE=0`` turns it off (plans then come from the cost model and are identical from run to run).
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, Tuple
+
+import torch
+
+from . import _lib
+
+KIND_F, KIND_T, KIND_W = 0, 1, 2
+enabled = os.environ.get("DCGAN_AUTOTUNE", "1") != "0"
+verbose = os.environ.get("DCGAN_AUTOTUNE_VERBOSE", "0") != "0"
+_done: Dict[Tuple[int, int, int, int, int, int], Tuple[int, int, float]] = {}
+_busy = False
+
+
+def plans() -> Dict[Tuple[int, int, int, int, int, int], Tuple[int, int, float]]:
+    """(kind, N, H, W, Cin, Cout) -> (block_n, ksplit, microseconds) of every shape tuned so far."""
+    return dict(_done)
+
+
+def _time_us(fn, reps: int = 6) -> float:
+    for _ in range(2):
+        fn()
+    best = float("inf")
+    for _ in range(2):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(reps):
+            fn()
+        e.record()
+        e.synchronize()
+        best = min(best, s.elapsed_time(e) * 1e3 / reps)
+    return best
+
+
+def ensure(kind: int, N: int, H: int, W: int, Cin: int, Cout: int) -> None:
+    """Tune the shape if it has not been tuned in this process.  conv kinds: input [N,H,W,Cin] -> Cout channels;
+    KIND_W: small grid [N,H,W,Cout=Cd], big grid [N,2H,2W,Cin=Cg]."""
+    global _busy
+    key = (kind, N, H, W, Cin, Cout)
+    if not enabled or _busy or key in _done or not torch.cuda.is_available():
+        return
+    if torch.cuda.is_current_stream_capturing():
+        return
+    lib = _lib.load()
+    if not hasattr(lib, "dcgan_igemm_plan_set"):
+        return
+    # a global override is active (A/B runs, tests): the table would not be consulted, and tuning must not disturb it
+    if (lib.dcgan_get_igemm_ksplit() != 0 or os.environ.get("DCGAN_IGEMM_TILE")
+            or (int(os.environ.get("DCGAN_IGEMM_TUNING", "1")) & 128)):
+        return
+    _busy = True
+    try:
+        best = _tune(lib, kind, N, H, W, Cin, Cout)
+    finally:
+        lib.dcgan_set_igemm_ksplit(0)
+        _busy = False
+    _done[key] = best
+    if best[0] > 0:
+        lib.dcgan_igemm_plan_set(kind, N, H, W, Cin, Cout, best[0], best[1])
+    if verbose:
+        print(f"[autotune] kind {kind} N {N} HxW {H}x{W} Cin {Cin} Cout {Cout}: block_n {best[0]} ksplit {best[1]} "
+              f"{best[2]:.1f} us", flush=True)
+
+
+def _tune(lib, kind, N, H, W, Cin, Cout):
+    dev = torch.cuda.current_device()
+    bf = dict(device=f"cuda:{dev}", dtype=torch.bfloat16)
+    g = torch.Generator(device=f"cuda:{dev}").manual_seed(1)
+    rnd = lambda *shape: (torch.rand(*shape, generator=g, device=f"cuda:{dev}") - 0.5).to(torch.bfloat16)
+    if Cin % 64 or Cout % 64:
+        return (0, 0, 0.0)
+    if kind == KIND_W:
+        if Cout % 128 or (N * H * W) % 64:
+            return (0, 0, 0.0)
+        big, small = rnd(N, 2 * H, 2 * W, Cin), rnd(N, H, W, Cout)
+        dw = torch.zeros(25, Cin, Cout, device=f"cuda:{dev}")
+        total_kb = N * H * W // 64
+        cands = [(bn, ks) for bn in (64, 128, 256) if Cin % bn == 0 for ks in (1, 2, 3, 4, 6, 8, 12, 16)
+                 if ks <= total_kb]
+
+        def run(bn, ks):
+            _lib.call("dcgan_conv_wgrad", big.data_ptr(), small.data_ptr(), dw.data_ptr(), N, H, W, Cin, Cout, ks, bn)
+    else:
+        x = rnd(N, H, W, Cin)
+        transposed = kind == KIND_T
+        oH, oW = (2 * H, 2 * W) if transposed else (H // 2, W // 2)
+        w = rnd(25, Cout, Cin) if transposed else rnd(25, Cin, Cout)
+        out = torch.empty(N, oH, oW, Cout, **bf)
+        min_kb = (4 if transposed else 25) * (Cin // 64)
+        cands = [(bn, ks) for bn in (64, 128, 256) if Cout % bn == 0 for ks in (1, 2, 3, 4, 6, 8) if ks <= min_kb]
+        entry = "dcgan_conv_tconv" if transposed else "dcgan_conv_fprop_kn"
+
+        def run(bn, ks):
+            lib.dcgan_set_igemm_ksplit(ks)
+            _lib.call(entry, x.data_ptr(), w.data_ptr(), None, out.data_ptr(), N, H, W, Cin, Cout, 0, bn)
+    before = _lib.launch_count
+    best = (0, 0, float("inf"))
+    try:
+        for bn, ks in cands:
+            try:
+                t = _time_us(lambda: run(bn, ks))
+            except _lib.KernelError:
+                continue
+            if t < best[2] * 0.985:  # a later candidate has to win by more than the timer's noise
+                best = (bn, ks, t)
+    finally:
+        _lib.launch_count = before  # tuning launches are not part of anybody's step
+    torch.cuda.synchronize()
+    return best if best[0] > 0 else (0, 0, 0.0)

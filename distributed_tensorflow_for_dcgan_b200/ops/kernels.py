@@ -9,7 +9,7 @@ from typing import Optional
 
 import torch
 
-from . import _lib
+from . import _lib, autotune
 from ._lib import call, ptr
 
 ACT = {"none": 0, "relu": 1, "lrelu": 2, "tanh": 3, "sigmoid": 4}
@@ -23,6 +23,8 @@ def conv_fprop(x, w_nk, bias=None, act="none", out=None, block_n=0):
     """5x5 s2 SAME conv.  x [N,H,W,Cin] bf16, w_nk [25,Cout,Cin] bf16 -> [N,H/2,W/2,Cout] bf16."""
     N, H, W, Cin = x.shape
     Cout = w_nk.shape[1]
+    if block_n == 0:
+        autotune.ensure(autotune.KIND_F, N, H, W, Cin, Cout)
     if out is None:
         out = _bf16((N, H // 2, W // 2, Cout), x)
     call("dcgan_conv_fprop", ptr(x), ptr(w_nk), ptr(bias), ptr(out), N, H, W, Cin, Cout, ACT[act], block_n)
@@ -33,6 +35,8 @@ def conv_fprop_kn(x, w_kn, bias=None, act="none", out=None, block_n=0):
     """5x5 s2 SAME conv with the filter in TF layout: w_kn [25,Cin,Cout] bf16 (no transposed copy)."""
     N, H, W, Cin = x.shape
     Cout = w_kn.shape[2]
+    if block_n == 0:
+        autotune.ensure(autotune.KIND_F, N, H, W, Cin, Cout)
     if out is None:
         out = _bf16((N, H // 2, W // 2, Cout), x)
     call("dcgan_conv_fprop_kn", ptr(x), ptr(w_kn), ptr(bias), ptr(out), N, H, W, Cin, Cout, ACT[act], block_n)
@@ -43,6 +47,8 @@ def conv_tconv(x, w_nk, bias=None, act="none", out=None, block_n=0):
     """5x5 s2 transposed conv (TF crop).  x [N,H,W,Cin], w_nk [25,Cout,Cin] -> [N,2H,2W,Cout]."""
     N, H, W, Cin = x.shape
     Cout = w_nk.shape[1]
+    if block_n == 0:
+        autotune.ensure(autotune.KIND_T, N, H, W, Cin, Cout)
     if out is None:
         out = _bf16((N, 2 * H, 2 * W, Cout), x)
     call("dcgan_conv_tconv", ptr(x), ptr(w_nk), ptr(bias), ptr(out), N, H, W, Cin, Cout, ACT[act], block_n)
@@ -52,6 +58,8 @@ def conv_tconv(x, w_nk, bias=None, act="none", out=None, block_n=0):
 def conv_fprop_kn_stats(x, w_kn, bias, out, stats, groups, block_n=0):
     """conv_fprop_kn + batch-norm moments of the output accumulated into stats [groups,2,Cout]."""
     N, H, W, Cin = x.shape
+    if block_n == 0:
+        autotune.ensure(autotune.KIND_F, N, H, W, Cin, w_kn.shape[2])
     call("dcgan_conv_fprop_kn_stats", ptr(x), ptr(w_kn), ptr(bias), ptr(out), ptr(stats), groups, N, H, W, Cin,
          w_kn.shape[2], block_n)
     return out
@@ -59,6 +67,8 @@ def conv_fprop_kn_stats(x, w_kn, bias, out, stats, groups, block_n=0):
 
 def conv_tconv_stats(x, w_nk, bias, out, stats, groups, block_n=0):
     N, H, W, Cin = x.shape
+    if block_n == 0:
+        autotune.ensure(autotune.KIND_T, N, H, W, Cin, w_nk.shape[1])
     call("dcgan_conv_tconv_stats", ptr(x), ptr(w_nk), ptr(bias), ptr(out), ptr(stats), groups, N, H, W, Cin,
          w_nk.shape[1], block_n)
     return out
@@ -69,6 +79,8 @@ def conv_dgrad_bnred(x, w, out, pre, saved, gamma, beta, red, slabs, stat_groups
     the batch-norm backward reductions ``red [slabs,2,Cout]`` of the layer that ``out`` is the activation gradient
     of (``pre`` / ``saved`` / ``gamma`` / ``beta`` are that layer's)."""
     N, H, W, Cin = x.shape
+    if block_n == 0:
+        autotune.ensure(autotune.KIND_T if transposed else autotune.KIND_F, N, H, W, Cin, w.shape[1] if transposed else w.shape[2])
     Cout = w.shape[1] if transposed else w.shape[2]
     call("dcgan_conv_tconv_bnred" if transposed else "dcgan_conv_fprop_kn_bnred", ptr(x), ptr(w), ptr(out), ptr(pre),
          ptr(saved), ptr(gamma), ptr(beta), ptr(red), slabs, stat_groups, ACT[act], N, H, W, Cin, Cout, block_n)
@@ -81,6 +93,8 @@ def conv_dgrad_bnbwd(x, w, out, pre, saved, gamma, beta, red, dpre, dgamma, dbet
     grid-wide barrier the kernel turns ``out`` (= da) into ``dpre`` and writes ``dgamma`` / ``dbeta``.  Kernels of
     this family (this, ``conv_bn_fwd``, ``bn_forward_fused``, ``bn_backward_fused``) go on ONE stream per device."""
     N, H, W, Cin = x.shape
+    if block_n == 0:
+        autotune.ensure(autotune.KIND_T if transposed else autotune.KIND_F, N, H, W, Cin, w.shape[1] if transposed else w.shape[2])
     Cout = w.shape[1] if transposed else w.shape[2]
     call("dcgan_conv_tconv_bnbwd" if transposed else "dcgan_conv_fprop_kn_bnbwd", ptr(x), ptr(w), ptr(out), ptr(pre),
          ptr(saved), ptr(gamma), ptr(beta), ptr(red), ptr(dpre), ptr(dgamma), ptr(dbeta), slabs, stat_groups,
@@ -94,6 +108,8 @@ def conv_bn_fwd(x, w, bias, pre, act_out, sums, gamma, beta, saved, ema_mean, em
     in one launch: ``pre`` (bf16 conv output, kept for backward), ``sums`` [groups,2,Cout] (+=), then
     ``act_out = act(bn(pre))``, ``saved`` = (mean, rstd) and the EMA shadows."""
     N, H, W, Cin = x.shape
+    if block_n == 0:
+        autotune.ensure(autotune.KIND_T if transposed else autotune.KIND_F, N, H, W, Cin, w.shape[1] if transposed else w.shape[2])
     Cout = w.shape[1] if transposed else w.shape[2]
     call("dcgan_conv_tconv_bn" if transposed else "dcgan_conv_fprop_kn_bn", ptr(x), ptr(w), ptr(bias), ptr(pre),
          ptr(act_out), ptr(sums), ptr(gamma), ptr(beta), ptr(saved), ptr(ema_mean), ptr(ema_var), groups, N, H, W,
@@ -105,6 +121,8 @@ def conv_wgrad(big, small, dw, splits=0, block_n=0):
     """dw[25,Cg,Cd] (f32, +=) from big [N,2Hs,2Ws,Cg] and small [N,Hs,Ws,Cd]."""
     N, Hs, Ws, Cd = small.shape
     Cg = big.shape[3]
+    if block_n == 0 and splits == 0:
+        autotune.ensure(autotune.KIND_W, N, Hs, Ws, Cg, Cd)
     call("dcgan_conv_wgrad", ptr(big), ptr(small), ptr(dw), N, Hs, Ws, Cg, Cd, splits, block_n)
     return dw
 

@@ -57,6 +57,12 @@ void dcgan_set_igemm_max_ctas(int v);
 void dcgan_set_igemm_stage_mode(int v);
 /* Tile width (64 / 128 / 256 output channels) used wherever it divides the layer; 0 = the library's choice. */
 void dcgan_set_igemm_tile(int v);
+/* Records the measured-best (tile width, split-K factor) of one layer shape; later calls of that shape which leave
+ * both to the library (block_n = 0, splits = 0) use it instead of the cost model.  kind: 0 strided conv (fprop*),
+ * 1 transposed conv (tconv*), 2 filter gradient (there H, W = the small grid, Cin = Cg, Cout = Cd).  block_n <= 0
+ * forgets the entry.  ops/autotune.py fills the table by timing the candidates once per shape. */
+int dcgan_get_igemm_ksplit(void); /* the factor forced by dcgan_set_igemm_ksplit, 0 = none */
+int dcgan_igemm_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit);
 /* Bring-up only: per-CTA cycle counters [CTA][16] written by a library built with -DIGEMM2_TIMING (else ignored). */
 void dcgan_set_igemm_debug(long long* counters);
 /* Split-K scratch of the second-generation kernels for the calling host thread: `bytes` of device memory whose
