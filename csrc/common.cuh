@@ -60,6 +60,13 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// 1024-byte aligned start of the dynamic shared memory (SWIZZLE_128B atoms).  Pointer arithmetic on the __shared__
+// array itself -- a round trip through uintptr_t makes the compiler lose the address space, and every shared-memory
+// access of the kernel becomes a generic LD / ST with 64-bit address math instead of LDS / STS.
+__device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* raw) {
+  return raw + ((1024u - (smem_u32(raw) & 1023u)) & 1023u);
+}
+
 // ---------------------------------------------------------------------------------------------
 // mbarrier
 // ---------------------------------------------------------------------------------------------

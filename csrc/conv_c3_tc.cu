@@ -13,6 +13,7 @@
 //
 // Both then run at memory speed.  Filter layout is the shared [25][3][C] of csrc/conv_c3.cu.
 #include "common.cuh"
+#include "igemm2.h"
 #include "../include/dcgan_b200.h"
 
 namespace dcgan {
@@ -135,7 +136,7 @@ c3_fprop_tc_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict_
                    __nv_bfloat16* __restrict__ out, int N, int H, int W, int C, int act, int* err_flag) {
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   uint8_t* a_tiles = smem;                       // 2 x [128][128 B]
   uint8_t* b_tiles = smem + 32768;               // 2 x [64][128 B]
   __nv_bfloat16* patch = reinterpret_cast<__nv_bfloat16*>(smem + 32768 + 16384);
@@ -233,13 +234,17 @@ c3_fprop_tc_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict_
       tmem_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16) + c, v);
       tmem_ld_wait();
       if (ok) {
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 b = *reinterpret_cast<const float4*>(bias_s + c + j);
+          f[j] = __uint_as_float(v[j]) + b.x; f[j + 1] = __uint_as_float(v[j + 1]) + b.y;
+          f[j + 2] = __uint_as_float(v[j + 2]) + b.z; f[j + 3] = __uint_as_float(v[j + 3]) + b.w;
+        }
+        apply_act_chunk(f, act);  // kind selected once per chunk (a per-element switch multiplies the code size)
         uint32_t packed[16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float a = __uint_as_float(v[2 * j]) + bias_s[c + 2 * j];
-          const float b = __uint_as_float(v[2 * j + 1]) + bias_s[c + 2 * j + 1];
-          packed[j] = pack_bf16x2(apply_act(a, act), apply_act(b, act));
-        }
+        for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
         uint4* dst = reinterpret_cast<uint4*>(orow + c);
 #pragma unroll
         for (int j = 0; j < 4; ++j)
@@ -257,10 +262,10 @@ c3_fprop_tc_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict_
 // ---------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kTcThreads)
 c3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ x3, const __nv_bfloat16* __restrict__ y, float* __restrict__ dw,
-                   int N, int Hs, int Ws, int C, int* err_flag) {
+                   float* __restrict__ partial, int N, int Hs, int Ws, int C, int* err_flag) {
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   uint8_t* a_tiles = smem;                       // 2 x [128 px][128 B]  (MN-major A: M = k index)
   uint8_t* b_tile = smem + 32768;                // [128 px][128 B]      (MN-major B: N = 64 channels)
   __nv_bfloat16* patch = reinterpret_cast<__nv_bfloat16*>(smem + 32768 + 16384);
@@ -332,14 +337,27 @@ c3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ x3, const __nv_bfloat16* __
   // epilogue: TMEM lane m = padded k index kh*16 + kk; rows with kk == 15 or m >= 80 are padding
   const int m = t;
   const int kh = m >> 4, kk = m & 15;
-  const bool real = any && ok && m < 80 && kk < 15;
+  const bool real = m < 80 && kk < 15;
   float* orow = dw + (size_t)(kh * 15 + kk) * C + c0;
+  // with `partial`: this CTA's [75][64] tile goes to scratch (plain stores, zero if it had no tile) and
+  // c3_wgrad_reduce_kernel adds the tiles up in a fixed order -- no atomics, reproducible
+  float* prow = partial != nullptr
+                    ? partial + ((size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 75 + (kh * 15 + kk)) * 64
+                    : nullptr;
 #pragma unroll
   for (int c = 0; c < 64; c += 32) {
     uint32_t v[32];
     tmem_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16) + c, v);
     tmem_ld_wait();
-    if (real) {
+    if (real && prow != nullptr) {
+      const bool have = any && ok;
+#pragma unroll
+      for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4*>(prow + c + j) =
+            have ? make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                               __uint_as_float(v[j + 3]))
+                 : make_float4(0.f, 0.f, 0.f, 0.f);
+    } else if (real && any && ok) {
 #pragma unroll
       for (int j = 0; j < 32; ++j) atomicAdd(orow + c + j, __uint_as_float(v[j]));
     }
@@ -349,6 +367,38 @@ c3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ x3, const __nv_bfloat16* __
   if (warp == 0) tmem_dealloc(tmem_base, 64);
 }
 
+
+// dw[row][c0 + col] += sum over the CTAs' partial tiles, in CTA order.  One warp = 32 consecutive outputs; the 8
+// warps of a CTA take the partials b = warp, warp + 8, ... and are combined through shared memory in warp order.
+// grid = (75 * 64 / 32, C / 64), 256 threads.
+__global__ void __launch_bounds__(256)
+c3_wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int nparts, int C) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float acc_s[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int o = blockIdx.x * 32 + lane;  // element of the [75][64] tile
+  const float* src = partial + (size_t)blockIdx.y * nparts * 4800 + o;
+  float acc = 0.f;
+  int b = warp;
+  for (; b + 56 < nparts; b += 64) {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = __ldcg(src + (size_t)(b + 8 * u) * 4800);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) acc += v[u];
+  }
+  for (; b < nparts; b += 8) acc += __ldcg(src + (size_t)b * 4800);
+  acc_s[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += acc_s[w][lane];
+    const int row = o >> 6, col = o & 63;
+    dw[(size_t)row * C + blockIdx.y * 64 + col] += t;
+  }
+}
 
 // ---------------------------------------------------------------------------------------------------------
 // C -> 3 transposed conv on tensor cores (g_h4 forward, distriubted_model.py:109; d_h0 data gradient).
@@ -371,7 +421,7 @@ c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
                    int mode, int* err_flag) {
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   uint8_t* a_tiles = smem;                       // 2 x [128 rows][128 B]: halo rows 0..179 (+ zero rows)
   uint8_t* b_tile = smem + 32768;                // [80 rows (tap*3+co)][128 B]
   float* ysm = reinterpret_cast<float*>(smem + 32768 + 16384);
@@ -591,11 +641,22 @@ int dcgan_c3_wgrad_tc(const void* x3, const void* y, float* dw, int N, int Hs, i
   // runs on the side stream beside the data-gradient chain.  In-step sweeps (profiles/README.md): without stream
   // priorities 444 CTAs 0.931 ms/step, 148 0.874, 64 0.820, 24 0.921; with the chain captured at high priority
   // (engine default) 444 0.895, 296 0.849, 222 0.834, 148 0.811-0.813, 64 0.821.
-  const int cap_w = g_c3_blocks_wgrad > 0 ? g_c3_blocks_wgrad : 148;
+  // (those sweeps predate the partial-tile path below, which has no atomics: more CTAs now only cost scratch)
+  const int cap_w = g_c3_blocks_wgrad > 0 ? g_c3_blocks_wgrad : 296;
   dim3 grid(tiles < cap_w ? tiles : cap_w, C / 64);
+  void* scratch = nullptr;
+  size_t scratch_bytes = 0;
+  const size_t need = (size_t)grid.x * grid.y * 4800 * sizeof(float);
+  float* partial = nullptr;
+  if (igemm2_scratch(&scratch, &scratch_bytes) == 0 && scratch_bytes >= need) partial = reinterpret_cast<float*>(scratch);
   launch_k(c3_wgrad_tc_kernel, dim3(grid), dim3(kTcThreads), kTcSmem, st, reinterpret_cast<const __nv_bfloat16*>(x3),
-                                                        reinterpret_cast<const __nv_bfloat16*>(y), dw, N, Hs, Ws, C, err);
-  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+           reinterpret_cast<const __nv_bfloat16*>(y), dw, partial, N, Hs, Ws, C, err);
+  if (cudaGetLastError() != cudaSuccess) return DCGAN_ERR_LAUNCH;
+  if (partial != nullptr) {
+    launch_k(c3_wgrad_reduce_kernel, dim3(4800 / 32, C / 64), dim3(256), 0, st, (const float*)partial, dw, (int)grid.x, C);
+    if (cudaGetLastError() != cudaSuccess) return DCGAN_ERR_LAUNCH;
+  }
+  return 0;
 }
 
 }  // extern "C"

@@ -101,6 +101,8 @@ int igemm2_tmap_2d(const void* ptr, unsigned long long rows, unsigned long long 
 bool igemm2_pixel_box(int rows, int rH, int rW, int* bw, int* bh, int* bn);
 int igemm2_attach_scratch(Igemm2Params* p, long tiles, int cols_per_tile);
 int igemm2_num_sms();
+// scratch area (beyond the counters) of the calling thread's workspace; kernels on one stream may share it
+int igemm2_scratch(void** ptr, size_t* bytes);
 int igemm2_max_ctas();
 int igemm2_forced_ksplit();
 

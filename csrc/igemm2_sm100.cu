@@ -142,7 +142,7 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
 #endif
   using L = Smem2<BLOCK_N, STAGES>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
@@ -811,6 +811,14 @@ int dispatch2(int block_n, const CUtensorMap& tg, const CUtensorMap& td, const I
 
 }  // namespace
 
+int igemm2_scratch(void** ptr, size_t* bytes) {  // the partial-tile area of the calling thread's workspace
+  Workspace ws;
+  int rc = get_workspace(&ws);
+  if (rc) return rc;
+  *ptr = reinterpret_cast<uint8_t*>(ws.ptr) + kCounterBytes;
+  *bytes = ws.bytes - kCounterBytes;
+  return 0;
+}
 int igemm2_num_sms() { return num_sms(); }
 int igemm2_max_ctas() { return g_max_ctas; }
 int igemm2_forced_ksplit() { return g_force_ksplit2; }

@@ -132,7 +132,7 @@ igemm_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
   using L = SmemLayout<BLOCK_N, STAGES>;
   constexpr int kGatherDepth = (STAGES >= 8) ? 6 : ((STAGES - 1 < 3) ? STAGES - 1 : 3);
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;
@@ -534,7 +534,7 @@ igemm_t4_kernel(const __grid_constant__ CUtensorMap tmap, const IgemmParams p) {
   using L = SmemLayoutT4<BLOCK_N, A_STAGES, B_SLOTS>;
   constexpr int kGatherDepth = (A_STAGES - 1 < 3) ? A_STAGES - 1 : 3;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   uint64_t* a_full = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
   uint64_t* a_empty = a_full + A_STAGES;
   uint64_t* b_full = a_empty + A_STAGES;
