@@ -132,52 +132,67 @@ rs_adam_ag_kernel(PeerTable peers, float* __restrict__ master, float* __restrict
   const size_t s0 = lo + min((size_t)rank * per4, total4) * 4;
   const size_t s1 = lo + min((size_t)(rank + 1) * per4, total4) * 4;
   if (ok) {
-    for (size_t i = s0 + ((size_t)blockIdx.x * kCommThreads + threadIdx.x) * 4; i < s1;
-         i += (size_t)gridDim.x * kCommThreads * 4) {
-      float4 g;
-      if (mc_grad != nullptr) {
-        g = multimem_ld_reduce_f4(mc_grad + i);  // summed inside the NVSwitch
-      } else {
-        g = make_float4(0.f, 0.f, 0.f, 0.f);
+    // kUnroll quads per thread and trip, every load (peer / in-switch reduction, master, both moments) issued before
+    // the first use: one trip costs one NVLink round trip (~2-3 us), so the loop is bound by trips, not by bytes
+    constexpr int kUnroll = 4;
+    const size_t stride = (size_t)gridDim.x * kCommThreads * 4;
+    for (size_t base = s0 + ((size_t)blockIdx.x * kCommThreads + threadIdx.x) * 4; base < s1;
+         base += stride * kUnroll) {
+      float4 g[kUnroll], pv[kUnroll], mv[kUnroll], vv[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const size_t i = base + (size_t)u * stride;
+        g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < s1) {
+          if (mc_grad != nullptr) {
+            g[u] = multimem_ld_reduce_f4(mc_grad + i);  // summed inside the NVSwitch
+          } else {
 #pragma unroll 4
-        for (int r = 0; r < world; ++r) {
-          const float4 x = ld_peer_f4(reinterpret_cast<const float*>(peers.buf_a[(rank + r) % world]) + i);
-          g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+            for (int r = 0; r < world; ++r) {
+              const float4 x = ld_peer_f4(reinterpret_cast<const float*>(peers.buf_a[(rank + r) % world]) + i);
+              g[u].x += x.x; g[u].y += x.y; g[u].z += x.z; g[u].w += x.w;
+            }
+          }
+          pv[u] = *reinterpret_cast<float4*>(master + i);
+          mv[u] = *reinterpret_cast<float4*>(m + i);
+          vv[u] = *reinterpret_cast<float4*>(v + i);
         }
       }
-      float4 pv = *reinterpret_cast<float4*>(master + i);
-      float4 mv = *reinterpret_cast<float4*>(m + i);
-      float4 vv = *reinterpret_cast<float4*>(v + i);
-      float* gp = &g.x; float* pp = &pv.x; float* mp = &mv.x; float* vp = &vv.x;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float gj = gp[j] * inv_world;
-        mp[j] = b1 * mp[j] + (1.f - b1) * gj;
-        vp[j] = b2 * vp[j] + (1.f - b2) * gj * gj;
-        pp[j] -= lr_t * mp[j] / (sqrtf(vp[j]) + eps);
-      }
-      *reinterpret_cast<float4*>(master + i) = pv;
-      *reinterpret_cast<float4*>(m + i) = mv;
-      *reinterpret_cast<float4*>(v + i) = vv;
-      const uint2 packed = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
-      if (i >= pull_lo && i < pull_hi) {
-        // gathered by its first consumer (lin_fwd_gather): only the owner's own shadow is written here
-        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[rank]) + i) = packed;
-      } else if (mc_bf16 != nullptr) {
-        multimem_st_b64(mc_bf16 + i, packed);  // one store, every rank's copy
-      } else {
-#pragma unroll 4
-        for (int r = 0; r < world; ++r)
-          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[(rank + r) % world]) + i) = packed;
-      }
-      if (i >= f32_from) {
-        if (mc_master != nullptr) {
-          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_master + i), "f"(pv.x),
-                       "f"(pv.y), "f"(pv.z), "f"(pv.w)
-                       : "memory");
+      for (int u = 0; u < kUnroll; ++u) {
+        const size_t i = base + (size_t)u * stride;
+        if (i >= s1) break;
+        float* gp = &g[u].x; float* pp = &pv[u].x; float* mp = &mv[u].x; float* vp = &vv[u].x;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float gj = gp[j] * inv_world;
+          mp[j] = b1 * mp[j] + (1.f - b1) * gj;
+          vp[j] = b2 * vp[j] + (1.f - b2) * gj * gj;
+          pp[j] -= lr_t * mp[j] / (sqrtf(vp[j]) + eps);
+        }
+        *reinterpret_cast<float4*>(master + i) = pv[u];
+        *reinterpret_cast<float4*>(m + i) = mv[u];
+        *reinterpret_cast<float4*>(v + i) = vv[u];
+        const uint2 packed = make_uint2(pack_bf16x2(pv[u].x, pv[u].y), pack_bf16x2(pv[u].z, pv[u].w));
+        if (i >= pull_lo && i < pull_hi) {
+          // gathered by its first consumer (lin_fwd_gather): only the owner's own shadow is written here
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[rank]) + i) = packed;
+        } else if (mc_bf16 != nullptr) {
+          multimem_st_b64(mc_bf16 + i, packed);  // one store, every rank's copy
         } else {
-          for (int r = 1; r < world; ++r)
-            *reinterpret_cast<float4*>(reinterpret_cast<float*>(peers.buf_c[(rank + r) % world]) + i) = pv;
+#pragma unroll 4
+          for (int r = 0; r < world; ++r)
+            *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[(rank + r) % world]) + i) = packed;
+        }
+        if (i >= f32_from) {
+          if (mc_master != nullptr) {
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_master + i),
+                         "f"(pv[u].x), "f"(pv[u].y), "f"(pv[u].z), "f"(pv[u].w)
+                         : "memory");
+          } else {
+            for (int r = 1; r < world; ++r)
+              *reinterpret_cast<float4*>(reinterpret_cast<float*>(peers.buf_c[(rank + r) % world]) + i) = pv[u];
+          }
         }
       }
     }
@@ -263,7 +278,9 @@ allreduce_small_kernel(PeerTable peers /* buf_a = staging */, float* __restrict_
 __global__ void __launch_bounds__(kCommThreads)
 async_apply_kernel(PeerTable peers, const float* __restrict__ grad, __nv_bfloat16* __restrict__ local_bf16,
                    float* __restrict__ local_master, long long* const* __restrict__ peer_counters, int rank,
-                   int world, size_t n, float lr, float b1, float b2, float eps) {
+                   int world, size_t n, size_t lo, size_t hi, int advance, float lr, float b1, float b2, float eps) {
+  // [lo, hi) = the part of the arena applied by this launch (ownership is always by the whole arena's shards);
+  // advance != 0: this launch is the one of the step that advances the owners' step counts and global_step
   const size_t total4 = n / 4;
   const size_t per4 = shard_quads(total4, world);
   __shared__ float s_lr_t[kMaxRanks];
@@ -272,7 +289,7 @@ async_apply_kernel(PeerTable peers, const float* __restrict__ grad, __nv_bfloat1
     // beta1_power); block 0 does the increment, the others read a possibly older value
     long long* c = peer_counters[threadIdx.x];
     long long t;
-    if (blockIdx.x == 0) {
+    if (blockIdx.x == 0 && advance) {
       t = atomicAdd_system(reinterpret_cast<unsigned long long*>(c), 1ull) + 1;
       if (threadIdx.x == 0) atomicAdd_system(reinterpret_cast<unsigned long long*>(peer_counters[0] + 1), 1ull);
     } else {
@@ -282,31 +299,47 @@ async_apply_kernel(PeerTable peers, const float* __restrict__ grad, __nv_bfloat1
     s_lr_t[threadIdx.x] = lr * sqrtf(1.f - powf(b2, tf)) / (1.f - powf(b1, tf));
   }
   __syncthreads();
-  for (size_t i4 = (size_t)blockIdx.x * kCommThreads + threadIdx.x; i4 < total4;
-       i4 += (size_t)gridDim.x * kCommThreads) {
-    const int owner = (int)min(i4 / per4, (size_t)(world - 1));
-    const size_t i = i4 * 4;
-    float* P = reinterpret_cast<float*>(peers.buf_a[owner]) + i;
-    float* M = reinterpret_cast<float*>(peers.buf_c[owner]) + i;
-    float* V = reinterpret_cast<float*>(peers.buf_d[owner]) + i;
-    float4 pv = ld_peer_f4(P), mv = ld_peer_f4(M), vv = ld_peer_f4(V);
-    const float4 g = *reinterpret_cast<const float4*>(grad + i);
-    const float* gp = &g.x; float* pp = &pv.x; float* mp = &mv.x; float* vp = &vv.x;
-    const float lr_t = s_lr_t[owner];
+  // kUnroll quads per thread and trip, all peer loads issued before the first use (a trip = one NVLink round trip)
+  constexpr int kUnroll = 4;
+  const size_t stride4 = (size_t)gridDim.x * kCommThreads;
+  const size_t last4 = min(hi / 4, total4);
+  for (size_t b4 = lo / 4 + (size_t)blockIdx.x * kCommThreads + threadIdx.x; b4 < last4; b4 += stride4 * kUnroll) {
+    float4 pv[kUnroll], mv[kUnroll], vv[kUnroll], g[kUnroll];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      mp[j] = b1 * mp[j] + (1.f - b1) * gp[j];
-      vp[j] = b2 * vp[j] + (1.f - b2) * gp[j] * gp[j];
-      pp[j] -= lr_t * mp[j] / (sqrtf(vp[j]) + eps);
+    for (int u = 0; u < kUnroll; ++u) {
+      const size_t i4 = b4 + (size_t)u * stride4;
+      if (i4 < last4) {
+        const int owner = (int)min(i4 / per4, (size_t)(world - 1));
+        const size_t i = i4 * 4;
+        pv[u] = ld_peer_f4(reinterpret_cast<float*>(peers.buf_a[owner]) + i);
+        mv[u] = ld_peer_f4(reinterpret_cast<float*>(peers.buf_c[owner]) + i);
+        vv[u] = ld_peer_f4(reinterpret_cast<float*>(peers.buf_d[owner]) + i);
+        g[u] = *reinterpret_cast<const float4*>(grad + i);
+      }
     }
-    *reinterpret_cast<float4*>(P) = pv;
-    *reinterpret_cast<float4*>(M) = mv;
-    *reinterpret_cast<float4*>(V) = vv;
-    const uint2 packed = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
-    *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[owner]) + i) = packed;
-    if (owner != rank) {  // what we just read and updated is our fresh pull (bf16 shadow + f32 for the f32 readers)
-      *reinterpret_cast<uint2*>(local_bf16 + i) = packed;
-      *reinterpret_cast<float4*>(local_master + i) = pv;
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const size_t i4 = b4 + (size_t)u * stride4;
+      if (i4 >= last4) break;
+      const int owner = (int)min(i4 / per4, (size_t)(world - 1));
+      const size_t i = i4 * 4;
+      const float* gp = &g[u].x; float* pp = &pv[u].x; float* mp = &mv[u].x; float* vp = &vv[u].x;
+      const float lr_t = s_lr_t[owner];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        mp[j] = b1 * mp[j] + (1.f - b1) * gp[j];
+        vp[j] = b2 * vp[j] + (1.f - b2) * gp[j] * gp[j];
+        pp[j] -= lr_t * mp[j] / (sqrtf(vp[j]) + eps);
+      }
+      *reinterpret_cast<float4*>(reinterpret_cast<float*>(peers.buf_a[owner]) + i) = pv[u];
+      *reinterpret_cast<float4*>(reinterpret_cast<float*>(peers.buf_c[owner]) + i) = mv[u];
+      *reinterpret_cast<float4*>(reinterpret_cast<float*>(peers.buf_d[owner]) + i) = vv[u];
+      const uint2 packed = make_uint2(pack_bf16x2(pv[u].x, pv[u].y), pack_bf16x2(pv[u].z, pv[u].w));
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(peers.buf_b[owner]) + i) = packed;
+      if (owner != rank) {  // what we just read and updated is our fresh pull (bf16 shadow + f32 for the f32 readers)
+        *reinterpret_cast<uint2*>(local_bf16 + i) = packed;
+        *reinterpret_cast<float4*>(local_master + i) = pv[u];
+      }
     }
   }
 }
@@ -430,9 +463,9 @@ int dcgan_comm_allreduce_small(const void* const* staging_ptrs, const void* cons
 
 int dcgan_comm_async_apply(const void* const* master_ptrs, const void* const* bf16_ptrs, const void* const* m_ptrs,
                            const void* const* v_ptrs, const float* grad, void* local_bf16, float* local_master,
-                           long long* const* peer_counters_dev, int rank, int world, size_t n, float lr, float b1,
-                           float b2, float eps, int blocks, cudaStream_t st) {
-  if (world < 1 || world > kMaxRanks || (n % 4)) return DCGAN_ERR_SHAPE;
+                           long long* const* peer_counters_dev, int rank, int world, size_t n, size_t lo, size_t hi,
+                           int advance, float lr, float b1, float b2, float eps, int blocks, cudaStream_t st) {
+  if (world < 1 || world > kMaxRanks || (n % 4) || (lo % 4) || (hi % 4) || lo > hi || hi > n) return DCGAN_ERR_SHAPE;
   PeerTable t{};
   fill(t.buf_a, master_ptrs, world);
   fill(t.buf_b, bf16_ptrs, world);
@@ -440,8 +473,8 @@ int dcgan_comm_async_apply(const void* const* master_ptrs, const void* const* bf
   fill(t.buf_d, v_ptrs, world);
   if (blocks <= 0) blocks = 148;
   async_apply_kernel<<<blocks, kCommThreads, 0, st>>>(t, grad, reinterpret_cast<__nv_bfloat16*>(local_bf16),
-                                                      local_master, peer_counters_dev, rank, world, n, lr, b1, b2,
-                                                      eps);
+                                                      local_master, peer_counters_dev, rank, world, n, lo, hi,
+                                                      advance, lr, b1, b2, eps);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
 

@@ -467,7 +467,7 @@ class DCGANEngine:
                    colsum=g["g_h4/biases"],  # g_h4's bias gradient falls out of the same pass, in f32
                    w_bf16=self.w_native["d_h0_conv/w"])
 
-    def generator_backward(self, early_adam: bool = False) -> Optional[int]:
+    def generator_backward(self, early_adam: bool = False, early_comm: bool = False) -> Optional[int]:
         """``early_adam``: the Adam update of g_h1/w .. g_h3/w (85 % of the generator's parameters) is issued on the
         side stream as soon as the last of their gradients is done and nothing reads those filters any more, under
         the tail of the backward pass; returns the arena offset where the remaining (final) update starts."""
@@ -489,6 +489,10 @@ class DCGANEngine:
                                              self.g_pre[i - 1], False, dpre=self.dg_pre[i - 1])
             else:
                 K.conv_fprop_kn(self.dg_pre[i], w, None, out=self.dg_act[i - 1])
+        if early_comm:
+            # multi-GPU: the exchange + Adam of g_h1/w .. g_h3/w goes to the communication stream now, ordered after
+            # g_h1's data gradient (last reader of those filters) and after the filter gradients on the side stream
+            self.comm.launch_bucket(self, "g1", side_stream=True, also_wait=self.side_event())
         if early_adam and self.wgrad_overlap:
             A = self.arena
             lo, hi = A.offsets["g_h1/w"][0], A.offsets["g_h0_lin/Matrix"][0]
@@ -567,9 +571,10 @@ class DCGANEngine:
             if self.comm is not None and getattr(self.comm, "overlap", False):
                 # D's gradient exchange + Adam runs on the communication stream under G's backward pass
                 self.comm.launch_bucket(self, "d", side_stream=True, also_wait=self.side_event())
-                self.generator_backward()
+                early = getattr(self.comm, "has_early_generator_bucket", lambda: False)()
+                self.generator_backward(early_comm=early)
                 self._join_side()
-                self.comm.launch_bucket(self, "g", side_stream=False)
+                self.comm.launch_bucket(self, "g2" if early else "g", side_stream=False)
                 self.comm.join()
                 self.refresh_compute_weights(cast=False)
             elif self.comm is None and self.wgrad_overlap:

@@ -60,7 +60,7 @@ _SIGNATURES = {
     "dcgan_comm_rs_adam_ag": "pppppppppiizzffffipppzzzis",
     "dcgan_comm_lin_fwd_gather": "ppppiiizzziis",
     "dcgan_comm_allreduce_small": "pppiipiiis",
-    "dcgan_comm_async_apply": "ppppppppiizffffis",
+    "dcgan_comm_async_apply": "ppppppppiizzziffffis",
     "dcgan_bn_forward_static": "pppppppiiiffis",
     "dcgan_copy_error_flag": "ps",
 }

@@ -22,13 +22,18 @@ from .fused_comm import _ptr_array
 
 
 class AsyncPSComm:
-    overlap = False
     sync_bn = False
 
-    def __init__(self, device, blocks: int = 148, group=None):
+    def __init__(self, device, blocks: int = 148, group=None, overlap: bool = True, overlap_blocks: int = 64):
+        import os
         import torch.distributed._symmetric_memory as symm_mem
         self.symm_mem = symm_mem
         self.device, self.blocks = device, blocks
+        # like the synchronous path, the push of D's variables runs on a stream of its own under G's backward pass
+        self.overlap = overlap and os.environ.get("DCGAN_COMM_OVERLAP", "1") != "0"
+        self.overlap_blocks = int(os.environ.get("DCGAN_COMM_BLOCKS", overlap_blocks))
+        self.stream = torch.cuda.Stream(device)
+        self._fork_event, self._join_event, self._forked = torch.cuda.Event(), torch.cuda.Event(), False
         self.group = group if group is not None else dist.group.WORLD   # the worker ranks (ps tasks excluded)
         self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
         self.chief = dist.get_global_rank(self.group, 0)
@@ -72,11 +77,38 @@ class AsyncPSComm:
         torch.cuda.synchronize(self.device)
         dist.barrier(group=self.group)
 
-    def optimizer_step(self, engine, which: str = "both") -> None:
+    def _apply(self, engine, lo: int, hi: int, advance: bool, blocks: int) -> None:
         A = engine.arena
         _lib.call("dcgan_comm_async_apply", self._p, self._b, self._m, self._v, engine.grads.data_ptr(),
-                  A.bf16.data_ptr(), A.master.data_ptr(), self._counter_ptrs.data_ptr(), self.rank, self.world, A.padded, engine.lr,
-                  engine.beta1, engine.beta2, engine.eps, self.blocks)
+                  A.bf16.data_ptr(), A.master.data_ptr(), self._counter_ptrs.data_ptr(), self.rank, self.world,
+                  A.padded, lo, hi, int(advance), engine.lr, engine.beta1, engine.beta2, engine.eps, blocks)
+
+    def optimizer_step(self, engine, which: str = "both") -> None:
+        A = engine.arena
+        lo, hi = {"both": (0, A.padded), "g": (0, A.g_end), "d": (A.g_end, A.padded)}[which]
+        self._apply(engine, lo, hi, which != "d", self.blocks)   # one advance per step: with G's (or the only) push
+
+    def launch_bucket(self, engine, which: str, side_stream: bool, also_wait=None) -> None:
+        """Same protocol as FusedComm.launch_bucket: 'd' under G's backward pass on the push stream, 'g' last."""
+        A = engine.arena
+        lo, hi = {"g": (0, A.g_end), "d": (A.g_end, A.padded)}[which]
+        if side_stream:
+            cur = torch.cuda.current_stream(self.device)
+            self._fork_event.record(cur)
+            self.stream.wait_event(self._fork_event)
+            if also_wait is not None:
+                self.stream.wait_event(also_wait)
+            with torch.cuda.stream(self.stream):
+                self._apply(engine, lo, hi, which != "d", self.overlap_blocks)
+                self._join_event.record(self.stream)
+            self._forked = True
+        else:
+            self._apply(engine, lo, hi, which != "d", self.blocks)
+
+    def join(self) -> None:
+        if self._forked:
+            torch.cuda.current_stream(self.device).wait_event(self._join_event)
+            self._forked = False
 
     def global_step(self) -> int:
         """Applies of all workers so far: rank 0's counter, read through peer memory from any rank."""

@@ -26,7 +26,7 @@ import torch.distributed as dist
 
 from ..ops import _lib
 
-SLOT_G, SLOT_D, SLOT_BN = 0, 1, 2
+SLOT_G, SLOT_D, SLOT_BN, SLOT_G1 = 0, 1, 2, 3
 N_SLOTS = 4
 MAX_RANKS = 16
 BN_STAGING = 8192  # floats per parity (largest site: 3 slabs x 2 x 1024 channels)
@@ -39,7 +39,7 @@ def _ptr_array(ptrs):
 
 class FusedComm:
     def __init__(self, device, sync_bn: bool = False, overlap: bool = True, use_multicast: bool = True,
-                 blocks: int = 32, gather_in_consumer: bool = True, group=None):
+                 blocks: int = 64, gather_in_consumer: bool = False, group=None):
         import torch.distributed._symmetric_memory as symm_mem
         self.symm_mem = symm_mem
         self.device, self.sync_bn, self.overlap = device, sync_bn, overlap
@@ -54,8 +54,12 @@ class FusedComm:
         self.handles: Dict[str, object] = {}
         self.tensors: Dict[str, torch.Tensor] = {}
         self.use_multicast = use_multicast
-        self.blocks = blocks
-        self.gather_in_consumer = gather_in_consumer and os.environ.get("DCGAN_GATHER_IN_CONSUMER", "1") != "0"
+        self.blocks = int(os.environ.get("DCGAN_COMM_BLOCKS", blocks))  # CTAs of an exchange that overlaps compute
+        # Measured at 2 GPUs (profiles/mg_ab_n2_r2.log): pushing g_h0_lin/Matrix with the rest of its bucket beats
+        # pulling it inside lin_fwd (whose loop then pays NVLink latency at the head of the step): 0.707 vs 0.723 ms,
+        # so the consumer-side gather is opt-in (DCGAN_GATHER_IN_CONSUMER=1)
+        env = os.environ.get("DCGAN_GATHER_IN_CONSUMER")
+        self.gather_in_consumer = gather_in_consumer if env is None else env != "0"
         self.overlap = overlap and os.environ.get("DCGAN_COMM_OVERLAP", "1") != "0"
         self.stream = torch.cuda.Stream(device)
         self._fork_event = torch.cuda.Event()
@@ -98,9 +102,23 @@ class FusedComm:
         self.mc_grad = int(hg.multicast_ptr) if mc_ok else None
         self.mc_bf16 = int(hb.multicast_ptr) if mc_ok else None
         self.mc_master = int(hm.multicast_ptr) if mc_ok else None
-        self.buckets = {"g": (0, A.g_end), "d": (A.g_end, A.padded), "both": None}
-        # f32-consumed variables start here inside each bucket (their master value is gathered too)
-        self.f32_from = {"g": A.f32_start["g"], "d": A.f32_start["d"]}
+        # Buckets = ranges of the arena exchanged by one kernel launch each, every one sharded over the ranks.  The
+        # generator is split in two: "g1" = g_h1/w .. g_h3/w (85 % of its parameters; their gradients are complete
+        # while the tail of the backward pass still runs, so this exchange overlaps it) and "g2" = the rest
+        # (g_h0_lin/Matrix, whose gradient is the last kernel of the step, and the small f32 variables).
+        split = A.offsets["g_h0_lin/Matrix"][0] if os.environ.get("DCGAN_COMM_SPLIT_G", "1") != "0" else 0
+        if 0 < split < A.f32_start["g"] and split % 8 == 0:
+            self.buckets = {"g1": (0, split), "g2": (split, A.g_end), "d": (A.g_end, A.padded)}
+            self.slots = {"g1": SLOT_G1, "g2": SLOT_G, "d": SLOT_D}
+            # f32-consumed variables start here inside each bucket (their master value is gathered too)
+            self.f32_from = {"g1": split, "g2": A.f32_start["g"], "d": A.f32_start["d"]}
+            self.parts = {"g": ("g1", "g2"), "d": ("d",), "g1": ("g1",), "g2": ("g2",), "both": ("d", "g1", "g2")}
+        else:
+            self.buckets = {"g": (0, A.g_end), "d": (A.g_end, A.padded)}
+            self.slots = {"g": SLOT_G, "d": SLOT_D}
+            self.f32_from = {"g": A.f32_start["g"], "d": A.f32_start["d"]}
+            self.parts = {"g": ("g",), "d": ("d",), "both": ("d", "g")}
+        self.bucket_names = tuple(self.buckets)
         # g_h0_lin/Matrix is gathered by its consumer (lin_fwd_gather), not pushed by the optimizer kernel
         off, shape = A.offsets["g_h0_lin/Matrix"]
         self.pull_range = (off, off + shape[0] * shape[1]) if self.gather_in_consumer else (0, 0)
@@ -115,7 +133,7 @@ class FusedComm:
     def owner_ranks(self, lo: int, hi: int):
         """Ranks whose optimizer shard intersects the arena range [lo, hi)."""
         out = []
-        for bucket in ("g", "d"):
+        for bucket in self.bucket_names:
             for r in range(self.world):
                 s0, s1 = self.shard_range(bucket, r)
                 if s0 < hi and lo < s1 and r not in out:
@@ -126,8 +144,8 @@ class FusedComm:
     def _launch(self, engine, which: str, blocks: int = 0) -> None:
         A = engine.arena
         lo, hi = self.buckets[which]
-        slot = SLOT_G if which == "g" else SLOT_D
-        pull_lo, pull_hi = self.pull_range if which == "g" else (0, 0)
+        slot = self.slots[which]
+        pull_lo, pull_hi = self.pull_range if (lo <= self.pull_range[0] and self.pull_range[1] <= hi) else (0, 0)
         _lib.call("dcgan_comm_rs_adam_ag", self._grad_ptrs, self._bf16_ptrs, self._sig_ptrs, self._master_ptrs,
                   A.master.data_ptr(), A.m.data_ptr(), A.v.data_ptr(), engine.counters.data_ptr(),
                   self.state[slot].data_ptr(), self.rank, self.world, lo, hi, engine.lr, engine.beta1, engine.beta2,
@@ -143,7 +161,8 @@ class FusedComm:
             K.lin_fwd(engine.z, engine.w_native["g_h0_lin/Matrix"], engine.params["g_h0_lin/bias"], out2d)
             return
         off, shape = A.offsets["g_h0_lin/Matrix"]
-        lo, hi = self.buckets["g"]
+        lo, hi = next(self.buckets[b] for b in self.bucket_names
+                      if self.buckets[b][0] <= off and off + shape[0] * shape[1] <= self.buckets[b][1])
         _lib.call("dcgan_comm_lin_fwd_gather", self._bf16_ptrs, engine.z.data_ptr(),
                   engine.params["g_h0_lin/bias"].data_ptr(), out2d.data_ptr(), engine.B, shape[0], shape[1], off, lo,
                   hi, self.rank, self.world)
@@ -156,12 +175,17 @@ class FusedComm:
             if also_wait is not None:   # e.g. the engine's side stream that carries the filter gradients
                 self.stream.wait_event(also_wait)
             with torch.cuda.stream(self.stream):
-                self._launch(engine, which)
+                for part in self.parts[which]:
+                    self._launch(engine, part)
                 self._join_event.record(self.stream)
             self._forked = True
         else:
             # nothing left to overlap with: give the exchange the whole GPU
-            self._launch(engine, which, blocks=148)
+            for part in self.parts[which]:
+                self._launch(engine, part, blocks=int(os.environ.get("DCGAN_COMM_BLOCKS_ALONE", 148)))
+
+    def has_early_generator_bucket(self) -> bool:
+        return "g1" in self.buckets
 
     def join(self) -> None:
         if self._forked:
@@ -169,8 +193,8 @@ class FusedComm:
             self._forked = False
 
     def optimizer_step(self, engine, which: str = "both") -> None:
-        for w in (("d", "g") if which == "both" else (which,)):
-            self._launch(engine, w)
+        for part in self.parts[which]:
+            self._launch(engine, part)
 
     # ---- cross-replica batch norm -----------------------------------------------------------------------------------
     def allreduce_bn(self, buf: torch.Tensor) -> None:
@@ -198,7 +222,7 @@ class FusedComm:
                 if r == self.rank:
                     continue
                 peer = hdl.get_buffer(r, (A.padded,), torch.float32)
-                for bucket in ("g", "d"):
+                for bucket in self.bucket_names:
                     s0, s1 = self.shard_range(bucket, r)
                     if s1 > s0:
                         local[s0:s1].copy_(peer[s0:s1])

@@ -293,11 +293,14 @@ int dcgan_comm_allreduce_small(const void* const* staging_ptrs, const void* cons
                                int staging_stride, unsigned* state, int rank, int world, int slot,
                                cudaStream_t stream);
 /* Async parameter-server mode: apply this worker's gradients to the owners' shards through peer memory
- * (unlocked, stale -- reference image_train.py:109-112 with use_locking=False) and refresh the local copy. */
+ * (unlocked, stale -- reference image_train.py:109-112 with use_locking=False) and refresh the local copy.
+ * [lo, hi) = the elements of the n-element arena this launch applies (the step may be split, e.g. D's variables
+ * while G's backward pass still runs); advance != 0 on the one launch per step that advances the owners' Adam step
+ * counts and global_step. */
 int dcgan_comm_async_apply(const void* const* master_ptrs, const void* const* bf16_ptrs, const void* const* m_ptrs,
                            const void* const* v_ptrs, const float* grad, void* local_bf16, float* local_master,
-                           long long* const* peer_counters_dev, int rank, int world, size_t n, float lr, float b1,
-                           float b2, float eps, int blocks, cudaStream_t stream);
+                           long long* const* peer_counters_dev, int rank, int world, size_t n, size_t lo, size_t hi,
+                           int advance, float lr, float b1, float b2, float eps, int blocks, cudaStream_t stream);
 
 #ifdef __cplusplus
 }
