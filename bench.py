@@ -57,9 +57,10 @@ class ClockSampler:
 
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_power_cap,index")
 
-    def __init__(self, index: int):
+    def __init__(self, index):
+        """``index``: one GPU index or a comma-separated list (every GPU of the job, sampled by rank 0)."""
         self.index, self.proc, self.lines = index, None, []
 
     def start(self):
@@ -79,7 +80,7 @@ class ClockSampler:
 
     def mark_begin(self):
         """Start of the timed region: samples before this line count as idle."""
-        self.mark_lo = max(len(self.lines) - 1, 0)
+        self.mark_lo = max(len(self.lines) - max(str(self.index).count(",") + 1, 1), 0)
 
     def mark_end(self):
         time.sleep(0.12)  # let the sample that covers the end of the region arrive
@@ -93,7 +94,7 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        sm, mx, reasons, by_gpu, pw = [], [], set(), {}, {}
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         lines = self.lines[self.mark_lo:self.mark_hi] if self.mark_hi else self.lines
         for ln in lines:
@@ -104,11 +105,22 @@ class ClockSampler:
                 sm.append(float(parts[0])); mx.append(float(parts[1]))
             except ValueError:
                 continue
+            gpu = parts[7] if len(parts) > 7 else "0"
+            by_gpu.setdefault(gpu, []).append(float(parts[0]))
+            try:
+                pw.setdefault(gpu, []).append(float(parts[2]))
+            except ValueError:
+                pass
             for n, v in zip(names, parts[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        out = {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+               "samples": len(sm), "reasons": sorted(reasons)}
+        if len(by_gpu) > 1:  # the slowest GPU bounds a synchronous step: report every GPU's median under load
+            out["sm_mhz"] = min(statistics.median(v) for v in by_gpu.values())
+            out["sm_mhz_by_gpu"] = {k: statistics.median(v) for k, v in sorted(by_gpu.items(), key=lambda kv: int(kv[0]))}
+            out["power_w_by_gpu"] = {k: round(statistics.median(v)) for k, v in sorted(pw.items(), key=lambda kv: int(kv[0]))}
+        return out
 
 
 def dist_env():
@@ -331,7 +343,7 @@ def main():
 
     # clocks / throttle reasons are sampled from before the warm-up; only the samples taken during the two
     # timed regions are reported
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(",".join(str(i) for i in range(world)) if world > 1 else local)
     if rank == 0:
         sampler.start()
     # ---- warm-up ------------------------------------------------------------------------------------
