@@ -549,6 +549,10 @@ class DCGANEngine:
         with self._off_critical_path():
             self.grads.zero_()
         self._scratch.zero_()
+        deferred_g = (self.update_mode == "simultaneous" and self.comm is not None
+                      and getattr(self.comm, "overlap", False) and getattr(self.comm, "deferred_g", False))
+        if deferred_g:  # async mode: the previous step's generator gradients are pushed under this step's passes
+            self.comm.launch_deferred_g(self)
         K.f32_to_bf16(self.real_f32, self.d_in[:B])
         split = self.split_d_forward and not (self.comm is not None and getattr(self.comm, "sync_bn", False))
         if split:  # D(real) needs nothing from G: it runs beside the generator's forward pass
@@ -574,8 +578,12 @@ class DCGANEngine:
                 early = getattr(self.comm, "has_early_generator_bucket", lambda: False)()
                 self.generator_backward(early_comm=early)
                 self._join_side()
-                self.comm.launch_bucket(self, "g2" if early else "g", side_stream=False)
-                self.comm.join()
+                if deferred_g:
+                    self.comm.join()
+                    self.comm.stash_g(self)
+                else:
+                    self.comm.launch_bucket(self, "g2" if early else "g", side_stream=False)
+                    self.comm.join()
                 self.refresh_compute_weights(cast=False)
             elif self.comm is None and self.wgrad_overlap:
                 # D's Adam (its gradients are complete) runs beside G's backward pass
@@ -627,6 +635,7 @@ class DCGANEngine:
         with torch.cuda.graph(self._graph, stream=hp):
             self.step_body()
         self.restore_state(state)
+        getattr(self.comm, "reset_deferred", lambda: None)()   # gradients stashed by the warm-up steps are not pushed
 
     def run_step(self) -> None:
         """One iteration on the inputs currently in ``real_f32`` / ``z`` (no host sync)."""
@@ -754,6 +763,8 @@ class DCGANEngine:
         TensorFlow's slot names.  With sharded optimizer state (multi-GPU) this is a
         collective: every rank must call it."""
         A = self.arena
+        if self.comm is not None and hasattr(self.comm, "flush"):
+            self.comm.flush(self)   # async mode: the generator gradients still waiting for their deferred push
         if self.comm is not None and hasattr(self.comm, "gather_state"):
             self.comm.gather_state(self)
         sd = {n: t.detach().clone() for n, t in self.params.items()}

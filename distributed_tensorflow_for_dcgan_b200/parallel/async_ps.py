@@ -12,6 +12,7 @@ There is no barrier, no lock and no aggregation, like the reference's ``use_lock
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict
 
 import torch
@@ -25,7 +26,6 @@ class AsyncPSComm:
     sync_bn = False
 
     def __init__(self, device, blocks: int = 148, group=None, overlap: bool = True, overlap_blocks: int = 64):
-        import os
         import torch.distributed._symmetric_memory as symm_mem
         self.symm_mem = symm_mem
         self.device, self.blocks = device, blocks
@@ -34,6 +34,13 @@ class AsyncPSComm:
         self.overlap_blocks = int(os.environ.get("DCGAN_COMM_BLOCKS", overlap_blocks))
         self.stream = torch.cuda.Stream(device)
         self._fork_event, self._join_event, self._forked = torch.cuda.Event(), torch.cuda.Event(), False
+        # Deferred generator push: the generator's gradients of step k are pushed at the START of step k + 1, on the
+        # push stream, under that step's forward passes and D's backward pass (they are the last thing a step
+        # computes, so pushed at once they would have nothing to hide behind).  The worker's own generator update
+        # therefore lands one step late -- one more step of the staleness this mode is made of; its reads of the
+        # generator's parameters meanwhile are as unlocked as the reference's (use_locking=False).
+        self.deferred_g = self.overlap and os.environ.get("DCGAN_ASYNC_DEFER_G", "1") != "0"
+        self.gprev = None
         self.group = group if group is not None else dist.group.WORLD   # the worker ranks (ps tasks excluded)
         self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
         self.chief = dist.get_global_rank(self.group, 0)
@@ -77,9 +84,10 @@ class AsyncPSComm:
         torch.cuda.synchronize(self.device)
         dist.barrier(group=self.group)
 
-    def _apply(self, engine, lo: int, hi: int, advance: bool, blocks: int) -> None:
+    def _apply(self, engine, lo: int, hi: int, advance: bool, blocks: int, grads=None) -> None:
         A = engine.arena
-        _lib.call("dcgan_comm_async_apply", self._p, self._b, self._m, self._v, engine.grads.data_ptr(),
+        _lib.call("dcgan_comm_async_apply", self._p, self._b, self._m, self._v,
+                  (engine.grads if grads is None else grads).data_ptr(),
                   A.bf16.data_ptr(), A.master.data_ptr(), self._counter_ptrs.data_ptr(), self.rank, self.world,
                   A.padded, lo, hi, int(advance), engine.lr, engine.beta1, engine.beta2, engine.eps, blocks)
 
@@ -109,6 +117,35 @@ class AsyncPSComm:
         if self._forked:
             torch.cuda.current_stream(self.device).wait_event(self._join_event)
             self._forked = False
+
+    # ---- deferred generator push ----------------------------------------------------------------------------------
+    def launch_deferred_g(self, engine) -> None:
+        """Start of a step: push the generator gradients stashed by the previous step (zeros the first time: an
+        Adam step on zero moments and a zero gradient moves nothing)."""
+        A = engine.arena
+        if self.gprev is None:
+            self.gprev = torch.zeros(A.g_end, dtype=torch.float32, device=self.device)
+        cur = torch.cuda.current_stream(self.device)
+        self._fork_event.record(cur)
+        self.stream.wait_event(self._fork_event)
+        with torch.cuda.stream(self.stream):
+            self._apply(engine, 0, A.g_end, True, self.overlap_blocks, grads=self.gprev)
+            self._join_event.record(self.stream)
+        self._forked = True
+
+    def stash_g(self, engine) -> None:
+        """End of a step (after ``join``): keep the generator's gradients for the next step's push."""
+        self.gprev.copy_(engine.grads[:engine.arena.g_end])
+
+    def reset_deferred(self) -> None:
+        if self.gprev is not None:
+            self.gprev.zero_()
+
+    def flush(self, engine) -> None:
+        """Push what ``stash_g`` holds now (end of training / before a checkpoint)."""
+        if self.deferred_g and self.gprev is not None:
+            self._apply(engine, 0, engine.arena.g_end, False, self.blocks, grads=self.gprev)
+            self.gprev.zero_()
 
     def global_step(self) -> int:
         """Applies of all workers so far: rank 0's counter, read through peer memory from any rank."""
