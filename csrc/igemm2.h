@@ -19,6 +19,7 @@ struct Igemm2Params {
   int m_tiles, n_tiles;  // tile grid (T: per parity class; W: per filter tap)
   int ksplit;            // K slices per tile
   int total_groups;      // work items of the static schedule: tiles * ksplit
+  int variant;           // kernel variant of the tile width: 0 default, 1 = two k-blocks per ring slot (64 columns)
   int b_mn;              // F: filter is [25][Ck][Cn] (TensorFlow layout) -> MN-major B operand
   // epilogue
   void* out;              // F/T: bf16 NHWC.  W: f32 [25][Cn][Cd]
@@ -112,7 +113,7 @@ void igemm2_set_ksplit(int v);
 void igemm2_set_tile(int v);
 // measured plan of one layer shape (kind: MODE_F / MODE_T / MODE_W; W: H, W = the small grid, Cin = Cg, Cout = Cd);
 // block_n <= 0 forgets it
-int igemm2_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit);
+int igemm2_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit, int variant);
 void igemm2_set_stage_mode(int v);
 int igemm2_set_workspace(void* ptr, size_t bytes);
 

@@ -62,10 +62,11 @@ constexpr int kMmaWarp = kNumProducers;             // warps [0, P) TMA producer
 constexpr int kThreads = (kNumProducers + 5) * 32;
 constexpr int kEpiThreads = 128;
 
-template <int BLOCK_N, int STAGES>
+template <int BLOCK_N, int STAGES, int KPS = 1>
 struct Smem2 {
   static constexpr int kBTileBytes = BLOCK_N * kBlockK * 2;
-  static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+  static constexpr int kSubBytes = kATileBytes + kBTileBytes;  // one k-block: A tile + B tile
+  static constexpr int kStageBytes = KPS * kSubBytes;          // a ring slot holds KPS consecutive k-blocks
   static constexpr int kBarOffset = STAGES * kStageBytes;  // full[STAGES], empty[STAGES], tfull[2], tempty[2]
   static constexpr int kMiscOffset = kBarOffset + 256;     // tmem base, abort flag, split-K "last" flag
   static constexpr int kStatOffset = kMiscOffset + 64;     // [4 warps][2][BLOCK_N] f32 epilogue column sums
@@ -130,7 +131,7 @@ __device__ __forceinline__ void stcg_f4(float4* p, float4 v) {
                : "memory");
 }
 
-template <int MODE, int BLOCK_N, int STAGES, int MINB>
+template <int MODE, int BLOCK_N, int STAGES, int MINB, int KPS>
 __global__ void __launch_bounds__(kThreads, MINB)
 igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 4-D NHWC activation tensor
               const __grid_constant__ CUtensorMap tmap_d,  // dense operand: 2-D (filter, or W: the small activation)
@@ -140,7 +141,7 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
   long long t_kernel_begin;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_kernel_begin));
 #endif
-  using L = Smem2<BLOCK_N, STAGES>;
+  using L = Smem2<BLOCK_N, STAGES, KPS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
@@ -211,47 +212,56 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
           tb = lt0 - ta * nb;
         }
         const int kh_w = wi.tap / 5, kw_w = wi.tap - 5 * (wi.tap / 5);
-        for (int kb = 0; kb < wi.nkb; ++kb) {
+        // a ring slot takes KPS consecutive k-blocks (the last slot of an item may be short): with 64-column tiles
+        // the MMA warp's fixed cost per slot exceeds the tensor time of one k-block, two per slot halve its share
+        for (int kb = 0; kb < wi.nkb; kb += KPS) {
+          const int nsub = (wi.nkb - kb) < KPS ? (wi.nkb - kb) : KPS;
           const bool mine = (s % kNumProducers) == warp;  // every warp walks the whole sequence, fills its own slots
           const long long tw0 = T_NOW();
           if (mine && !mbar_wait(&empty_bar[s], phase ^ 1, abort_flag, p.err_flag)) { ok = false; break; }
           T_ADD(tp_wait, tw0); ++tp_n;
-          uint8_t* sA = smem + s * L::kStageBytes;
-          uint8_t* sB = sA + kATileBytes;
-          if (mine && elect_one()) {
-          mbar_arrive_expect_tx(&full_bar[s], L::kStageBytes);
-          if (MODE == MODE_W) {
-            const int px0 = (wi.kb0 + kb) * kBlockK;
-            tma_load_2d(sA, &tmap_d, &full_bar[s], wi.m0, px0);
-            tma_load_2d(sA + kATileBytes / 2, &tmap_d, &full_bar[s], wi.m0 + 64, px0);
-            const int imgk = px0 >> (p.rW_log2 + p.rH_log2);
-            const int hk = (px0 >> p.rW_log2) & (rH - 1);
+          const bool issue = mine && elect_one();
+          if (issue) mbar_arrive_expect_tx(&full_bar[s], nsub * L::kSubBytes);
 #pragma unroll
-            for (int j = 0; j < BLOCK_N / 64; ++j)
-              tma_load_4d(sB + j * 8192, &tmap_g, &full_bar[s], wi.n0 + 64 * j, kw_w - 1, 2 * hk + kh_w - 1, imgk);
-          } else {
-            int tap;
-            if (MODE == MODE_F) {
-              tma_load_4d(sA, &tmap_g, &full_bar[s], cc * kBlockK, tb - 1, 2 * h0 + ta - 1, img0);
-              tap = ta * 5 + tb;
-            } else {
-              // out[2q+p] takes x[q + (p - i)] through tap k = 2i (p = 1) or 2i+1 (p = 0)
-              tma_load_4d(sA, &tmap_g, &full_bar[s], cc * kBlockK, wi.pw - tb, h0 + wi.ph - ta, img0);
-              const int kh = wi.ph ? 2 * ta : 2 * ta + 1;
-              const int kw = wi.pw ? 2 * tb : 2 * tb + 1;
-              tap = kh * 5 + kw;
-            }
-            if (p.b_mn) {  // TensorFlow layout [tap][Ck][Cn]: 64(k) x 64(n) boxes, one per 64 output channels
+          for (int j = 0; j < KPS; ++j) {
+            if (j < nsub) {
+              uint8_t* sA = smem + s * L::kStageBytes + j * L::kSubBytes;
+              uint8_t* sB = sA + kATileBytes;
+              if (issue) {
+                if (MODE == MODE_W) {
+                  const int px0 = (wi.kb0 + kb + j) * kBlockK;
+                  tma_load_2d(sA, &tmap_d, &full_bar[s], wi.m0, px0);
+                  tma_load_2d(sA + kATileBytes / 2, &tmap_d, &full_bar[s], wi.m0 + 64, px0);
+                  const int imgk = px0 >> (p.rW_log2 + p.rH_log2);
+                  const int hk = (px0 >> p.rW_log2) & (rH - 1);
 #pragma unroll
-              for (int j = 0; j < BLOCK_N / 64; ++j)
-                tma_load_2d(sB + j * 8192, &tmap_d, &full_bar[s], wi.n0 + 64 * j, tap * p.gC + cc * kBlockK);
-            } else {
-              tma_load_2d(sB, &tmap_d, &full_bar[s], cc * kBlockK, tap * p.Cn + wi.n0);
+                  for (int jj = 0; jj < BLOCK_N / 64; ++jj)
+                    tma_load_4d(sB + jj * 8192, &tmap_g, &full_bar[s], wi.n0 + 64 * jj, kw_w - 1, 2 * hk + kh_w - 1, imgk);
+                } else {
+                  int tap;
+                  if (MODE == MODE_F) {
+                    tma_load_4d(sA, &tmap_g, &full_bar[s], cc * kBlockK, tb - 1, 2 * h0 + ta - 1, img0);
+                    tap = ta * 5 + tb;
+                  } else {
+                    // out[2q+p] takes x[q + (p - i)] through tap k = 2i (p = 1) or 2i+1 (p = 0)
+                    tma_load_4d(sA, &tmap_g, &full_bar[s], cc * kBlockK, wi.pw - tb, h0 + wi.ph - ta, img0);
+                    const int kh = wi.ph ? 2 * ta : 2 * ta + 1;
+                    const int kw = wi.pw ? 2 * tb : 2 * tb + 1;
+                    tap = kh * 5 + kw;
+                  }
+                  if (p.b_mn) {  // TensorFlow layout [tap][Ck][Cn]: 64(k) x 64(n) boxes, one per 64 output channels
+#pragma unroll
+                    for (int jj = 0; jj < BLOCK_N / 64; ++jj)
+                      tma_load_2d(sB + jj * 8192, &tmap_d, &full_bar[s], wi.n0 + 64 * jj, tap * p.gC + cc * kBlockK);
+                  } else {
+                    tma_load_2d(sB, &tmap_d, &full_bar[s], cc * kBlockK, tap * p.Cn + wi.n0);
+                  }
+                }
+              }
+              if (MODE != MODE_W) { if (++cc == cpt) { cc = 0; if (++tb == nb) { tb = 0; ++ta; } } }
             }
-          }
           }
           __syncwarp();
-          if (MODE != MODE_W) { if (++cc == cpt) { cc = 0; if (++tb == nb) { tb = 0; ++ta; } } }
           if (++s == STAGES) { s = 0; phase ^= 1; }
         }
       }
@@ -291,19 +301,25 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
         T_ADD(tm_tmem, tt0);
         tc_fence_after();
         const uint32_t tacc = tmem_base + (uint32_t)(a * BLOCK_N);
-        for (int kb = 0; kb < wi.nkb; ++kb) {
+        for (int kb = 0; kb < wi.nkb; kb += KPS) {
+          const int nsub = (wi.nkb - kb) < KPS ? (wi.nkb - kb) : KPS;
           const long long tf0 = T_NOW();
           if (!mbar_wait(&full_bar[s], phase, abort_flag, p.err_flag)) { ok = false; break; }
           T_ADD(tm_full, tf0); ++tm_n;
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + s * L::kStageBytes);
-          const uint32_t a_lo = smem_desc_lo(a_addr, lbo);
-          const uint32_t b_lo = smem_desc_lo(a_addr + kATileBytes, lbo_b);
           if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k)
-              umma_bf16(tacc, smem_desc_join(hi_a, a_lo + k * kstep), smem_desc_join(hi_b, b_lo + k * kstep_b), idesc,
-                        (kb | k) != 0 ? 1u : 0u);
+            for (int j = 0; j < KPS; ++j) {
+              if (j < nsub) {
+                const uint32_t a_lo = smem_desc_lo(a_addr + j * L::kSubBytes, lbo);
+                const uint32_t b_lo = smem_desc_lo(a_addr + j * L::kSubBytes + kATileBytes, lbo_b);
+#pragma unroll
+                for (int k = 0; k < kBlockK / 16; ++k)
+                  umma_bf16(tacc, smem_desc_join(hi_a, a_lo + k * kstep), smem_desc_join(hi_b, b_lo + k * kstep_b),
+                            idesc, (kb | j | k) != 0 ? 1u : 0u);
+              }
+            }
             umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs retire
           }
           __syncwarp();
@@ -769,10 +785,10 @@ int g_stage_override = 0;  // 0 = deepest ring that fits
 // (barrier wait, fences, descriptor set-up, commit) per ring slot, more than the tensor work of a slot for tiles of
 // 64 or 128 columns (128 / 256 cycles), so those run two CTAs per SM -- two independent issue streams -- with half
 // the ring depth each; 256-column tiles (512 cycles per slot, all of TMEM) run one.
-template <int MODE, int BLOCK_N, int STAGES, int MINB>
+template <int MODE, int BLOCK_N, int STAGES, int MINB, int KPS = 1>
 int launch2(const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p, cudaStream_t stream) {
-  using L = Smem2<BLOCK_N, STAGES>;
-  auto kern = igemm2_kernel<MODE, BLOCK_N, STAGES, MINB>;
+  using L = Smem2<BLOCK_N, STAGES, KPS>;
+  auto kern = igemm2_kernel<MODE, BLOCK_N, STAGES, MINB, KPS>;
   static bool attr_done[64] = {false};  // per instantiation and device
   const int dev = current_device();
   if (dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
@@ -802,7 +818,10 @@ template <int MODE>
 int dispatch2(int block_n, const CUtensorMap& tg, const CUtensorMap& td, const Igemm2Params& p, cudaStream_t st) {
   const bool deep = g_stage_override == 2;  // one CTA per SM with the deepest ring that fits (A/B runs)
   switch (block_n) {
-    case 64: return deep ? launch2<MODE, 64, 8, 1>(tg, td, p, st) : launch2<MODE, 64, 4, 2>(tg, td, p, st);
+    case 64:
+      // variant 1 (or stage mode 3 for A/B runs): two k-blocks per ring slot, two slots, still two CTAs per SM
+      if (p.variant == 1 || g_stage_override == 3) return launch2<MODE, 64, 2, 2, 2>(tg, td, p, st);
+      return deep ? launch2<MODE, 64, 8, 1>(tg, td, p, st) : launch2<MODE, 64, 4, 2>(tg, td, p, st);
     case 128: return deep ? launch2<MODE, 128, 6, 1>(tg, td, p, st) : launch2<MODE, 128, 3, 2>(tg, td, p, st);
     case 256: return launch2<MODE, 256, 4, 1>(tg, td, p, st);
     default: return DCGAN_ERR_SHAPE;
@@ -901,7 +920,7 @@ static bool plan_key(int kind, int NB, int H, int W, int Cin, int Cout, uint64_t
          ((uint64_t)Cout << 49);
   return true;
 }
-int igemm2_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit) {
+int igemm2_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit, int variant) {
   uint64_t key;
   if (!plan_key(kind, NB, H, W, Cin, Cout, &key)) return DCGAN_ERR_SHAPE;
   std::lock_guard<std::mutex> lock(g_plan_mu);
@@ -909,18 +928,21 @@ int igemm2_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block
     g_plan_table.erase(key);
     return 0;
   }
-  if ((block_n != 64 && block_n != 128 && block_n != 256) || ksplit < 1 || ksplit > 16) return DCGAN_ERR_SHAPE;
-  g_plan_table[key] = std::make_pair(block_n, ksplit);
+  if ((block_n != 64 && block_n != 128 && block_n != 256) || ksplit < 1 || ksplit > 16 || variant < 0 ||
+      variant > 1 || (variant == 1 && block_n != 64))
+    return DCGAN_ERR_SHAPE;
+  g_plan_table[key] = std::make_pair(block_n, ksplit | (variant << 8));
   return 0;
 }
-static bool plan_lookup(int kind, int NB, int H, int W, int Cin, int Cout, int* block_n, int* ksplit) {
+static bool plan_lookup(int kind, int NB, int H, int W, int Cin, int Cout, int* block_n, int* ksplit, int* variant) {
   uint64_t key;
   if (g_force_ksplit2 > 0 || g_pref_bn > 0 || !plan_key(kind, NB, H, W, Cin, Cout, &key)) return false;
   std::lock_guard<std::mutex> lock(g_plan_mu);
   auto it = g_plan_table.find(key);
   if (it == g_plan_table.end()) return false;
   *block_n = it->second.first;
-  *ksplit = it->second.second;
+  *ksplit = it->second.second & 0xff;
+  *variant = it->second.second >> 8;
   return true;
 }
 
@@ -1010,11 +1032,12 @@ int igemm2_conv(int transposed, const void* x, const void* w, const float* bias,
   const double avg_kb = transposed ? 6.25 * cpt : 25.0 * cpt;
   p.num_kb = transposed ? 0 : 25 * cpt;
   int ks;
-  int tuned_bn, tuned_ks;
-  if (block_n <= 0 && plan_lookup(transposed ? MODE_T : MODE_F, NB, H, W, Cin, Cout, &tuned_bn, &tuned_ks) &&
+  int tuned_bn, tuned_ks, tuned_var;
+  if (block_n <= 0 && plan_lookup(transposed ? MODE_T : MODE_F, NB, H, W, Cin, Cout, &tuned_bn, &tuned_ks, &tuned_var) &&
       Cout % tuned_bn == 0 && tuned_ks <= min_kb) {
     block_n = tuned_bn;
     ks = tuned_ks;
+    p.variant = tuned_var;
   } else {
     igemm2_plan((long)mt * (Cout / 64) * classes, avg_kb, Cout, min_kb, block_n > 0 ? block_n : 0, &block_n, &ks);
   }
@@ -1061,11 +1084,12 @@ int igemm2_wgrad(const void* big, const void* small, float* dw, int NB, int Hs, 
     if (Cg % block_n) return DCGAN_ERR_SHAPE;
     ks = splits < total_kb ? splits : total_kb;
   } else {
-    int tuned_bn, tuned_ks;
-    if (block_n <= 0 && plan_lookup(MODE_W, NB, Hs, Ws, Cg, Cd, &tuned_bn, &tuned_ks) && Cg % tuned_bn == 0 &&
+    int tuned_bn, tuned_ks, tuned_var;
+    if (block_n <= 0 && plan_lookup(MODE_W, NB, Hs, Ws, Cg, Cd, &tuned_bn, &tuned_ks, &tuned_var) && Cg % tuned_bn == 0 &&
         tuned_ks <= total_kb) {
       block_n = tuned_bn;
       ks = tuned_ks;
+      p.variant = tuned_var;
     } else {
       igemm2_plan((long)25 * (Cd / kBlockM) * (Cg / 64), (double)total_kb, Cg, total_kb, block_n > 0 ? block_n : 0,
                   &block_n, &ks);

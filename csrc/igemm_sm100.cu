@@ -907,8 +907,8 @@ void dcgan_set_igemm_max_ctas(int v) { igemm2_set_max_ctas(v); }
 void dcgan_set_igemm_stage_mode(int v) { igemm2_set_stage_mode(v); }
 void dcgan_set_igemm_tile(int v) { igemm2_set_tile(v); }
 int dcgan_get_igemm_ksplit(void) { return igemm2_forced_ksplit(); }
-int dcgan_igemm_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit) {
-  return igemm2_plan_set(kind, NB, H, W, Cin, Cout, block_n, ksplit);
+int dcgan_igemm_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit, int variant) {
+  return igemm2_plan_set(kind, NB, H, W, Cin, Cout, block_n, ksplit, variant);
 }
 void dcgan_set_igemm_debug(long long* ptr) { igemm2_set_debug(ptr); }
 int dcgan_set_workspace(void* ptr, size_t bytes) { return igemm2_set_workspace(ptr, bytes); }

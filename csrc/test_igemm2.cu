@@ -258,10 +258,13 @@ static void time_layers(bool sweep) {
     const float t_new = time_us([&] { rc |= run(0, 0); }, 20);
     dcgan_set_igemm_stage_mode(2);  // one CTA per SM, deepest ring
     const float t_deep = time_us([&] { rc |= run(0, 0); }, 20);
+    dcgan_set_igemm_stage_mode(3);  // 64-column tiles, two k-blocks per slot
+    const float t_k2 = time_us([&] { rc |= run(64, l.kind == 2 ? 0 : 0); }, 20);
     dcgan_set_igemm_stage_mode(0);
+    const float t_64 = time_us([&] { rc |= run(64, 0); }, 20);
     const double fl = layer_flops(l);
-    printf("[TIME] %s  gen1 %7.1f us (%6.1f TF/s)   gen2 %7.1f us (%6.1f TF/s)   x%.2f   gen2 with one CTA per SM: %.1f us  rc=%d err=%d\n",
-           l.name, t_old, fl / t_old * 1e-6, t_new, fl / t_new * 1e-6, t_old / t_new, t_deep, rc, dcgan_last_device_error());
+    printf("[TIME] %s  gen1 %7.1f us (%6.1f TF/s)   gen2 %7.1f us (%6.1f TF/s)   x%.2f   gen2 with one CTA per SM: %.1f us   bn64: %.1f us, bn64 two k-blocks per slot: %.1f us  rc=%d err=%d\n",
+           l.name, t_old, fl / t_old * 1e-6, t_new, fl / t_new * 1e-6, t_old / t_new, t_deep, t_64, t_k2, rc, dcgan_last_device_error());
 #ifdef IGEMM2_TIMING
     {  // per-role cycle counters of one launch (bring-up builds only)
       long long* dbg; CK(cudaMalloc(&dbg, 296 * 16 * 8)); CK(cudaMemset(dbg, 0, 296 * 16 * 8));
@@ -364,6 +367,24 @@ int main(int argc, char** argv) {
     dcgan_set_igemm_stage_mode(2);  // one CTA per SM, deep rings
     fails += test_fprop(2, 16, 16, 128, 128, 128, 1, 1, false);
     fails += test_tconv(2, 8, 8, 64, 64, 64, 1, false);
+    dcgan_set_igemm_stage_mode(3);  // 64-column tiles with two k-blocks per ring slot (odd and even k-block counts,
+                                    // split-K slices that end inside a slot, several items per CTA)
+    fails += test_fprop(2, 16, 16, 128, 128, 64, 1, 1, false);
+    fails += test_fprop(4, 16, 16, 64, 128, 64, 1, 1, true);
+    fails += test_tconv(2, 8, 8, 64, 128, 64, 1, false);
+    fails += test_tconv(2, 8, 8, 128, 64, 64, 1, false);
+    fails += test_wgrad(8, 16, 16, 64, 128, 5, 64, 7, 2);
+    fails += test_wgrad(2, 8, 8, 128, 128, 3, 64, 1, 2);
+    dcgan_set_igemm_max_ctas(3);
+    fails += test_fprop(2, 16, 16, 128, 128, 64, 1, 1, false);
+    fails += test_tconv(2, 8, 8, 64, 128, 64, 1, false);
+    dcgan_set_igemm_max_ctas(0);
+    for (int ks : {2, 3, 5}) {
+      dcgan_set_igemm_ksplit(ks);
+      fails += test_fprop(2, 16, 16, 128, 128, 64, 1, 1, false);
+      fails += test_tconv(2, 8, 8, 128, 64, 64, 1, false);
+    }
+    dcgan_set_igemm_ksplit(0);
     dcgan_set_igemm_stage_mode(0);
     printf("small shapes: %d failing tests\n", fails);
     if (!quick) {

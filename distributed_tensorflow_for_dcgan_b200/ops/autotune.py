@@ -24,12 +24,12 @@ from . import _lib
 KIND_F, KIND_T, KIND_W = 0, 1, 2
 enabled = os.environ.get("DCGAN_AUTOTUNE", "1") != "0"
 verbose = os.environ.get("DCGAN_AUTOTUNE_VERBOSE", "0") != "0"
-_done: Dict[Tuple[int, int, int, int, int, int], Tuple[int, int, float]] = {}
+_done: Dict[Tuple[int, int, int, int, int, int], Tuple[int, int, int, float]] = {}
 _busy = False
 
 
-def plans() -> Dict[Tuple[int, int, int, int, int, int], Tuple[int, int, float]]:
-    """(kind, N, H, W, Cin, Cout) -> (block_n, ksplit, microseconds) of every shape tuned so far."""
+def plans() -> Dict[Tuple[int, int, int, int, int, int], Tuple[int, int, int, float]]:
+    """(kind, N, H, W, Cin, Cout) -> (block_n, ksplit, variant, microseconds) of every shape tuned so far."""
     return dict(_done)
 
 
@@ -61,7 +61,7 @@ def ensure(kind: int, N: int, H: int, W: int, Cin: int, Cout: int) -> None:
     if not hasattr(lib, "dcgan_igemm_plan_set"):
         return
     # a global override is active (A/B runs, tests): the table would not be consulted, and tuning must not disturb it
-    if (lib.dcgan_get_igemm_ksplit() != 0 or os.environ.get("DCGAN_IGEMM_TILE")
+    if (lib.dcgan_get_igemm_ksplit() != 0 or os.environ.get("DCGAN_IGEMM_TILE") or os.environ.get("DCGAN_IGEMM_STAGE_MODE")
             or (int(os.environ.get("DCGAN_IGEMM_TUNING", "1")) & 128)):
         return
     _busy = True
@@ -69,13 +69,14 @@ def ensure(kind: int, N: int, H: int, W: int, Cin: int, Cout: int) -> None:
         best = _tune(lib, kind, N, H, W, Cin, Cout)
     finally:
         lib.dcgan_set_igemm_ksplit(0)
+        lib.dcgan_set_igemm_stage_mode(0)
         _busy = False
     _done[key] = best
     if best[0] > 0:
-        lib.dcgan_igemm_plan_set(kind, N, H, W, Cin, Cout, best[0], best[1])
+        lib.dcgan_igemm_plan_set(kind, N, H, W, Cin, Cout, best[0], best[1], best[2])
     if verbose:
         print(f"[autotune] kind {kind} N {N} HxW {H}x{W} Cin {Cin} Cout {Cout}: block_n {best[0]} ksplit {best[1]} "
-              f"{best[2]:.1f} us", flush=True)
+              f"variant {best[2]} {best[3]:.1f} us", flush=True)
 
 
 def _tune(lib, kind, N, H, W, Cin, Cout):
@@ -84,17 +85,18 @@ def _tune(lib, kind, N, H, W, Cin, Cout):
     g = torch.Generator(device=f"cuda:{dev}").manual_seed(1)
     rnd = lambda *shape: (torch.rand(*shape, generator=g, device=f"cuda:{dev}") - 0.5).to(torch.bfloat16)
     if Cin % 64 or Cout % 64:
-        return (0, 0, 0.0)
+        return (0, 0, 0, 0.0)
     if kind == KIND_W:
         if Cout % 128 or (N * H * W) % 64:
-            return (0, 0, 0.0)
+            return (0, 0, 0, 0.0)
         big, small = rnd(N, 2 * H, 2 * W, Cin), rnd(N, H, W, Cout)
         dw = torch.zeros(25, Cin, Cout, device=f"cuda:{dev}")
         total_kb = N * H * W // 64
-        cands = [(bn, ks) for bn in (64, 128, 256) if Cin % bn == 0 for ks in (1, 2, 3, 4, 6, 8, 12, 16)
-                 if ks <= total_kb]
+        cands = [(bn, ks, var) for bn in (64, 128, 256) if Cin % bn == 0 for ks in (1, 2, 3, 4, 6, 8, 12, 16)
+                 if ks <= total_kb for var in ((0, 1) if bn == 64 else (0,))]
 
-        def run(bn, ks):
+        def run(bn, ks, var):
+            lib.dcgan_set_igemm_stage_mode(3 if var else 0)
             _lib.call("dcgan_conv_wgrad", big.data_ptr(), small.data_ptr(), dw.data_ptr(), N, H, W, Cin, Cout, ks, bn)
     else:
         x = rnd(N, H, W, Cin)
@@ -103,23 +105,25 @@ def _tune(lib, kind, N, H, W, Cin, Cout):
         w = rnd(25, Cout, Cin) if transposed else rnd(25, Cin, Cout)
         out = torch.empty(N, oH, oW, Cout, **bf)
         min_kb = (4 if transposed else 25) * (Cin // 64)
-        cands = [(bn, ks) for bn in (64, 128, 256) if Cout % bn == 0 for ks in (1, 2, 3, 4, 6, 8) if ks <= min_kb]
+        cands = [(bn, ks, var) for bn in (64, 128, 256) if Cout % bn == 0 for ks in (1, 2, 3, 4, 6, 8) if ks <= min_kb
+                 for var in ((0, 1) if bn == 64 else (0,))]
         entry = "dcgan_conv_tconv" if transposed else "dcgan_conv_fprop_kn"
 
-        def run(bn, ks):
+        def run(bn, ks, var):
+            lib.dcgan_set_igemm_stage_mode(3 if var else 0)
             lib.dcgan_set_igemm_ksplit(ks)
             _lib.call(entry, x.data_ptr(), w.data_ptr(), None, out.data_ptr(), N, H, W, Cin, Cout, 0, bn)
     before = _lib.launch_count
-    best = (0, 0, float("inf"))
+    best = (0, 0, 0, float("inf"))
     try:
-        for bn, ks in cands:
+        for bn, ks, var in cands:
             try:
-                t = _time_us(lambda: run(bn, ks))
+                t = _time_us(lambda: run(bn, ks, var))
             except _lib.KernelError:
                 continue
-            if t < best[2] * 0.985:  # a later candidate has to win by more than the timer's noise
-                best = (bn, ks, t)
+            if t < best[3] * 0.985:  # a later candidate has to win by more than the timer's noise
+                best = (bn, ks, var, t)
     finally:
         _lib.launch_count = before  # tuning launches are not part of anybody's step
     torch.cuda.synchronize()
-    return best if best[0] > 0 else (0, 0, 0.0)
+    return best if best[0] > 0 else (0, 0, 0, 0.0)

@@ -52,7 +52,8 @@ void dcgan_set_pdl(int v);
  * only act on the first generation: bit 0 = two CTAs per SM (default on). */
 void dcgan_set_igemm_tuning(int v);
 /* Second-generation kernels: cap on the persistent grid (0 = every CTA slot of the device), ring configuration
- * (0 = default: two CTAs per SM for tiles of 64 / 128 columns; 2 = one CTA per SM with the deepest ring). */
+ * (0 = default: two CTAs per SM for tiles of 64 / 128 columns; 2 = one CTA per SM with the deepest ring; 3 = 64-column
+ * tiles with two k-blocks per ring slot). */
 void dcgan_set_igemm_max_ctas(int v);
 void dcgan_set_igemm_stage_mode(int v);
 /* Tile width (64 / 128 / 256 output channels) used wherever it divides the layer; 0 = the library's choice. */
@@ -60,9 +61,10 @@ void dcgan_set_igemm_tile(int v);
 /* Records the measured-best (tile width, split-K factor) of one layer shape; later calls of that shape which leave
  * both to the library (block_n = 0, splits = 0) use it instead of the cost model.  kind: 0 strided conv (fprop*),
  * 1 transposed conv (tconv*), 2 filter gradient (there H, W = the small grid, Cin = Cg, Cout = Cd).  block_n <= 0
- * forgets the entry.  ops/autotune.py fills the table by timing the candidates once per shape. */
+ * forgets the entry.  variant: 0 = default kernel of that width, 1 = two k-blocks per ring slot (64 columns only; what
+ * dcgan_set_igemm_stage_mode(3) forces globally).  ops/autotune.py fills the table by timing the candidates once per shape. */
 int dcgan_get_igemm_ksplit(void); /* the factor forced by dcgan_set_igemm_ksplit, 0 = none */
-int dcgan_igemm_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit);
+int dcgan_igemm_plan_set(int kind, int NB, int H, int W, int Cin, int Cout, int block_n, int ksplit, int variant);
 /* Bring-up only: per-CTA cycle counters [CTA][16] written by a library built with -DIGEMM2_TIMING (else ignored). */
 void dcgan_set_igemm_debug(long long* counters);
 /* Split-K scratch of the second-generation kernels for the calling host thread: `bytes` of device memory whose
