@@ -238,3 +238,97 @@ def test_pipelined_submit_matches_train_step(cuda_lib):
         assert dist(got[i], want[i]) < 0.5 * dist(got[i], wrong[i]), (i, got[i], want[i], wrong[i])
     with pytest.raises(ValueError):
         eng.result(0)
+
+
+def test_engine_layers_match_oracle_fed_with_engine_tensors(cuda_lib):
+    """Per-layer check that does not compound bf16 error across the nine layers: every conv layer's filter
+    gradient, data gradient and forward output are recomputed in fp32 PyTorch from the ENGINE'S OWN bf16 inputs of
+    that layer (activations, upstream gradients, bf16 filter shadows) and must agree to cos > 0.999 and
+    5e-2 of the maximum -- a wrong tap, a dropped parity class or a mis-ordered slab fails this by a wide margin."""
+    from distributed_tensorflow_for_dcgan_b200.engine import DCGANEngine
+    F = torch.nn.functional
+    cfg = ModelConfig(batch_size=64)
+    eng = DCGANEngine(cfg, seed=7)
+    B = cfg.batch_size
+    eng.real_f32.copy_(torch.rand(B, 64, 64, 3, device="cuda") * 2 - 1)
+    eng.z.copy_(torch.rand(B, cfg.z_dim, device="cuda") * 2 - 1)
+    eng.early_adam = False        # keep the filters of this step in place until the checks below have read them
+    # run the step without its optimizer so that weights, activations and gradients all belong to one iteration
+    real_adam = eng._adam_range
+    eng._adam_range = lambda lo, hi: None
+    try:
+        eng.step_body()
+    finally:
+        eng._adam_range = real_adam
+    torch.cuda.synchronize()
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    K.check_device_error()
+
+    def close(got, ref, what):
+        got, ref = got.float().flatten(), ref.float().flatten()
+        cos = F.cosine_similarity(got, ref, dim=0).item()
+        err = (got - ref).abs().max().item()
+        den = ref.abs().max().item()
+        assert cos > 0.999 and err <= 5e-2 * den, f"{what}: cos {cos} err {err} max {den}"
+
+    nchw = lambda t: t.float().permute(0, 3, 1, 2)
+    nhwc = lambda t: t.permute(0, 2, 3, 1)
+    g = eng.grad_views
+    # ---- discriminator: strided convs d_h1..d_h3 ------------------------------------------------------------
+    for i in (1, 2, 3):
+        ci, co = eng.d_ch[i], eng.d_ch[i + 1]
+        x = nchw(eng.d_act[i - 1])                                   # [2B, ci, H, W] the layer's bf16 input
+        w = eng.w_native[f"d_h{i}_conv/w"].float().view(5, 5, ci, co).permute(3, 2, 0, 1).contiguous()
+        xp = F.pad(x, (1, 2, 1, 2))
+        out = F.conv2d(xp, w, eng.params[f"d_h{i}_conv/biases"], stride=2)
+        close(eng.d_pre[i], nhwc(out), f"d_h{i} forward")
+        dy = nchw(eng.dd_pre[i])                                     # [3B, co, h, w] upstream (bf16, as the kernels saw it)
+        dw = torch.nn.grad.conv2d_weight(xp, w.shape, dy[:2 * B], stride=2)
+        close(g[f"d_h{i}_conv/w"].view(5, 5, ci, co), dw.permute(2, 3, 1, 0), f"d_h{i} filter gradient")
+        H = x.shape[2]
+        dx = F.conv_transpose2d(dy, w, stride=2)[:, :, 1:1 + H, 1:1 + H]   # gradient w.r.t. the unpadded input
+        # slab 2 of the input gradient belongs to the generator's loss: its upstream activations are the fake half
+        close(eng.dd_act[i - 1], nhwc(dx), f"d_h{i} data gradient")
+    # ---- generator: transposed convs g_h1..g_h3 ------------------------------------------------------------
+    for i in (1, 2, 3):
+        ci, co = eng.g_ch[i - 1], eng.g_ch[i]
+        x = nchw(eng.g_act[i - 1]).requires_grad_(True)              # [B, ci, H, W]
+        w = eng.w_native[f"g_h{i}/w"].float().view(5, 5, co, ci).permute(3, 2, 0, 1).contiguous().requires_grad_(True)
+        H = x.shape[2]
+        out = F.conv_transpose2d(x, w, stride=2)[:, :, 1:1 + 2 * H, 1:1 + 2 * H] + \
+            eng.params[f"g_h{i}/biases"].view(1, -1, 1, 1)
+        close(eng.g_pre[i], nhwc(out.detach()), f"g_h{i} forward")
+        out.backward(nchw(eng.dg_pre[i]))
+        close(g[f"g_h{i}/w"].view(5, 5, co, ci), w.grad.permute(2, 3, 1, 0), f"g_h{i} filter gradient")
+        close(eng.dg_act[i - 1], nhwc(x.grad), f"g_h{i} data gradient")
+
+
+def test_ordered_reductions_are_reproducible(cuda_lib):
+    """The filter gradients (split-K partial tiles summed in slice order; the 3-channel layers' per-CTA tiles summed
+    in CTA order) come out bit-identical when the same backward pass runs twice on the same tensors."""
+    from distributed_tensorflow_for_dcgan_b200.engine import DCGANEngine
+    cfg = ModelConfig(batch_size=64)
+    eng = DCGANEngine(cfg, seed=11)
+    B = cfg.batch_size
+    eng.real_f32.copy_(torch.rand(B, 64, 64, 3, device="cuda") * 2 - 1)
+    eng.z.copy_(torch.rand(B, cfg.z_dim, device="cuda") * 2 - 1)
+    eng.step_body()
+    torch.cuda.synchronize()
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    names = [f"d_h{i}_conv/w" for i in (1, 2, 3)] + [f"g_h{i}/w" for i in (1, 2, 3)] + ["d_h0_conv/w", "g_h4/w"]
+    runs = []
+    for _ in range(2):
+        eng.grads.zero_()
+        for i in (1, 2, 3):
+            K.conv_wgrad(eng.d_act[i - 1], eng.dd_pre[i][:2 * B],
+                         eng.grad_views[f"d_h{i}_conv/w"].view(25, eng.d_ch[i], eng.d_ch[i + 1]))
+            K.conv_wgrad(eng.dg_pre[i], eng.g_act[i - 1],
+                         eng.grad_views[f"g_h{i}/w"].view(25, eng.g_ch[i], eng.g_ch[i - 1]))
+        K.c3_wgrad(eng.d_in, eng.dd_pre[0][:2 * B], eng.grad_views["d_h0_conv/w"])
+        K.c3_wgrad(eng.dimg, eng.g_act[3], eng.grad_views["g_h4/w"])
+        torch.cuda.synchronize()
+        runs.append({n: eng.grad_views[n].clone() for n in names})
+    K.check_device_error()
+    for n in names:
+        assert runs[0][n].abs().max().item() > 0, n
+        assert torch.equal(runs[0][n], runs[1][n]), f"{n} differs between two runs"
