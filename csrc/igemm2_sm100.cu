@@ -8,10 +8,12 @@
 //     asymmetric SAME padding (1 before / 2 after) is the TMA unit's out-of-bounds zero fill (signed
 //     coordinates), and the stride-2 sampling of the forward conv is the tensor map's element stride {1,2,2,1}.
 //     One elected lane issues one bulk tensor copy per operand and k-block; no address arithmetic in the SM.
-//   * One CTA per SM loops over work items (tile x K slice) with a static round-robin schedule; the smem ring
+//   * Persistent CTAs loop over work items (tile x K slice) with a static round-robin schedule; the smem ring
 //     keeps streaming across tile boundaries, so a short K loop (8-18 k-blocks in the transposed layers) no
-//     longer pays barrier init / TMEM allocation / pipeline fill / epilogue per tile.
-//   * TMEM holds two accumulators (2 x BLOCK_N columns): warps 2-5 drain tile i (tcgen05.ld -> bias / activation /
+//     longer pays barrier init / TMEM allocation / pipeline fill / epilogue per tile.  Tiles of 64 / 128 columns run
+//     TWO CTAs per SM (half the ring each, see launch2): two independent MMA-issue streams hide each other's
+//     per-slot control flow; measured residency in profiles/igemm2_residency_r2.log.
+//   * TMEM holds two accumulators per CTA (2 x BLOCK_N columns): warps 2-5 drain tile i (tcgen05.ld -> bias / activation /
 //     batch-norm moments -> bf16 stores) while warp 1 already issues the MMAs of tile i+1.
 //   * Split-K is deterministic: every slice stores its f32 partial tile to a scratch buffer, bumps the tile's
 //     arrival counter, and the slice that arrives last adds all partials in slice order and runs the epilogue.
@@ -41,13 +43,13 @@ namespace {
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;
 constexpr int kATileBytes = kBlockM * kBlockK * 2;  // 16 KiB
-// Bulk tensor loads issued by ONE warp are processed one after the other (~285 ns each whatever their size; chip-wide
-// 8.2 TB/s with one issuing warp per CTA, 16.3 with two, 19.4 with four -- profiles/tma_issue_microbench.log), so the
-// ring slots are dealt to kNumProducers producer warps.  A slot always belongs to the same warp (slot % kNumProducers):
-// its waits on that slot's barrier then come in phase order (a warp that skipped a phase could not tell "two phases
-// done" from "none" by parity).
+// The ring slots can be dealt to several producer warps (a stand-alone TMA-only loop during bring-up moved ~2x the
+// bytes with two issuing warps per CTA; that microbenchmark is not kept).  A slot always belongs to the same warp
+// (slot % kNumProducers): its waits on that slot's barrier then come in phase order (a warp that skipped a phase
+// could not tell "two phases done" from "none" by parity).  In the real kernels a second producer warp gains nothing
+// once two CTAs share an SM (profiles/igemm2_two_producers_r2.log vs profiles/igemm2_harness_r2.log), so it is off.
 #ifndef IGEMM2_PRODUCERS
-#define IGEMM2_PRODUCERS 1  // measured: a second producer warp gains nothing once two CTAs share an SM
+#define IGEMM2_PRODUCERS 1
 #endif
 constexpr int kNumProducers = IGEMM2_PRODUCERS;
 // -DIGEMM2_TIMING: per-role cycle counters written to Igemm2Params::dbg ([CTA][16] long long), bring-up only

@@ -73,6 +73,13 @@ int dcgan_copy_error_flag(int* host_dst, cudaStream_t stream) {
              ? 0 : DCGAN_ERR_LAUNCH;
 }
 
+// Stream-ordered zero fill: one memset node when captured into a CUDA graph (the gradient / reduction buffers of the
+// training step), instead of a fill kernel launch.
+int dcgan_zero_async(void* ptr, size_t bytes, cudaStream_t stream) {
+  if (!ptr || bytes == 0) return 0;
+  return cudaMemsetAsync(ptr, 0, bytes, stream) == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
 void dcgan_set_mn_desc_variant(int v) { cudaMemcpyToSymbol(dcgan::g_mn_desc_variant, &v, sizeof(int)); }
 
 }  // extern "C"

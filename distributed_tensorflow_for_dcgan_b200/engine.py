@@ -211,6 +211,7 @@ class DCGANEngine:
             self.fuse_bn &= ~3
         self._grid_barrier = torch.zeros(2, dtype=torch.int32, device=self.device)
         self.early_adam = os.environ.get("DCGAN_EARLY_ADAM", "1") != "0"
+        self.memset_nodes = os.environ.get("DCGAN_MEMSET_NODES", "1") != "0"  # cudaMemsetAsync instead of fill kernels
         self.prioritize_main = os.environ.get("DCGAN_MAIN_PRIORITY", "1") != "0"
         self.split_d_forward = self.wgrad_overlap and os.environ.get("DCGAN_SPLIT_D_FORWARD", "0") != "0"
         self.side = torch.cuda.Stream(self.device)
@@ -546,9 +547,14 @@ class DCGANEngine:
     def _step_body(self) -> None:
         B = self.B
         # gradients are not touched before the backward pass: their memset runs beside the forward pass
-        with self._off_critical_path():
-            self.grads.zero_()
-        self._scratch.zero_()
+        if self.memset_nodes:
+            with self._off_critical_path():
+                K.zero_(self.grads)
+            K.zero_(self._scratch)
+        else:
+            with self._off_critical_path():
+                self.grads.zero_()
+            self._scratch.zero_()
         deferred_g = (self.update_mode == "simultaneous" and self.comm is not None
                       and getattr(self.comm, "overlap", False) and getattr(self.comm, "deferred_g", False))
         if deferred_g:  # async mode: the previous step's generator gradients are pushed under this step's passes

@@ -63,6 +63,7 @@ _SIGNATURES = {
     "dcgan_comm_async_apply": "ppppppppiizzziffffis",
     "dcgan_bn_forward_static": "pppppppiiiffis",
     "dcgan_copy_error_flag": "ps",
+    "dcgan_zero_async": "pzs",
 }
 _KIND = {"p": c_void_p, "i": c_int, "f": c_float, "z": c_size_t, "s": c_void_p}
 

@@ -279,6 +279,14 @@ def colsum(x2d, out):
     return out
 
 
+def zero_(t):
+    """Stream-ordered zero fill of a contiguous tensor (a memset node under graph capture, not a fill kernel)."""
+    assert t.is_contiguous()
+    call("dcgan_zero_async", ptr(t), t.numel() * t.element_size())
+    _lib.launch_count -= 1  # not a kernel launch
+    return t
+
+
 def decode_f64(src, dst, scale=1.0, shift=0.0):
     call("dcgan_decode_f64", ptr(src), ptr(dst), src.numel(), scale, shift)
     return dst

@@ -38,6 +38,8 @@ int dcgan_last_device_error(void);
  * training loop fetches it with the losses of every step and stops when it is non-zero, so that a timed-out
  * peer wait -- which makes a rank skip its shard's update -- cannot go unnoticed. */
 int dcgan_copy_error_flag(int* host_dst, cudaStream_t stream);
+/* Stream-ordered zero fill of `bytes` bytes (cudaMemsetAsync: a memset node inside a captured graph). */
+int dcgan_zero_async(void* ptr, size_t bytes, cudaStream_t stream);
 
 /* Bring-up switch for the MN-major UMMA descriptor convention (0 = CuTe convention). */
 void dcgan_set_mn_desc_variant(int v);
