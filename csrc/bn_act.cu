@@ -476,7 +476,7 @@ int dcgan_bn_stats(const void* x, float* sums, int groups, int rows_per_group, i
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  launch_k(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 0, st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
+  launch_k_light(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 0, st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
                                                                   rows_per_group, C, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
 }
@@ -487,7 +487,7 @@ int dcgan_bn_apply(const void* x, void* y, const float* sums, const float* gamma
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  launch_k(bn_apply_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, 
+  launch_k_light(bn_apply_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, 
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, saved,
       ema_mean, ema_var, rows_per_group, C, 1.0f / (float)rows_per_group, eps, decay, act, use_ema, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -499,7 +499,7 @@ int dcgan_bn_bwd_reduce(const void* da, const void* pre, const float* saved, con
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  launch_k(bn_bwd_reduce_kernel, dim3(grid), dim3(kBnThreads), 0, st, 
+  launch_k_light(bn_bwd_reduce_kernel, dim3(grid), dim3(kBnThreads), 0, st, 
       reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(pre), saved, gamma, beta,
       red, rows_per_group, C, stat_groups, act, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -511,7 +511,7 @@ int dcgan_bn_bwd_apply(const void* da, const void* pre, void* dpre, const float*
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  launch_k(bn_bwd_apply_kernel, dim3(grid), dim3(kBnThreads), 6 * C * sizeof(float), st, 
+  launch_k_light(bn_bwd_apply_kernel, dim3(grid), dim3(kBnThreads), 6 * C * sizeof(float), st, 
       reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(pre),
       reinterpret_cast<__nv_bfloat16*>(dpre), saved, gamma, beta, red, dgamma, dbeta, rows_per_group, C,
       stat_groups, param_groups, 1.0f / (float)rows_per_group, act, rpb);
@@ -529,7 +529,7 @@ int dcgan_bn_forward_fused(const void* x, void* y, float* sums, const float* gam
   if (chunks < 1) return DCGAN_ERR_LAUNCH;
   int* err = error_flag_ptr();
   if (!err) return DCGAN_ERR_DRIVER;
-  launch_k(bn_forward_fused_kernel, dim3(groups * chunks), dim3(kBnThreads), 0, st,
+  launch_k_light(bn_forward_fused_kernel, dim3(groups * chunks), dim3(kBnThreads), 0, st,
            reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, saved,
            ema_mean, ema_var, groups, rows_per_group, C, eps, decay, act, rpb, chunks, barrier, err);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -546,7 +546,7 @@ int dcgan_bn_backward_fused(const void* da, const void* pre, void* dpre, const f
   if (chunks < 1) return DCGAN_ERR_LAUNCH;
   int* err = error_flag_ptr();
   if (!err) return DCGAN_ERR_DRIVER;
-  launch_k(bn_backward_fused_kernel, dim3(groups * chunks), dim3(kBnThreads), 0, st,
+  launch_k_light(bn_backward_fused_kernel, dim3(groups * chunks), dim3(kBnThreads), 0, st,
            reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(pre),
            reinterpret_cast<__nv_bfloat16*>(dpre), saved, gamma, beta, red, dgamma, dbeta, groups, stat_groups,
            param_groups, rows_per_group, C, act, rpb, chunks, barrier, err);
@@ -558,7 +558,7 @@ int dcgan_act_bwd(const void* da, const void* a, void* dpre, float* dbias, int r
   if (C % 8 || C / 8 > kBnThreads) return DCGAN_ERR_SHAPE;
   const int rpb = pick_rows_per_block(rows, C, 1);
   dim3 grid((rows + rpb - 1) / rpb);
-  launch_k(act_bwd_kernel, dim3(grid), dim3(kBnThreads), 0, st, 
+  launch_k_light(act_bwd_kernel, dim3(grid), dim3(kBnThreads), 0, st, 
       reinterpret_cast<const __nv_bfloat16*>(da), reinterpret_cast<const __nv_bfloat16*>(a),
       reinterpret_cast<__nv_bfloat16*>(dpre), dbias, rows, a_rows, C, act, bias_rows, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
@@ -637,10 +637,10 @@ extern "C" int dcgan_bn_forward_static(const void* x, void* y, const float* gamm
   if (cudaMemsetAsync(sums, 0, need * sizeof(float), st) != cudaSuccess) return DCGAN_ERR_LAUNCH;
   const int rpb = pick_rows_per_block(rows_per_group, C, groups);
   dim3 grid((rows_per_group + rpb - 1) / rpb, groups);
-  launch_k(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 0, st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
+  launch_k_light(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 0, st, reinterpret_cast<const __nv_bfloat16*>(x), sums,
                                                                   rows_per_group, C, rpb);
   if (cudaGetLastError() != cudaSuccess) return DCGAN_ERR_LAUNCH;
-  launch_k(bn_apply_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, 
+  launch_k_light(bn_apply_kernel, dim3(grid), dim3(kBnThreads), 2 * C * sizeof(float), st, 
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, saved,
       ema_mean, ema_var, rows_per_group, C, 1.0f / (float)rows_per_group, eps, decay, act, 0, rpb);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;

@@ -27,15 +27,16 @@ int* mn_variant_ptr();       // host: device address of the MN-major descriptor 
 // global memory (pdl_wait), so barrier init / TMEM allocation / shared-memory setup of kernel N+1
 // overlap the tail wave of kernel N.  Without the launch attribute both instructions are no-ops.
 // ---------------------------------------------------------------------------------------------
-bool use_pdl();  // host: DCGAN_PDL env / dcgan_set_pdl()
+bool use_pdl();        // host: DCGAN_PDL=1 / dcgan_set_pdl(1): every hot-path kernel
+bool use_pdl_light();  // host: DCGAN_PDL=2 (or 1): only the light kernels (batch norm, heads, linear, casts)
 __device__ __forceinline__ void pdl_launch_dependents() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
-                            Args&&... args) {
+inline cudaError_t launch_k_attr(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                 cudaStream_t st, Args&&... args) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -45,8 +46,20 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = use_pdl() ? 1 : 0;
+  cfg.numAttrs = pdl ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                            Args&&... args) {
+  return launch_k_attr(use_pdl(), kern, grid, block, smem, st, static_cast<Args&&>(args)...);
+}
+// Light kernels (a few warps and KB per CTA): launched early they wait inside griddepcontrol.wait without taking
+// the SM slots that the side stream's kernels need -- unlike the persistent conv kernels, which would.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k_light(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                  Args&&... args) {
+  return launch_k_attr(use_pdl_light(), kern, grid, block, smem, st, static_cast<Args&&>(args)...);
 }
 
 enum DeviceError : int {

@@ -451,7 +451,7 @@ int dcgan_lin_fwd(const float* z, const void* W, const float* bias, void* out, i
                   cudaStream_t st) {
   if (F % 2) return DCGAN_ERR_SHAPE;
   dim3 grid((F / 2 + 127) / 128, (NB + kLinTile - 1) / kLinTile);
-  launch_k(lin_fwd_kernel, dim3(grid), dim3(128), kLinTile * K * sizeof(float), st, z, reinterpret_cast<const __nv_bfloat16*>(W),
+  launch_k_light(lin_fwd_kernel, dim3(grid), dim3(128), kLinTile * K * sizeof(float), st, z, reinterpret_cast<const __nv_bfloat16*>(W),
                                                                   bias, reinterpret_cast<__nv_bfloat16*>(out), NB,
                                                                   K, F);
   return LAUNCH_OK();
@@ -461,7 +461,7 @@ int dcgan_lin_wgrad(const float* z, const void* dy, float* dW, float* dbias, int
                     cudaStream_t st) {
   if ((size_t)NB * 20 * sizeof(float) > 48 * 1024) return DCGAN_ERR_SHAPE;
   dim3 grid((F + 127) / 128, (K + 19) / 20);
-  launch_k(lin_wgrad_kernel, dim3(grid), dim3(128), NB * 20 * sizeof(float), st, z, reinterpret_cast<const __nv_bfloat16*>(dy), dW,
+  launch_k_light(lin_wgrad_kernel, dim3(grid), dim3(128), NB * 20 * sizeof(float), st, z, reinterpret_cast<const __nv_bfloat16*>(dy), dW,
                                                                dbias, NB, K, F);
   return LAUNCH_OK();
 }
@@ -469,13 +469,13 @@ int dcgan_lin_wgrad(const float* z, const void* dy, float* dW, float* dbias, int
 int dcgan_head_fwd(const void* h, const float* w, const float* b, float* logits, int rows, int F,
                    cudaStream_t st) {
   if (F % 8) return DCGAN_ERR_SHAPE;
-  launch_k(head_fwd_kernel, dim3(rows), dim3(256), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w, b, logits, F);
+  launch_k_light(head_fwd_kernel, dim3(rows), dim3(256), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w, b, logits, F);
   return LAUNCH_OK();
 }
 
 int dcgan_gan_loss(const float* logits, float* losses, float* dlogit, float* probs, long long* counters, int B,
                    float grad_div, int advance, cudaStream_t st) {
-  launch_k(gan_loss_kernel, dim3(1), dim3(256), 0, st, logits, losses, dlogit, probs, counters, B, grad_div, advance);
+  launch_k_light(gan_loss_kernel, dim3(1), dim3(256), 0, st, logits, losses, dlogit, probs, counters, B, grad_div, advance);
   return LAUNCH_OK();
 }
 
@@ -484,7 +484,7 @@ int dcgan_head_bwd(const void* h, const float* w, const float* dlogit, void* dh,
   if (F % 8) return DCGAN_ERR_SHAPE;
   const int threads_needed = F / 8;
   dim3 grid((threads_needed + 127) / 128, (3 * B + kHeadBwdChunk - 1) / kHeadBwdChunk);
-  launch_k(head_bwd_kernel<false>, dim3(grid), dim3(128), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w,
+  launch_k_light(head_bwd_kernel<false>, dim3(grid), dim3(128), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w,
            dlogit, reinterpret_cast<__nv_bfloat16*>(dh), dW, db, B, F, LossArgs{});
   return LAUNCH_OK();
 }
@@ -496,7 +496,7 @@ int dcgan_head_loss_bwd(const void* h, const float* w, const float* logits, floa
   const int threads_needed = F / 8;
   dim3 grid((threads_needed + 127) / 128, (3 * B + kHeadBwdChunk - 1) / kHeadBwdChunk);
   LossArgs la{logits, losses, dlogit, probs, counters, grad_div, advance};
-  launch_k(head_bwd_kernel<true>, dim3(grid), dim3(128), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w,
+  launch_k_light(head_bwd_kernel<true>, dim3(grid), dim3(128), 0, st, reinterpret_cast<const __nv_bfloat16*>(h), w,
            static_cast<const float*>(nullptr), reinterpret_cast<__nv_bfloat16*>(dh), dW, db, B, F, la);
   return LAUNCH_OK();
 }
@@ -547,7 +547,7 @@ int dcgan_decode_f64(const double* src, void* dst, size_t n, float scale, float 
 int dcgan_f32_to_bf16(const float* src, void* dst, size_t n, float scale, float shift, cudaStream_t st) {
   size_t blocks = (n + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  launch_k(f32_to_bf16_affine_kernel, dim3((unsigned)blocks), dim3(256), 0, st, src, reinterpret_cast<__nv_bfloat16*>(dst), n, scale,
+  launch_k_light(f32_to_bf16_affine_kernel, dim3((unsigned)blocks), dim3(256), 0, st, src, reinterpret_cast<__nv_bfloat16*>(dst), n, scale,
                                                               shift);
   return LAUNCH_OK();
 }

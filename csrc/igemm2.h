@@ -40,6 +40,9 @@ struct Igemm2Params {
   int bn_slab_out_rows;   // output rows (pixels) per slab
   int bn_stat_groups;     // slab g uses the statistics / pre-activations of group min(g, bn_stat_groups - 1)
   int bn_act;             // the layer's activation (ReLU / LeakyReLU)
+  int bn_act_only;        // the layer has no batch norm: bn_pre = its saved ACTIVATION, `out` receives dy = da * act'(a),
+                          // bn_red = its bias gradient [Cn] += column sums of dy over the first bn_bias_slabs slabs
+  int bn_bias_slabs;
   // optional elementwise pass after a grid-wide barrier (every tile stored, every sum complete): the batch-norm
   // forward apply of the layer this conv feeds (tail_kind 1; bn_gamma / bn_beta / bn_act are that layer's, `stats`
   // its sums) or the backward apply of the layer `out` is the activation gradient of (tail_kind 2, after bn_red)
@@ -74,6 +77,9 @@ struct BnRedArgs {  // see Igemm2Params::bn_*
   float* dgamma;
   float* dbeta;
   int param_slabs;
+  // activation-only layer below (no batch norm): see Igemm2Params::bn_act_only
+  int act_only;
+  int bias_slabs;
 };
 struct BnFwdArgs {  // batch-norm forward apply in the conv's launch; `stats` of igemm2_conv must be given
   void* act_out;

@@ -477,6 +477,22 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
               f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
             }
           }
+          if (do_bnred && p.bn_act_only) {
+            // the layer below has no batch norm (d_h0: bias + LeakyReLU): what is stored is already the gradient
+            // w.r.t. its pre-activation, dy = da * act'(a), with the sign taken from the saved activation
+            uint4 pv[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              pv[j] = valid ? __ldg(reinterpret_cast<const uint4*>(prow + c) + j) : make_uint4(0, 0, 0, 0);
+            const uint32_t* pw32 = reinterpret_cast<const uint32_t*>(pv);
+            const float neg = (p.bn_act == kActRelu) ? 0.f : (p.bn_act == kActLrelu ? 0.2f : 1.f);
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float2 a2 = unpack_bf16x2(pw32[j >> 1]);
+              f[j] = valid ? f[j] * (a2.x > 0.f ? 1.f : neg) : 0.f;
+              f[j + 1] = valid ? f[j + 1] * (a2.y > 0.f ? 1.f : neg) : 0.f;
+            }
+          }
           const long long ts0 = T_NOW();
           {
             uint32_t packed[16];
@@ -501,7 +517,10 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
           T_ADD(te_st, ts0);
           if (do_stats) {  // batch-norm moments of this tile, reduced over the warp's 32 rows
             float sq[32];
-            if (do_bnred) {
+            if (do_bnred && p.bn_act_only) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) sq[j] = 0.f;  // only the column sums of dy (the bias gradient) are wanted
+            } else if (do_bnred) {
               // dy = da * act'(gamma * xhat + beta) and dy * xhat instead of (x, x^2)
               uint4 pv[4];
 #pragma unroll
@@ -554,8 +573,11 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
         }
         if (do_stats) {
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          float* gs = (do_bnred ? p.bn_red : p.stats) + (size_t)(wi.m0 / p.stat_group_rows) * 2 * p.Cn + wi.n0;
-          for (int i = et; i < BLOCK_N && wi.m0 < p.rows_total; i += kEpiThreads) {
+          const int grp = wi.m0 / p.stat_group_rows;
+          float* gs = (do_bnred ? p.bn_red : p.stats) + (size_t)grp * 2 * p.Cn + wi.n0;
+          const bool act_only = do_bnred && p.bn_act_only;
+          if (act_only) gs = (grp < p.bn_bias_slabs) ? p.bn_red + wi.n0 : nullptr;  // bn_red = the bias gradient [Cn]
+          for (int i = et; i < BLOCK_N && wi.m0 < p.rows_total && gs != nullptr; i += kEpiThreads) {
             float t1 = 0.f, t2 = 0.f;
 #pragma unroll
             for (int ww = 0; ww < 4; ++ww) {
@@ -563,7 +585,7 @@ igemm2_kernel(const __grid_constant__ CUtensorMap tmap_g,  // gathered operand: 
               t2 += ssm[(ww * 2 + 1) * BLOCK_N + i];
             }
             atomicAdd(gs + i, t1);
-            atomicAdd(gs + p.Cn + i, t2);
+            if (!act_only) atomicAdd(gs + p.Cn + i, t2);
           }
         }
       } else {
@@ -1007,6 +1029,9 @@ int igemm2_conv(int transposed, const void* x, const void* w, const float* bias,
   if (bnred != nullptr) {
     // slabs are groups of whole images; every 128-row tile must lie inside one slab
     if (bnred->slabs < 1 || NB % bnred->slabs || ((NB / bnred->slabs) * rH * rW) % kBlockM) return DCGAN_ERR_SHAPE;
+    p.bn_act_only = bnred->act_only; p.bn_bias_slabs = bnred->bias_slabs;
+    if (bnred->act_only && (bnred->dpre != nullptr || bnred->bias_slabs < 0 || bnred->bias_slabs > bnred->slabs))
+      return DCGAN_ERR_SHAPE;
     p.bn_pre = bnred->pre; p.bn_saved = bnred->saved; p.bn_gamma = bnred->gamma; p.bn_beta = bnred->beta;
     p.bn_red = bnred->red; p.bn_stat_groups = bnred->stat_groups; p.bn_act = bnred->act;
     p.stat_group_rows = (NB / bnred->slabs) * rH * rW;

@@ -1062,7 +1062,7 @@ int dcgan_conv_tconv_bnred(const void* x, const void* w_nk, void* out, const voi
                            const float* gamma, const float* beta, float* red, int slabs, int stat_groups, int bn_act,
                            int NB, int H, int W, int Cin, int Cout, int block_n, cudaStream_t stream) {
   if (!use_v2()) return DCGAN_ERR_SHAPE;
-  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, nullptr, nullptr, nullptr, 0};
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, nullptr, nullptr, nullptr, 0, 0, 0};
   return igemm2_conv(1, x, w_nk, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 0, nullptr, 1, stream, &a);
 }
 
@@ -1071,7 +1071,7 @@ int dcgan_conv_fprop_kn_bnred(const void* x, const void* w_kn, void* out, const 
                               int bn_act, int NB, int H, int W, int Cin, int Cout, int block_n,
                               cudaStream_t stream) {
   if (!use_v2()) return DCGAN_ERR_SHAPE;
-  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, nullptr, nullptr, nullptr, 0};
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, nullptr, nullptr, nullptr, 0, 0, 0};
   return igemm2_conv(0, x, w_kn, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 1, nullptr, 1, stream, &a);
 }
 
@@ -1082,7 +1082,7 @@ int dcgan_conv_tconv_bnbwd(const void* x, const void* w_nk, void* out, const voi
                            int slabs, int stat_groups, int param_slabs, int bn_act, int NB, int H, int W, int Cin,
                            int Cout, int block_n, cudaStream_t stream) {
   if (!use_v2() || dpre == nullptr) return DCGAN_ERR_SHAPE;
-  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, dpre, dgamma, dbeta, param_slabs};
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, dpre, dgamma, dbeta, param_slabs, 0, 0};
   return igemm2_conv(1, x, w_nk, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 0, nullptr, 1, stream, &a);
 }
 
@@ -1091,8 +1091,20 @@ int dcgan_conv_fprop_kn_bnbwd(const void* x, const void* w_kn, void* out, const 
                               float* dbeta, int slabs, int stat_groups, int param_slabs, int bn_act, int NB, int H,
                               int W, int Cin, int Cout, int block_n, cudaStream_t stream) {
   if (!use_v2() || dpre == nullptr) return DCGAN_ERR_SHAPE;
-  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, dpre, dgamma, dbeta, param_slabs};
+  BnRedArgs a{pre, saved, gamma, beta, red, slabs, stat_groups, bn_act, dpre, dgamma, dbeta, param_slabs, 0, 0};
   return igemm2_conv(0, x, w_kn, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 1, nullptr, 1, stream, &a);
+}
+
+// Transposed-conv data gradient into a layer that is bias + activation only (d_h0_conv): the epilogue multiplies by
+// act'(saved activation) and accumulates the bias gradient, so `out` is the gradient w.r.t. that layer's
+// pre-activation (what dcgan_act_bwd produced in a launch of its own).
+int dcgan_conv_tconv_actbwd(const void* x, const void* w_nk, void* out, const void* act_saved, float* dbias, int slabs,
+                            int stat_groups, int bias_slabs, int act, int NB, int H, int W, int Cin, int Cout,
+                            int block_n, cudaStream_t stream) {
+  if (!use_v2() || act_saved == nullptr || dbias == nullptr) return DCGAN_ERR_SHAPE;
+  BnRedArgs a{act_saved, nullptr, nullptr, nullptr, dbias, slabs, stat_groups, act, nullptr, nullptr, nullptr, 0, 1,
+              bias_slabs};
+  return igemm2_conv(1, x, w_nk, nullptr, out, NB, H, W, Cin, Cout, 0, block_n, 0, nullptr, 1, stream, &a);
 }
 
 // Forward conv + training-mode batch norm + activation in one launch: pre = conv(x) + bias (bf16, kept for the

@@ -38,15 +38,23 @@ int* mn_variant_ptr() {
   return ptrs[dev];
 }
 
+// 0 = off, 1 = every hot-path kernel, 2 = the light kernels only (batch norm, heads, linear, casts).
+// Measured (profiles/README.md): with 1 the early-launched persistent conv CTAs sit on the SM slots the side
+// stream's kernels need: 0.665 -> 0.772 ms/step.
+#ifndef DCGAN_PDL_DEFAULT
+#define DCGAN_PDL_DEFAULT 0
+#endif
 static int g_use_pdl = -1;
-bool use_pdl() {
+static int pdl_mode() {
   if (g_use_pdl < 0) {
     const char* e = getenv("DCGAN_PDL");
-    g_use_pdl = (e != nullptr && e[0] == '1') ? 1 : 0;  // measured: 0.979 ms with, 0.948 ms without -> off by default
+    g_use_pdl = (e != nullptr && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : DCGAN_PDL_DEFAULT;
   }
-  return g_use_pdl != 0;
+  return g_use_pdl;
 }
-void set_pdl(int v) { g_use_pdl = v ? 1 : 0; }
+bool use_pdl() { return pdl_mode() == 1; }
+bool use_pdl_light() { return pdl_mode() >= 1; }
+void set_pdl(int v) { g_use_pdl = (v >= 0 && v <= 2) ? v : 0; }
 
 }  // namespace dcgan
 

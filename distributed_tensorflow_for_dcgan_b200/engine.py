@@ -210,6 +210,8 @@ class DCGANEngine:
         if (int(os.environ.get("DCGAN_IGEMM_TUNING", "1")) & 128) != 0:
             self.fuse_bn &= ~3
         self._grid_barrier = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.fuse_act_bwd = (os.environ.get("DCGAN_FUSE_ACT_BWD", "1") != "0"
+                             and (int(os.environ.get("DCGAN_IGEMM_TUNING", "1")) & 128) == 0)
         self.early_adam = os.environ.get("DCGAN_EARLY_ADAM", "1") != "0"
         self.memset_nodes = os.environ.get("DCGAN_MEMSET_NODES", "1") != "0"  # cudaMemsetAsync instead of fill kernels
         self.prioritize_main = os.environ.get("DCGAN_MAIN_PRIORITY", "1") != "0"
@@ -453,14 +455,22 @@ class DCGANEngine:
             # whose two reductions the conv's epilogue forms on the fly
             red_done = i > 1 and self._bnred_fusable(f"d_bn{i - 1}", self.dd_act[i - 1],
                                                      self.d_sz[i + 1] * self.d_sz[i + 1])
+            act_done = False
             if red_done:
                 red_done = self._dgrad_bnred(f"d_bn{i - 1}", self.dd_pre[i], w, self.dd_act[i - 1],
                                              self.d_pre[i - 1], True, dpre=self.dd_pre[i - 1])
+            elif i == 1 and self.fuse_act_bwd and (B * self.d_sz[2] * self.d_sz[2]) % 128 == 0:
+                # d_h0 is bias + LeakyReLU without batch norm: its activation backward and bias gradient ride in the
+                # epilogue of d_h1's data gradient (slabs 0, 1 = d_loss feed the bias gradient, slab 2 = g_loss)
+                K.conv_tconv_actbwd(self.dd_pre[1], w, self.dd_pre[0], self.d_act[0], g["d_h0_conv/biases"], 3, 2, 2,
+                                    "lrelu")
+                act_done = True
             else:
                 K.conv_tconv(self.dd_pre[i], w, None, out=self.dd_act[i - 1])
         C0 = self.d_ch[1]
-        K.act_bwd(self.dd_act[0].view(-1, C0), self.d_act[0].view(-1, C0), self.dd_pre[0].view(-1, C0),
-                  g["d_h0_conv/biases"], "lrelu", bias_rows=2 * B * self.d_sz[1] * self.d_sz[1])
+        if not act_done:
+            K.act_bwd(self.dd_act[0].view(-1, C0), self.d_act[0].view(-1, C0), self.dd_pre[0].view(-1, C0),
+                      g["d_h0_conv/biases"], "lrelu", bias_rows=2 * B * self.d_sz[1] * self.d_sz[1])
         with self._off_critical_path():
             K.c3_wgrad(self.d_in, self.dd_pre[0][:2 * B], g["d_h0_conv/w"])
         # g_loss slab only: gradient w.r.t. the generator's pre-tanh output

@@ -28,6 +28,7 @@ _SIGNATURES = {
     "dcgan_conv_fprop_kn_bnred": "ppppppppiiiiiiiiis",
     "dcgan_conv_tconv_bnbwd": "pppppppppppiiiiiiiiiis",
     "dcgan_conv_fprop_kn_bnbwd": "pppppppppppiiiiiiiiiis",
+    "dcgan_conv_tconv_actbwd": "pppppiiiiiiiiiis",
     "dcgan_conv_fprop_kn_bn": "pppppppppppiiiiiiffiis",
     "dcgan_conv_tconv_bn": "pppppppppppiiiiiiffiis",
     "dcgan_bn_forward_fused": "pppppppppiiiffis",

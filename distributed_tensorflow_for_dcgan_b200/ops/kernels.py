@@ -102,6 +102,18 @@ def conv_dgrad_bnbwd(x, w, out, pre, saved, gamma, beta, red, dpre, dgamma, dbet
     return dpre
 
 
+def conv_tconv_actbwd(x, w_nk, out, act_saved, dbias, slabs, stat_groups, bias_slabs, act, block_n=0):
+    """Transposed conv (data gradient of a strided conv) whose epilogue applies the activation backward of the layer
+    below (bias + activation, no batch norm) and accumulates that layer's bias gradient: ``conv_tconv`` + ``act_bwd``."""
+    N, H, W, Cin = x.shape
+    Cout = w_nk.shape[1]
+    if block_n == 0:
+        autotune.ensure(autotune.KIND_T, N, H, W, Cin, Cout)
+    call("dcgan_conv_tconv_actbwd", ptr(x), ptr(w_nk), ptr(out), ptr(act_saved), ptr(dbias), slabs, stat_groups,
+         bias_slabs, ACT[act], N, H, W, Cin, Cout, block_n)
+    return out
+
+
 def conv_bn_fwd(x, w, bias, pre, act_out, sums, gamma, beta, saved, ema_mean, ema_var, groups, act, transposed,
                 eps=1e-5, decay=0.9, block_n=0):
     """Forward conv (transposed: w [25,Cout,Cin]; strided: w [25,Cin,Cout]) + training-mode batch norm + activation

@@ -151,6 +151,14 @@ int dcgan_conv_fprop_kn_bnbwd(const void* x, const void* w_kn, void* out, const 
                               const float* gamma, const float* beta, float* red, void* dpre, float* dgamma,
                               float* dbeta, int slabs, int stat_groups, int param_slabs, int bn_act, int NB, int H,
                               int W, int Cin, int Cout, int block_n, cudaStream_t stream);
+/* Data gradient of a strided conv (= transposed conv of the upstream gradient) into a layer that is bias +
+ * activation without batch norm (d_h0_conv, distriubted_model.py:118): out = tconv(x) * act'(act_saved) is the gradient
+ * w.r.t. that layer's pre-activation, dbias[Cout] += its column sums over the first bias_slabs of `slabs` equal image
+ * groups (the slabs that belong to d_loss); slab g reads the saved activations of group min(g, stat_groups - 1).
+ * dcgan_conv_tconv followed by dcgan_act_bwd, in one launch. */
+int dcgan_conv_tconv_actbwd(const void* x, const void* w_nk, void* out, const void* act_saved, float* dbias, int slabs,
+                            int stat_groups, int bias_slabs, int act, int NB, int H, int W, int Cin, int Cout,
+                            int block_n, cudaStream_t stream);
 /* Forward conv + training-mode batch norm + activation in one launch (reference: conv2d / deconv2d followed by
  * batch_norm(train=True) and relu / lrelu, distriubted_model.py:91-121): pre = conv(x) + bias (bf16, kept for the
  * backward pass), sums[stat_groups][2][Cout] += its moments (zero it first), then behind a grid-wide barrier

@@ -288,7 +288,15 @@ def test_engine_layers_match_oracle_fed_with_engine_tensors(cuda_lib):
         H = x.shape[2]
         dx = F.conv_transpose2d(dy, w, stride=2)[:, :, 1:1 + H, 1:1 + H]   # gradient w.r.t. the unpadded input
         # slab 2 of the input gradient belongs to the generator's loss: its upstream activations are the fake half
-        close(eng.dd_act[i - 1], nhwc(dx), f"d_h{i} data gradient")
+        if i == 1:
+            # d_h0 has no batch norm: the data gradient's epilogue already applied LeakyReLU' (saved activation of the
+            # matching half: slab 2 = g_loss reads the fake half) and accumulated d_h0's bias gradient (slabs 0, 1)
+            a = nchw(eng.d_act[0])
+            dx = dx * torch.where(torch.cat([a, a[B:]], 0) > 0, 1.0, 0.2)
+            close(eng.dd_pre[0], nhwc(dx), "d_h1 data gradient through d_h0's LeakyReLU")
+            close(g["d_h0_conv/biases"], dx[:2 * B].sum((0, 2, 3)), "d_h0 bias gradient")
+        else:
+            close(eng.dd_act[i - 1], nhwc(dx), f"d_h{i} data gradient")
     # ---- generator: transposed convs g_h1..g_h3 ------------------------------------------------------------
     for i in (1, 2, 3):
         ci, co = eng.g_ch[i - 1], eng.g_ch[i]

@@ -639,3 +639,28 @@ def test_one_launch_batch_norm_kernels(cuda_lib):
         assert (res[0][0].float() - res[1][0].float()).abs().max().item() <= 1e-2 * res[1][0].float().abs().max().item()
     assert barrier.tolist() == [0, 0]
     K.check_device_error()
+
+
+def test_tconv_with_activation_backward_in_its_epilogue(cuda_lib):
+    """Data gradient into a bias + LeakyReLU layer without batch norm (d_h0): one launch against conv_tconv followed
+    by act_bwd, three slabs with the g_loss slab reading the fake half's saved activations, bias gradient from the
+    first two slabs only."""
+    from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
+    B, H, Cin, Cout = 8, 8, 128, 64
+    x = _rand((3 * B, H, H, Cin), 0.5)
+    w = _rand((25, Cout, Cin), 0.05)
+    act = _rand((2 * B, 2 * H, 2 * H, Cout))            # saved post-activation of the layer below
+    out = torch.empty(3 * B, 2 * H, 2 * H, Cout, device="cuda", dtype=torch.bfloat16)
+    dbias = torch.zeros(Cout, device="cuda")
+    K.conv_tconv_actbwd(x, w, out, act, dbias, 3, 2, 2, "lrelu")
+    da = K.conv_tconv(x, w, None)
+    ref = torch.empty_like(out)
+    dbias_ref = torch.zeros(Cout, device="cuda")
+    K.act_bwd(da.view(-1, Cout), act.view(-1, Cout), ref.view(-1, Cout), dbias_ref, "lrelu",
+              bias_rows=2 * B * 4 * H * H)
+    K.check_device_error()
+    # the fused path multiplies the f32 accumulator, the two-launch path the bf16-rounded data gradient
+    assert (out.float() - ref.float()).abs().max().item() <= 1e-2 * ref.float().abs().max().item()
+    _close(dbias, dbias_ref, rel=5e-3, name="bias gradient")
+    slope = torch.where(torch.cat([act, act[B:]], 0).float() > 0, 1.0, 0.2)
+    _close(out, da.float() * slope, rel=1e-2, name="dy vs da * lrelu'(a)")
