@@ -589,11 +589,13 @@ int dcgan_c3_fprop_tc(const void* x, const float* w, const float* bias, void* ou
                       int act, cudaStream_t st) {
   const int oH = H / 2, oW = W / 2;
   if (C % 64 || (H & 1) || (W & 1) || (oW != 32 && oW != 64 && oW != 128) || (oH * oW) % 128) return DCGAN_ERR_SHAPE;
-  static bool attr = false;
-  if (!attr) {
+  static bool attr_done[64] = {false};  // per device: the attribute belongs to the device's copy of the kernel
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
+  if (!attr_done[dev]) {
     if (cudaFuncSetAttribute(c3_fprop_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem) != cudaSuccess)
       return DCGAN_ERR_LAUNCH;
-    attr = true;
+    attr_done[dev] = true;
   }
   int* err = error_flag_ptr();
   if (!err) return DCGAN_ERR_DRIVER;
@@ -608,12 +610,14 @@ int dcgan_c3_fprop_tc(const void* x, const float* w, const float* bias, void* ou
 int dcgan_c3_tconv_tc(const void* x, const void* w_bf16, const float* bias, const void* aux, void* out, float* colsum,
                       int N, int H, int W, int C, int act, int mode, cudaStream_t st) {
   if (C != 64 || H % kTH2 || W % kTW2) return DCGAN_ERR_SHAPE;
-  static bool attr = false;
-  if (!attr) {
+  static bool attr_done[64] = {false};  // per device: the attribute belongs to the device's copy of the kernel
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
+  if (!attr_done[dev]) {
     if (cudaFuncSetAttribute(c3_tconv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTconvTcSmem) !=
         cudaSuccess)
       return DCGAN_ERR_LAUNCH;
-    attr = true;
+    attr_done[dev] = true;
   }
   int* err = error_flag_ptr();
   if (!err) return DCGAN_ERR_DRIVER;
@@ -628,11 +632,13 @@ int dcgan_c3_tconv_tc(const void* x, const void* w_bf16, const float* bias, cons
 
 int dcgan_c3_wgrad_tc(const void* x3, const void* y, float* dw, int N, int Hs, int Ws, int C, cudaStream_t st) {
   if (C % 64 || (Ws != 32 && Ws != 64 && Ws != 128) || (Hs * Ws) % 128) return DCGAN_ERR_SHAPE;
-  static bool attr = false;
-  if (!attr) {
+  static bool attr_done[64] = {false};  // per device: the attribute belongs to the device's copy of the kernel
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
+  if (!attr_done[dev]) {
     if (cudaFuncSetAttribute(c3_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem) != cudaSuccess)
       return DCGAN_ERR_LAUNCH;
-    attr = true;
+    attr_done[dev] = true;
   }
   int* err = error_flag_ptr();
   if (!err) return DCGAN_ERR_DRIVER;

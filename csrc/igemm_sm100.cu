@@ -795,11 +795,13 @@ template <int MODE, int BLOCK_N, int STAGES>
 static int launch(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cudaStream_t stream) {
   using L = SmemLayout<BLOCK_N, STAGES>;
   auto kern = igemm_kernel<MODE, BLOCK_N, STAGES>;
-  static bool attr_done = false;  // per instantiation
-  if (!attr_done) {
+  static bool attr_done[64] = {false};  // per instantiation and device
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
+  if (!attr_done[dev]) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal) != cudaSuccess)
       return DCGAN_ERR_LAUNCH;
-    attr_done = true;
+    attr_done[dev] = true;
   }
   if (MODE != MODE_W && p.ksplit > 1) {
     // split-K: the ksplit CTAs that share an output tile form one thread-block cluster along x
@@ -868,11 +870,13 @@ template <int BLOCK_N, int A_STAGES, int B_SLOTS>
 static int launch_t4(const CUtensorMap& tmap, const IgemmParams& p, dim3 grid, cudaStream_t stream) {
   using L = SmemLayoutT4<BLOCK_N, A_STAGES, B_SLOTS>;
   auto kern = igemm_t4_kernel<BLOCK_N, A_STAGES, B_SLOTS>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static bool attr_done[64] = {false};  // per device
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
+  if (!attr_done[dev]) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal) != cudaSuccess)
       return DCGAN_ERR_LAUNCH;
-    attr_done = true;
+    attr_done[dev] = true;
   }
   launch_k(kern, dim3(grid), dim3(kNumThreads), L::kTotal, stream, tmap, p);
   return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;

@@ -175,6 +175,7 @@ def c3_wgrad(x3, y, dw, tensor_cores=True):
     N, Hs, Ws, C = y.shape
     if tensor_cores and _tc_width_ok(Ws, Hs):
         call("dcgan_c3_wgrad_tc", ptr(x3), ptr(y), ptr(dw), N, Hs, Ws, C)
+        _lib.launch_count += 1  # two kernels: per-CTA partial tiles, then the ordered reduce
     else:
         call("dcgan_c3_wgrad", ptr(x3), ptr(y), ptr(dw), N, Hs, Ws, C)
     return dw
