@@ -400,6 +400,13 @@ decode_f64_kernel(const double* __restrict__ src, __nv_bfloat16* __restrict__ ds
   for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256)
     dst[i] = __float2bfloat16((float)src[i] * scale + shift);
 }
+// the same cast with float32 output: what the reference's tf.cast(image, tf.float32) (image_input.py:51) does, moved
+// to the device so that the host threads only copy bytes
+__global__ void __launch_bounds__(256)
+decode_f64_f32_kernel(const double* __restrict__ src, float* __restrict__ dst, size_t n, float scale, float shift) {
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256)
+    dst[i] = (float)src[i] * scale + shift;
+}
 __global__ void __launch_bounds__(256)
 f32_to_bf16_affine_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n, float scale,
                           float shift) {
@@ -541,6 +548,13 @@ int dcgan_decode_f64(const double* src, void* dst, size_t n, float scale, float 
   size_t blocks = (n + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   decode_f64_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), n, scale, shift);
+  return LAUNCH_OK();
+}
+
+int dcgan_decode_f64_f32(const double* src, float* dst, size_t n, float scale, float shift, cudaStream_t st) {
+  size_t blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  decode_f64_f32_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, dst, n, scale, shift);
   return LAUNCH_OK();
 }
 

@@ -108,7 +108,9 @@ struct Reader {
   std::vector<std::thread> threads;
   std::mutex mu;
   std::condition_variable not_full, not_empty;
-  std::vector<float> pool;        // capacity * elems
+  std::vector<uint8_t> pool;  // capacity records of rec_bytes() each: float32, or the raw float64 of the file
+  bool raw_f64 = false;
+  size_t rec_bytes() const { return (size_t)elems * (raw_f64 ? 8 : 4); }
   size_t size = 0;
   std::mt19937_64 rng;
   std::atomic<bool> stop{false};
@@ -150,8 +152,12 @@ struct Reader {
     std::unique_lock<std::mutex> l(mu);
     not_full.wait(l, [&] { return size < capacity || stop.load(); });
     if (stop) return;
-    float* dst = pool.data() + size * (size_t)elems;
-    for (int i = 0; i < elems; ++i) dst[i] = (float)src[i];
+    if (raw_f64) {  // records stay float64: the cast happens on the GPU (dcgan_decode_f64_f32)
+      memcpy(pool.data() + size * rec_bytes(), src, rec_bytes());
+    } else {
+      float* dst = reinterpret_cast<float*>(pool.data() + size * rec_bytes());
+      for (int i = 0; i < elems; ++i) dst[i] = (float)src[i];
+    }
     ++size; ++records_read;
     l.unlock();
     not_empty.notify_one();
@@ -188,7 +194,9 @@ struct Reader {
   }
 
   // RandomShuffleQueue.dequeue_many(n): waits until size - n >= min_after_dequeue (or the producers are done)
-  int dequeue(int n, float* out) {
+  int dequeue(int n, void* out_v) {
+    uint8_t* out = static_cast<uint8_t*>(out_v);
+    const size_t rb = rec_bytes();
     std::unique_lock<std::mutex> l(mu);
     for (int i = 0; i < n; ++i) {
       not_empty.wait(l, [&] {
@@ -198,12 +206,12 @@ struct Reader {
       if (!error.empty()) return -1;
       if (size == 0) return i;  // producers finished (finite epochs)
       size_t idx = shuffle ? (size_t)(rng() % size) : 0;
-      float* src = pool.data() + idx * (size_t)elems;
-      memcpy(out + (size_t)i * elems, src, (size_t)elems * sizeof(float));
+      uint8_t* src = pool.data() + idx * rb;
+      memcpy(out + (size_t)i * rb, src, rb);
       if (shuffle) {
-        if (idx != size - 1) memcpy(src, pool.data() + (size - 1) * (size_t)elems, (size_t)elems * sizeof(float));
+        if (idx != size - 1) memcpy(src, pool.data() + (size - 1) * rb, rb);
       } else {
-        memmove(pool.data(), pool.data() + elems, (size - 1) * (size_t)elems * sizeof(float));
+        memmove(pool.data(), pool.data() + rb, (size - 1) * rb);
       }
       --size;
       not_full.notify_one();
@@ -222,8 +230,19 @@ uint32_t dcgan_io_crc32c(const uint8_t* data, size_t n, uint32_t crc) { return c
 
 const char* dcgan_io_last_error(void) { return g_last_error.c_str(); }
 
+void* dcgan_io_reader_create2(const char** files, int nfiles, int h, int w, int c, long capacity, long min_after,
+                              int threads, unsigned long long seed, int shuffle, int epochs, int verify_crc,
+                              int raw_f64);
 void* dcgan_io_reader_create(const char** files, int nfiles, int h, int w, int c, long capacity, long min_after,
                              int threads, unsigned long long seed, int shuffle, int epochs, int verify_crc) {
+  return dcgan_io_reader_create2(files, nfiles, h, w, c, capacity, min_after, threads, seed, shuffle, epochs,
+                                 verify_crc, 0);
+}
+
+// raw_f64 != 0: the queue holds the records as stored (float64); dequeue copies 8 bytes per element
+void* dcgan_io_reader_create2(const char** files, int nfiles, int h, int w, int c, long capacity, long min_after,
+                              int threads, unsigned long long seed, int shuffle, int epochs, int verify_crc,
+                              int raw_f64) {
   if (nfiles <= 0 || capacity <= 0 || min_after < 0 || min_after >= capacity || threads <= 0) {
     g_last_error = "bad reader arguments";
     return nullptr;
@@ -231,8 +250,9 @@ void* dcgan_io_reader_create(const char** files, int nfiles, int h, int w, int c
   Reader* r = new Reader();
   for (int i = 0; i < nfiles; ++i) r->files.emplace_back(files[i]);
   r->elems = h * w * c;
+  r->raw_f64 = raw_f64 != 0;
   r->capacity = (size_t)capacity; r->min_after = (size_t)min_after; r->shuffle = shuffle != 0;
-  r->pool.resize((size_t)capacity * r->elems);
+  r->pool.resize((size_t)capacity * r->rec_bytes());
   r->rng.seed(seed); r->file_rng.seed(seed ^ 0x9E3779B97F4A7C15ull);
   r->epochs_limit = epochs; r->verify_crc = verify_crc != 0;
   r->live_threads = threads;
@@ -240,7 +260,7 @@ void* dcgan_io_reader_create(const char** files, int nfiles, int h, int w, int c
   return r;
 }
 
-int dcgan_io_reader_dequeue(void* handle, int n, float* out) {
+int dcgan_io_reader_dequeue(void* handle, int n, void* out) {
   Reader* r = static_cast<Reader*>(handle);
   int got = r->dequeue(n, out);
   if (got < 0) g_last_error = r->error;

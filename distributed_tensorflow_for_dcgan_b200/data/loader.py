@@ -78,7 +78,7 @@ class PythonShuffleReader:
 
 def distorted_inputs(data_dir: str, batch_size: int = 64, image_size: int = 64, depth: int = 3, seed: int = 0,
                      num_threads: int = 16, native: bool = True, min_after_dequeue: Optional[int] = None,
-                     capacity: Optional[int] = None):
+                     capacity: Optional[int] = None, raw_f64: bool = False):
     """Returns a reader whose ``dequeue_many(batch_size)`` yields float32 ``[B, 64, 64, 3]`` batches."""
     files = tfrecord.list_data_files(data_dir)
     if not files:
@@ -90,7 +90,10 @@ def distorted_inputs(data_dir: str, batch_size: int = 64, image_size: int = 64, 
           "This will take a few minutes." % mq)  # image_input.py:137-138 (wording kept)
     if native:
         from .native_reader import NativeShuffleReader
-        return NativeShuffleReader(files, image_size, image_size, depth, cap, mq, num_threads, seed, True)
+        return NativeShuffleReader(files, image_size, image_size, depth, cap, mq, num_threads, seed, True,
+                                   raw_f64=raw_f64)
+    if raw_f64:
+        raise ValueError("raw float64 records need the native reader")
     return PythonShuffleReader(files, image_size, image_size, depth, cap, mq, seed, True)
 
 
@@ -112,10 +115,20 @@ class DevicePrefetcher:
     """Device-resident prefetch ring: a background thread dequeues into pinned host buffers and issues
     the H2D copies on a side stream, ``depth`` batches ahead of the consumer."""
 
-    def __init__(self, reader, batch_size: int, shape=(64, 64, 3), device="cuda", depth: int = 3):
+    def __init__(self, reader, batch_size: int, shape=(64, 64, 3), device="cuda", depth: int = 3,
+                 gpu_decode: bool = False):
+        """``gpu_decode``: the reader hands out the records as stored (float64, ``raw_f64`` readers); they are copied
+        to the device unconverted and cast to float32 there by ``decode_f64_f32_kernel`` on the prefetch stream -- the
+        reference's ``decode_raw(float64)`` + ``cast(float32)`` (image_input.py:48-51) as device work."""
         self.reader, self.B, self.device, self.depth = reader, batch_size, torch.device(device), depth
         self.cuda = self.device.type == "cuda"
-        self.host = [torch.empty((batch_size,) + tuple(shape), pin_memory=self.cuda) for _ in range(depth)]
+        self.gpu_decode = bool(gpu_decode) and self.cuda
+        if gpu_decode and not getattr(reader, "raw_f64", False):
+            raise ValueError("gpu_decode needs a reader that yields raw float64 records (raw_f64=True)")
+        hdt = torch.float64 if self.gpu_decode else torch.float32
+        self.host = [torch.empty((batch_size,) + tuple(shape), dtype=hdt, pin_memory=self.cuda) for _ in range(depth)]
+        self.raw = ([torch.empty((batch_size,) + tuple(shape), dtype=torch.float64, device=self.device)
+                     for _ in range(depth)] if self.gpu_decode else None)
         self.dev = [torch.empty((batch_size,) + tuple(shape), device=self.device) for _ in range(depth)]
         self.ready = [threading.Event() for _ in range(depth)]
         self.free = [threading.Event() for _ in range(depth)]
@@ -151,7 +164,12 @@ class DevicePrefetcher:
                     return
                 if self.cuda:
                     with torch.cuda.stream(self.stream):
-                        self.dev[slot].copy_(h, non_blocking=True)
+                        if self.gpu_decode:
+                            from ..ops import kernels as K
+                            self.raw[slot].copy_(h, non_blocking=True)
+                            K.decode_f64(self.raw[slot], self.dev[slot])
+                        else:
+                            self.dev[slot].copy_(h, non_blocking=True)
                         ev = torch.cuda.Event()
                         ev.record(self.stream)
                     self.events[slot] = ev

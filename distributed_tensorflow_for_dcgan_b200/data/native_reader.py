@@ -42,6 +42,8 @@ def load() -> ctypes.CDLL:
                                                ctypes.c_int, ctypes.c_long, ctypes.c_long, ctypes.c_int,
                                                ctypes.c_ulonglong, ctypes.c_int, ctypes.c_int, ctypes.c_int]
         lib.dcgan_io_reader_create.restype = ctypes.c_void_p
+        lib.dcgan_io_reader_create2.argtypes = list(lib.dcgan_io_reader_create.argtypes) + [ctypes.c_int]
+        lib.dcgan_io_reader_create2.restype = ctypes.c_void_p
         lib.dcgan_io_reader_dequeue.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
         lib.dcgan_io_reader_dequeue.restype = ctypes.c_int
         lib.dcgan_io_reader_size.argtypes = [ctypes.c_void_p]
@@ -63,18 +65,22 @@ class NativeShuffleReader:
     until more than ``min_after_dequeue`` elements remain (image_input.py:77-84)."""
 
     def __init__(self, files: List[str], height=64, width=64, depth=3, capacity=10968, min_after_dequeue=10776,
-                 num_threads=16, seed=0, shuffle=True, epochs=0, verify_crc=True):
+                 num_threads=16, seed=0, shuffle=True, epochs=0, verify_crc=True, raw_f64=False):
+        """``raw_f64``: keep the records as stored (float64, image_input.py:48 ``decode_raw(.., tf.float64)``) and
+        hand them out unconverted -- the cast to float32 then runs on the GPU (``DevicePrefetcher(gpu_decode=True)``)."""
         lib = load()
         arr = (ctypes.c_char_p * len(files))(*[f.encode() for f in files])
-        self._h = lib.dcgan_io_reader_create(arr, len(files), height, width, depth, capacity, min_after_dequeue,
-                                             num_threads, seed, int(shuffle), epochs, int(verify_crc))
+        self._h = lib.dcgan_io_reader_create2(arr, len(files), height, width, depth, capacity, min_after_dequeue,
+                                              num_threads, seed, int(shuffle), epochs, int(verify_crc), int(raw_f64))
         if not self._h:
             raise RuntimeError(lib.dcgan_io_last_error().decode())
         self.shape = (height, width, depth)
+        self.raw_f64 = bool(raw_f64)
+        self.dtype = np.float64 if raw_f64 else np.float32
 
     def dequeue_many(self, n: int, out: Optional[np.ndarray] = None) -> np.ndarray:
         if out is None:
-            out = np.empty((n,) + self.shape, dtype=np.float32)
+            out = np.empty((n,) + self.shape, dtype=self.dtype)
         got = load().dcgan_io_reader_dequeue(self._h, n, out.ctypes.data_as(ctypes.c_void_p))
         if got < 0:
             raise IOError(load().dcgan_io_last_error().decode())

@@ -66,6 +66,8 @@ def define_flags() -> None:
     flags.DEFINE_integer("seed", 0, "initialisation / data seed")
     flags.DEFINE_bool("cuda_graph", True, "replay the step from a CUDA graph")
     flags.DEFINE_integer("num_reader_threads", 16, "input pipeline threads (image_input.py:76)")
+    flags.DEFINE_bool("gpu_decode", True, "GPU runs: copy the float64 records to the device as stored and cast them "
+                      "there (image_input.py:48-51 as device work) instead of casting on the reader threads")
     flags.DEFINE_integer("shuffle_min_after_dequeue", -1, "override of int(107766*0.1); -1 keeps the reference value")
     flags.DEFINE_bool("profile", False, "NVTX ranges + CUDA-event step timing report")
     flags.DEFINE_bool("identical_replicas", False, "testing aid: every worker draws the same data and z, so "

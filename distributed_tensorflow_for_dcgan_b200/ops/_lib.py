@@ -55,6 +55,7 @@ _SIGNATURES = {
     "dcgan_transpose_taps": "ppiiis",
     "dcgan_colsum": "ppzis",
     "dcgan_decode_f64": "ppzffs",
+    "dcgan_decode_f64_f32": "ppzffs",
     "dcgan_f32_to_bf16": "ppzffs",
     "dcgan_grid_merge": "ppiiiiis",
     "dcgan_count_zeros": "ppzs",

@@ -301,7 +301,9 @@ def zero_(t):
 
 
 def decode_f64(src, dst, scale=1.0, shift=0.0):
-    call("dcgan_decode_f64", ptr(src), ptr(dst), src.numel(), scale, shift)
+    """float64 records -> bf16 (``dst`` bf16) or float32 (``dst`` float32), ``x * scale + shift`` on the way."""
+    call("dcgan_decode_f64_f32" if dst.dtype == torch.float32 else "dcgan_decode_f64", ptr(src), ptr(dst), src.numel(),
+         scale, shift)
     return dst
 
 

@@ -25,7 +25,7 @@ from .utils import sample as S
 SAMPLE_SIZE = 64  # image_train.py:43
 
 
-def _make_reader(FLAGS, data_dir, batch_size, cfg, seed):
+def _make_reader(FLAGS, data_dir, batch_size, cfg, seed, raw_f64=False):
     from .data import loader
     if FLAGS.synthetic_data:
         return loader.SyntheticImages(batch_size, cfg.output_size, cfg.c_dim, seed)
@@ -34,7 +34,8 @@ def _make_reader(FLAGS, data_dir, batch_size, cfg, seed):
         kw = dict(min_after_dequeue=FLAGS.shuffle_min_after_dequeue,
                   capacity=FLAGS.shuffle_min_after_dequeue + 3 * batch_size)
     return loader.distorted_inputs(data_dir, batch_size, cfg.output_size, cfg.c_dim, seed=seed,
-                                   num_threads=FLAGS.num_reader_threads, **kw)
+                                   num_threads=FLAGS.num_reader_threads,
+                                   raw_f64=raw_f64, **kw)
 
 
 def run_ps(FLAGS, role, cfg) -> int:
@@ -159,7 +160,9 @@ def run_worker(FLAGS, role, cfg) -> int:
     if FLAGS.log_device_placement and is_chief:
         log_placement(trainer, role, use_cuda)
     replica = 0 if FLAGS.identical_replicas else role.task_index
-    images = _make_reader(FLAGS, FLAGS.data_dir, batch, cfg, FLAGS.seed + 17 * replica)
+    # --gpu_decode: the training pipeline ships the float64 records as stored and casts them on the device
+    images = _make_reader(FLAGS, FLAGS.data_dir, batch, cfg, FLAGS.seed + 17 * replica,
+                          raw_f64=bool(FLAGS.gpu_decode) and use_cuda and not FLAGS.synthetic_data)
     sample_images = None
     if is_chief:
         # the second pipeline (image_train.py:84) is built before the loop, as in the reference graph: filling its
@@ -171,7 +174,8 @@ def run_worker(FLAGS, role, cfg) -> int:
     prefetch = None
     if use_cuda:
         from .data.loader import DevicePrefetcher
-        prefetch = DevicePrefetcher(images, batch, (cfg.output_size, cfg.output_size, cfg.c_dim), trainer.device)
+        prefetch = DevicePrefetcher(images, batch, (cfg.output_size, cfg.output_size, cfg.c_dim), trainer.device,
+                                    gpu_decode=getattr(images, "raw_f64", False))
 
     step = trainer.global_step
     start_time = time.time()

@@ -270,6 +270,9 @@ int dcgan_transpose_taps(const void* src, void* dst, int taps, int R, int C, cud
 int dcgan_colsum(const void* x, float* out, size_t rows, int C, cudaStream_t stream);
 /* float64 records -> bf16 (image_input.py:48,118 decode_raw + cast), with an optional affine map. */
 int dcgan_decode_f64(const double* src, void* dst, size_t n, float scale, float shift, cudaStream_t stream);
+/* The same with float32 output (the input pipeline's device-side decode: raw float64 records are copied to the GPU
+ * as stored and cast here, data/loader.py DevicePrefetcher(gpu_decode=True)). */
+int dcgan_decode_f64_f32(const double* src, float* dst, size_t n, float scale, float shift, cudaStream_t stream);
 int dcgan_f32_to_bf16(const float* src, void* dst, size_t n, float scale, float shift, cudaStream_t stream);
 /* inverse_transform + merge of the sample grid (image_train.py:205-219) into f32 [rows*H][cols*W][C]. */
 int dcgan_grid_merge(const void* img, float* out, int N, int H, int W, int C, int cols, cudaStream_t stream);

@@ -213,6 +213,27 @@ def test_native_reader_matches_python_reader(tmp_path):
     assert n == ref.shape[0]
 
 
+def test_native_reader_raw_float64_mode(tmp_path):
+    """raw_f64: the queue hands out the records as stored (float64, no cast on the reader threads); the float32 cast
+    of the default mode equals casting these afterwards -- which is what the GPU decode path does on the device."""
+    from distributed_tensorflow_for_dcgan_b200.data import native_reader, tfrecord
+    d, imgs = _write_dataset(tmp_path, 2, 20)
+    files = tfrecord.list_data_files(d)
+    raw = native_reader.NativeShuffleReader(files, capacity=30, min_after_dequeue=10, num_threads=2, seed=5, epochs=1,
+                                            raw_f64=True)
+    got = []
+    while True:
+        b = raw.dequeue_many(8)
+        if b.shape[0] == 0:
+            break
+        assert b.dtype == np.float64
+        got.append(b.copy())
+    raw.close()
+    got = np.concatenate(got)
+    assert sorted(a.tobytes() for a in got) == sorted(a.tobytes() for a in imgs)   # bit-exact float64 payloads
+    assert sorted(a.astype(np.float32).tobytes() for a in got) == sorted(a.astype(np.float32).tobytes() for a in imgs)
+
+
 def test_shuffle_queue_waits_for_min_after_dequeue(tmp_path):
     from distributed_tensorflow_for_dcgan_b200.data import loader, native_reader, tfrecord
     assert loader.queue_sizes(64) == (10776, 10968)  # image_input.py:134-136,82-84

@@ -664,3 +664,32 @@ def test_tconv_with_activation_backward_in_its_epilogue(cuda_lib):
     _close(dbias, dbias_ref, rel=5e-3, name="bias gradient")
     slope = torch.where(torch.cat([act, act[B:]], 0).float() > 0, 1.0, 0.2)
     _close(out, da.float() * slope, rel=1e-2, name="dy vs da * lrelu'(a)")
+
+
+def test_device_prefetcher_decodes_float64_records_on_the_gpu(cuda_lib, tmp_path):
+    """Input pipeline with the decode on the device: raw float64 records -> pinned host -> H2D -> decode_f64_f32
+    kernel on the prefetch stream.  Every batch equals the float32 cast of the records (bit exact) and nothing is
+    lost or duplicated."""
+    import numpy as np
+    from distributed_tensorflow_for_dcgan_b200.data import loader, native_reader, tfrecord
+    rng = np.random.RandomState(1)
+    imgs = rng.rand(48, 64, 64, 3) * 2 - 1
+    d = tmp_path / "train"
+    d.mkdir()
+    for i in range(2):
+        tfrecord.write_image_tfrecord(str(d / f"image_{i}.tfrecords"), imgs[i * 24:(i + 1) * 24])
+    reader = native_reader.NativeShuffleReader(tfrecord.list_data_files(str(d)), capacity=40, min_after_dequeue=8,
+                                               num_threads=2, seed=2, epochs=1, raw_f64=True)
+    pf = loader.DevicePrefetcher(reader, 8, (64, 64, 3), "cuda", gpu_decode=True)
+    got = []
+    for _ in range(6):
+        b = pf.next()
+        assert b.dtype == torch.float32 and b.is_cuda
+        got.append(b.cpu().numpy().copy())
+        pf.release()
+    pf.close()
+    got = np.concatenate(got)
+    ref = imgs.astype(np.float32)
+    assert sorted(a.tobytes() for a in got) == sorted(a.tobytes() for a in ref)
+    with pytest.raises(ValueError):
+        loader.DevicePrefetcher(loader.SyntheticImages(8), 8, (64, 64, 3), "cuda", gpu_decode=True)
