@@ -404,28 +404,34 @@ c3_wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw
 // C -> 3 transposed conv on tensor cores (g_h4 forward, distriubted_model.py:109; d_h0 data gradient).
 //   step 1 (tcgen05): Y[q][tap*3+co] = sum_ci x[q][ci] * W[tap][co][ci]       -- a plain GEMM, no im2col:
 //           M = input locations (an 8x16 tile plus a one-pixel halo = 180 rows in two 128-row MMAs),
-//           N = 80 (75 tap/channel pairs + padding), K = 64 channels.
+//           N = 80 (75 tap/channel pairs + padding), K = C channels in KC = C / 64 chunks (C = 64, or 128 for the
+//           wide configuration).
 //   step 2 (col2im in shared memory): out[2q+p][co] = sum over the taps of parity p of Y[q + (p+1-k)/2][tap][co],
 //           then bias+tanh, or the tanh backward against `aux`, and the optional per-channel sum.
-// grid = (tiles, 1); C must be 64.
+// grid = (tiles, 1); C = 64 * KC, KC in {1, 2}.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kTH2 = 8, kTW2 = 16;                       // interior tile (input locations)
 constexpr int kHaloW = kTW2 + 2, kHaloRows = (kTH2 + 2) * (kTW2 + 2);  // 18, 180
 constexpr int kYPitch = 77;                              // f32 per Y row (75 used; odd pitch -> conflict-free)
-constexpr int kTconvTcSmem = 32768 /*A*/ + 128 * 128 /*B (80 rows used)*/ + kHaloRows * kYPitch * 4 + 64 + 1024;
+template <int KC>
+constexpr int tconv_tc_smem() {
+  return KC * 32768 /*A*/ + KC * 128 * 128 /*B (80 rows used)*/ + kHaloRows * kYPitch * 4 + 64 + 1024;
+}
 
+template <int KC>
 __global__ void __launch_bounds__(kTcThreads)
-c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w_bf16 /*[75][64]*/,
+c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w_bf16 /*[75][C]*/,
                    const float* __restrict__ bias, const __nv_bfloat16* __restrict__ aux,
                    __nv_bfloat16* __restrict__ out, float* __restrict__ colsum, int N, int H, int W, int act,
                    int mode, int* err_flag) {
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
-  uint8_t* a_tiles = smem;                       // 2 x [128 rows][128 B]: halo rows 0..179 (+ zero rows)
-  uint8_t* b_tile = smem + 32768;                // [80 rows (tap*3+co)][128 B]
-  float* ysm = reinterpret_cast<float*>(smem + 32768 + 16384);
-  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(smem + 32768 + 16384 + kHaloRows * kYPitch * 4);
+  constexpr int C = 64 * KC;
+  uint8_t* a_tiles = smem;                       // KC x 2 x [128 rows][128 B]: halo rows 0..179 (+ zero rows)
+  uint8_t* b_tile = smem + KC * 32768;           // KC x [80 rows (tap*3+co)][128 B]
+  float* ysm = reinterpret_cast<float*>(smem + KC * (32768 + 16384));
+  uint64_t* mma_bar = reinterpret_cast<uint64_t*>(smem + KC * (32768 + 16384) + kHaloRows * kYPitch * 4);
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(mma_bar + 1);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
   __shared__ float cred[3];
@@ -435,12 +441,13 @@ c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
   if (t < 3) cred[t] = 0.f;
   if (warp == 0) { tmem_alloc(tmem_ptr_smem, 256); tmem_relinquish(); }
   pdl_wait();
-  // B: filter rows (tap*3+co) x 64 channels, K-major SW128; rows 75..79 zero
-  for (int i = t; i < 80 * 8; i += kTcThreads) {
-    const int row = i >> 3, ch = i & 7;
+  // B: filter rows (tap*3+co) x C channels, K-major SW128, one tile per 64-channel chunk; rows 75..79 zero
+  for (int i = t; i < KC * 80 * 8; i += kTcThreads) {
+    const int kc = i / (80 * 8), r8 = i - kc * (80 * 8);
+    const int row = r8 >> 3, ch = r8 & 7;
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (row < 75) v = __ldg(reinterpret_cast<const uint4*>(w_bf16 + (size_t)row * 64) + ch);
-    *reinterpret_cast<uint4*>(b_tile + swz(row, ch)) = v;
+    if (row < 75) v = __ldg(reinterpret_cast<const uint4*>(w_bf16 + (size_t)row * C + kc * 64) + ch);
+    *reinterpret_cast<uint4*>(b_tile + kc * 16384 + swz(row, ch)) = v;
   }
   tc_fence_before();
   __syncthreads();
@@ -459,7 +466,8 @@ c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
     const int tr = tile - n * tiles_y * tiles_x;
     const int qy0 = (tr / tiles_x) * kTH2, qx0 = (tr % tiles_x) * kTW2;
     // ---- gather the halo tile: 256 rows x 8 chunks, zero outside the image / beyond row 179 -----------------
-    {
+#pragma unroll 1
+    for (int kc = 0; kc < KC; ++kc) {
       uint4 v[16];
 #pragma unroll
       for (int k = 0; k < 16; ++k) {
@@ -470,14 +478,14 @@ c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
           const int ly = row / kHaloW, lx = row - ly * kHaloW;
           const int qy = qy0 - 1 + ly, qx = qx0 - 1 + lx;
           if ((unsigned)qy < (unsigned)H && (unsigned)qx < (unsigned)W)
-            v[k] = __ldg(reinterpret_cast<const uint4*>(x + (((size_t)n * H + qy) * W + qx) * 64) + ch);
+            v[k] = __ldg(reinterpret_cast<const uint4*>(x + (((size_t)n * H + qy) * W + qx) * C + kc * 64) + ch);
         }
       }
 #pragma unroll
       for (int k = 0; k < 16; ++k) {
         const int idx = t + k * kTcThreads;
         const int row = idx >> 3, ch = idx & 7;
-        *reinterpret_cast<uint4*>(a_tiles + (row >> 7) * 16384 + swz(row & 127, ch)) = v[k];
+        *reinterpret_cast<uint4*>(a_tiles + kc * 32768 + (row >> 7) * 16384 + swz(row & 127, ch)) = v[k];
       }
     }
     fence_proxy_async_smem();
@@ -487,11 +495,13 @@ c3_tconv_tc_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
 #pragma unroll
       for (int j = 0; j < 2; ++j)
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint64_t da = make_smem_desc_sw128(a_addr + j * 16384 + k * 32, 16, 1024);
-          const uint64_t db = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-          umma_bf16(tmem_base + j * 128, da, db, idesc, k != 0 ? 1u : 0u);
-        }
+        for (int kc = 0; kc < KC; ++kc)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t da = make_smem_desc_sw128(a_addr + kc * 32768 + j * 16384 + k * 32, 16, 1024);
+            const uint64_t db = make_smem_desc_sw128(b_addr + kc * 16384 + k * 32, 16, 1024);
+            umma_bf16(tmem_base + j * 128, da, db, idesc, (kc | k) != 0 ? 1u : 0u);
+          }
       umma_commit(mma_bar);
     }
     const bool ok = mbar_wait(mma_bar, phase, abort_flag, err_flag);
@@ -578,6 +588,30 @@ using namespace dcgan;
 
 static int g_c3_blocks_fprop = 0, g_c3_blocks_wgrad = 0;  // 0 = default; profiling overrides
 
+template <int KC>
+static int launch_tconv_tc(const void* x, const void* w_bf16, const float* bias, const void* aux, void* out,
+                           float* colsum, int N, int H, int W, int act, int mode, cudaStream_t st) {
+  static bool attr_done[64] = {false};  // per device: the attribute belongs to the device's copy of the kernel
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
+  if (!attr_done[dev]) {
+    if (cudaFuncSetAttribute(c3_tconv_tc_kernel<KC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             tconv_tc_smem<KC>()) != cudaSuccess)
+      return DCGAN_ERR_LAUNCH;
+    attr_done[dev] = true;
+  }
+  int* err = error_flag_ptr();
+  if (!err) return DCGAN_ERR_DRIVER;
+  const int tiles = N * (H / kTH2) * (W / kTW2);
+  const int cap = KC == 1 ? 296 : 148;  // two CTAs per SM fit with 64 channels (106 KB), one with 128 (154 KB)
+  dim3 grid(tiles < cap ? tiles : cap);
+  launch_k(c3_tconv_tc_kernel<KC>, dim3(grid), dim3(kTcThreads), tconv_tc_smem<KC>(), st,
+           reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(w_bf16), bias,
+           reinterpret_cast<const __nv_bfloat16*>(aux), reinterpret_cast<__nv_bfloat16*>(out), colsum, N, H, W, act, mode,
+           err);
+  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+}
+
 extern "C" {
 
 void dcgan_set_c3_tuning(int fprop_blocks, int wgrad_blocks) {
@@ -609,25 +643,9 @@ int dcgan_c3_fprop_tc(const void* x, const float* w, const float* bias, void* ou
 
 int dcgan_c3_tconv_tc(const void* x, const void* w_bf16, const float* bias, const void* aux, void* out, float* colsum,
                       int N, int H, int W, int C, int act, int mode, cudaStream_t st) {
-  if (C != 64 || H % kTH2 || W % kTW2) return DCGAN_ERR_SHAPE;
-  static bool attr_done[64] = {false};  // per device: the attribute belongs to the device's copy of the kernel
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DCGAN_ERR_DRIVER;
-  if (!attr_done[dev]) {
-    if (cudaFuncSetAttribute(c3_tconv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTconvTcSmem) !=
-        cudaSuccess)
-      return DCGAN_ERR_LAUNCH;
-    attr_done[dev] = true;
-  }
-  int* err = error_flag_ptr();
-  if (!err) return DCGAN_ERR_DRIVER;
-  const int tiles = N * (H / kTH2) * (W / kTW2);
-  dim3 grid(tiles < 296 ? tiles : 296);
-  launch_k(c3_tconv_tc_kernel, dim3(grid), dim3(kTcThreads), kTconvTcSmem, st, 
-      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(w_bf16), bias,
-      reinterpret_cast<const __nv_bfloat16*>(aux), reinterpret_cast<__nv_bfloat16*>(out), colsum, N, H, W, act, mode,
-      err);
-  return cudaGetLastError() == cudaSuccess ? 0 : DCGAN_ERR_LAUNCH;
+  if ((C != 64 && C != 128) || H % kTH2 || W % kTW2) return DCGAN_ERR_SHAPE;
+  return C == 64 ? launch_tconv_tc<1>(x, w_bf16, bias, aux, out, colsum, N, H, W, act, mode, st)
+                 : launch_tconv_tc<2>(x, w_bf16, bias, aux, out, colsum, N, H, W, act, mode, st);
 }
 
 int dcgan_c3_wgrad_tc(const void* x3, const void* y, float* dw, int N, int Hs, int Ws, int C, cudaStream_t st) {

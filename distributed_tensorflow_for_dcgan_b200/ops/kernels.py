@@ -158,11 +158,11 @@ def c3_fprop(x, w, bias=None, act="none", out=None, tensor_cores=True):
 
 def c3_tconv(x, w, bias=None, act="none", aux=None, out=None, colsum=None, w_bf16=None):
     """mode 0: act(v + bias); with ``aux``: v * (1 - aux^2).  ``colsum`` (f32[3]) += channel sums.
-    With ``w_bf16`` (the bf16 shadow of the [25,3,64] filter) and C == 64 the tensor-core kernel runs."""
+    With ``w_bf16`` (the bf16 shadow of the [25,3,C] filter) and C in (64, 128) the tensor-core kernel runs."""
     N, H, W, C = x.shape
     if out is None:
         out = _bf16((N, 2 * H, 2 * W, 3), x)
-    if w_bf16 is not None and C == 64 and H % 8 == 0 and W % 16 == 0:
+    if w_bf16 is not None and C in (64, 128) and H % 8 == 0 and W % 16 == 0:
         call("dcgan_c3_tconv_tc", ptr(x), ptr(w_bf16), ptr(bias), ptr(aux), ptr(out), ptr(colsum), N, H, W, C,
              ACT[act], 0 if aux is None else 1)
     else:

@@ -133,11 +133,12 @@ def test_c3_fprop(cuda_lib, tc, S, C):
     _close(out, ref, name="c3_fprop")
 
 
+@pytest.mark.parametrize("C", [64, 128])  # 128 = the wide configuration: also on the tensor cores
 @pytest.mark.parametrize("tc", [True, False])
-def test_c3_tconv_fwd_and_tanh_bwd(cuda_lib, tc):
+def test_c3_tconv_fwd_and_tanh_bwd(cuda_lib, tc, C):
     from distributed_tensorflow_for_dcgan_b200.ops import kernels as K
-    x = _rand((3, 32, 32, 64))
-    w = torch.randn(5, 5, 3, 64, device="cuda") * 0.05
+    x = _rand((3, 32, 32, C))
+    w = torch.randn(5, 5, 3, C, device="cuda") * 0.05
     wb = w.to(torch.bfloat16) if tc else None
     if tc:
         w = wb.float()
