@@ -3,14 +3,18 @@
 // batch-norm kernels (csrc/bn_act.cu).  Same arithmetic as bn_apply_kernel / bn_bwd_apply_kernel.
 //
 // Thread t of a CTA owns the 8-channel vector t % (C/8) and walks rows; rows are interleaved across CTAs in batches
-// of kTailRows per thread so that all loads of a batch are in flight together (the tensors are L2-resident).
+// of kTailRows{Fwd,Bwd} per thread so that all loads of a batch are in flight together (the tensors are L2-resident).
 // Tensors produced earlier in the same launch by other CTAs are read with ld.global.cg.
 #pragma once
 #include "common.cuh"
 
 namespace dcgan {
 
-constexpr int kTailRows = 4;
+// rows in flight per thread: at the conv kernels' occupancy (12 warps per SM) the pass is bound by memory-level
+// parallelism -- four 16-byte loads per thread kept ~3.6 MB in flight chip-wide and cost 12.7 us per layer, three
+// times a stand-alone bn_apply
+constexpr int kTailRowsFwd = 12;
+constexpr int kTailRowsBwd = 8;
 
 __device__ __forceinline__ uint4 ldcg_u4(const uint4* p) {
   uint4 v;
@@ -36,7 +40,7 @@ __device__ __forceinline__ void bn_fwd_apply_grid(const __nv_bfloat16* x, __nv_b
   const int rl = threadIdx.x / cvec;
   if (rl >= lanes) return;
   const float inv_count = 1.0f / (float)rows_per_group;
-  const int stride = gridDim.x * lanes * kTailRows;
+  const int stride = gridDim.x * lanes * kTailRowsFwd;
   for (int g = 0; g < groups; ++g) {
     float sc[8], sh[8];
 #pragma unroll
@@ -59,15 +63,15 @@ __device__ __forceinline__ void bn_fwd_apply_grid(const __nv_bfloat16* x, __nv_b
     }
     const uint4* xb = reinterpret_cast<const uint4*>(x) + (size_t)g * rows_per_group * cvec + cv;
     uint4* yb = reinterpret_cast<uint4*>(y) + (size_t)g * rows_per_group * cvec + cv;
-    for (int rb = blockIdx.x * lanes * kTailRows + rl; rb < rows_per_group; rb += stride) {
-      uint4 v[kTailRows];
+    for (int rb = blockIdx.x * lanes * kTailRowsFwd + rl; rb < rows_per_group; rb += stride) {
+      uint4 v[kTailRowsFwd];
 #pragma unroll
-      for (int u = 0; u < kTailRows; ++u) {
+      for (int u = 0; u < kTailRowsFwd; ++u) {
         const int r = rb + u * lanes;
         v[u] = r < rows_per_group ? ldcg_u4(xb + (size_t)r * cvec) : make_uint4(0, 0, 0, 0);
       }
 #pragma unroll
-      for (int u = 0; u < kTailRows; ++u) {
+      for (int u = 0; u < kTailRowsFwd; ++u) {
         const int r = rb + u * lanes;
         if (r >= rows_per_group) break;
         const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
@@ -103,7 +107,7 @@ __device__ __forceinline__ void bn_bwd_apply_grid(const __nv_bfloat16* da, const
   const int rl = threadIdx.x / cvec;
   if (rl >= lanes) return;
   const float inv_count = 1.0f / (float)rows_per_slab;
-  const int stride = gridDim.x * lanes * kTailRows;
+  const int stride = gridDim.x * lanes * kTailRowsBwd;
   const float pos = 1.f;
   const float neg = act == kActRelu ? 0.f : (act == kActLrelu ? 0.2f : 1.f);
   for (int g = 0; g < slabs; ++g) {
@@ -131,10 +135,10 @@ __device__ __forceinline__ void bn_bwd_apply_grid(const __nv_bfloat16* da, const
     const uint4* dab = reinterpret_cast<const uint4*>(da) + (size_t)g * rows_per_slab * cvec + cv;
     const uint4* prb = reinterpret_cast<const uint4*>(pre) + (size_t)sg * rows_per_slab * cvec + cv;
     uint4* dpb = reinterpret_cast<uint4*>(dpre) + (size_t)g * rows_per_slab * cvec + cv;
-    for (int rb = blockIdx.x * lanes * kTailRows + rl; rb < rows_per_slab; rb += stride) {
-      uint4 dvv[kTailRows], pvv[kTailRows];
+    for (int rb = blockIdx.x * lanes * kTailRowsBwd + rl; rb < rows_per_slab; rb += stride) {
+      uint4 dvv[kTailRowsBwd], pvv[kTailRowsBwd];
 #pragma unroll
-      for (int u = 0; u < kTailRows; ++u) {
+      for (int u = 0; u < kTailRowsBwd; ++u) {
         const int r = rb + u * lanes;
         dvv[u] = pvv[u] = make_uint4(0, 0, 0, 0);
         if (r < rows_per_slab) {
@@ -143,7 +147,7 @@ __device__ __forceinline__ void bn_bwd_apply_grid(const __nv_bfloat16* da, const
         }
       }
 #pragma unroll
-      for (int u = 0; u < kTailRows; ++u) {
+      for (int u = 0; u < kTailRowsBwd; ++u) {
         const int r = rb + u * lanes;
         if (r >= rows_per_slab) break;
         const uint32_t dw[4] = {dvv[u].x, dvv[u].y, dvv[u].z, dvv[u].w};
