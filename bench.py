@@ -358,9 +358,18 @@ def main():
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(K_steps)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(K_steps)]
     barrier()
+    # Synchronous replicas end a step together (the exchange is a barrier), so a rank whose untimed inter-step work
+    # (input copy, L2 flush) finishes EARLIER starts its next step earlier and then waits inside it: its event pair
+    # would measure the other ranks' start skew, not work (profiles/README.md: ranks 4-7 read 6 % slower in every
+    # synchronous arm while each of the eight GPUs alone runs the same 0.66 ms and the barrier-free async arm shows
+    # no such pattern).  A one-element all-reduce in front of the start event lines the ranks up on the device; it is
+    # outside the event pair and hides nothing: a genuinely slower rank still ends last and the max over ranks sees it.
+    align = torch.zeros(1, device=dev) if (world > 1 and args.mode == "sync") else None
     for i in range(K_steps):
         stage_inputs(i)
         flush.fill_(i & 0xff)
+        if align is not None:
+            dist.all_reduce(align)
         starts[i].record()
         device_step(i)
         ends[i].record()
@@ -421,6 +430,8 @@ def main():
                        "global_batch": gb, "batch_per_gpu": B, "seq_len": None, "parallelism": parallelism,
                        "update_mode": "simultaneous", "replica_mode": args.mode, "cuda_graph": bool(use_graph),
                        "l2": "flushed between timed steps (256 MiB write outside the event pairs)",
+                       "rank_alignment": ("one-element all-reduce before each start event (outside the event pair)"
+                                          if (world > 1 and args.mode == "sync") else None),
                        "step_ms_min_med_max": [round(min(per_step), 4), round(statistics.median(per_step), 4),
                                                round(max(per_step), 4)],
                        "ms_per_step_by_rank": per_rank},
