@@ -72,3 +72,53 @@ def test_optimizer_shards_tile_the_buckets():
             assert cursor == hi, (world, bucket)
             sizes = [comm.shard_range(bucket, r)[1] - comm.shard_range(bucket, r)[0] for r in range(world)]
             assert max(sizes) - min(sizes[:-1] or sizes) <= 8 or sizes[-1] <= max(sizes)   # balanced up to rounding
+
+
+def test_generator_filters_come_first_and_the_linear_last():
+    """The early generator update / exchange covers [g_h1/w, g_h0_lin/Matrix): those three filters must be contiguous at
+    the start of the arena and g_h0_lin/Matrix (whose gradient is the last kernel of the step) must follow them,
+    before the f32-consumed variables."""
+    A = ParamArena(ModelConfig(batch_size=4), "cpu")
+    o = {n: A.offsets[n][0] for n in ("g_h1/w", "g_h2/w", "g_h3/w", "g_h0_lin/Matrix")}
+    assert o["g_h1/w"] == 0 and o["g_h1/w"] < o["g_h2/w"] < o["g_h3/w"] < o["g_h0_lin/Matrix"] < A.f32_start["g"]
+    n3 = 1
+    for d in A.offsets["g_h3/w"][1]:
+        n3 *= d
+    assert o["g_h0_lin/Matrix"] == o["g_h3/w"] + n3                      # nothing between them
+    assert o["g_h0_lin/Matrix"] % 8 == 0
+    early = o["g_h0_lin/Matrix"] / A.g_end
+    assert 0.8 < early < 0.9                                               # ~85 % of the generator's parameters
+
+
+def test_three_exchange_buckets_tile_the_arena():
+    """The generator's bucket is split at g_h0_lin/Matrix; the buckets (g1, g2, d) and their per-rank shards cover
+    the padded arena exactly once, and the consumer-side pull range lies inside one bucket."""
+    from distributed_tensorflow_for_dcgan_b200.parallel.fused_comm import FusedComm
+    A = ParamArena(ModelConfig(batch_size=4), "cpu")
+    split = A.offsets["g_h0_lin/Matrix"][0]
+    for world in (2, 4, 8):
+        comm = FusedComm.__new__(FusedComm)
+        comm.world = world
+        comm.buckets = {"g1": (0, split), "g2": (split, A.g_end), "d": (A.g_end, A.padded)}
+        comm.bucket_names = tuple(comm.buckets)
+        cursor = 0
+        for b in comm.bucket_names:
+            lo, hi = comm.buckets[b]
+            assert lo == cursor and (hi - lo) % 4 == 0
+            for r in range(world):
+                s0, s1 = comm.shard_range(b, r)
+                assert s0 == cursor and (s0 - lo) % 8 == 0
+                cursor = s1
+            assert cursor == hi
+        assert cursor == A.padded
+        off, shape = A.offsets["g_h0_lin/Matrix"]
+        assert comm.buckets["g2"][0] <= off and off + shape[0] * shape[1] <= comm.buckets["g2"][1]
+
+
+def test_autotune_is_inert_without_a_gpu():
+    from distributed_tensorflow_for_dcgan_b200.ops import autotune
+    if torch.cuda.is_available():
+        pytest.skip("CPU-only check")
+    before = dict(autotune.plans())
+    autotune.ensure(autotune.KIND_F, 64, 32, 32, 64, 128)
+    assert autotune.plans() == before
