@@ -1,6 +1,7 @@
 """Layout of the flat parameter arena (engine.ParamArena) -- the contract the optimizer / communication kernels
 rely on: [G bf16-consumed | G f32-consumed | D bf16-consumed | D f32-consumed], every tensor 32-byte aligned,
 TF names and TF layouts, padded to whole 1024-element blocks."""
+import pytest
 import torch
 
 from distributed_tensorflow_for_dcgan_b200.config import ModelConfig
