@@ -15,7 +15,8 @@ for obj in sorted(os.listdir(OBJ)):
     for line in sass.splitlines():
         m = re.search(r"Function : (\S+)", line)
         if m:
-            fn = subprocess.run(["c++filt", m.group(1)], capture_output=True, text=True).stdout.strip().split("(")[0]
+            fn = subprocess.run(["c++filt", m.group(1)], capture_output=True, text=True).stdout.strip()
+            fn = fn.replace("(anonymous namespace)::", "").split("(")[0]
             counts[fn] = collections.Counter()
             continue
         m = re.match(r"\s*/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z][\w.]*)", line)
