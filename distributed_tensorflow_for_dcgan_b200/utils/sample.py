@@ -17,15 +17,13 @@ def inverse_transform(images: np.ndarray) -> np.ndarray:
 
 
 def merge(images: np.ndarray, size) -> np.ndarray:
-    """Tiles N images row-major into ``[h*size[0], w*size[1], 3]``: image idx -> column idx %
-    size[1], row idx // size[1]."""
-    h, w = images.shape[1], images.shape[2]
-    img = np.zeros((h * size[0], w * size[1], images.shape[3]))
-    for idx, image in enumerate(images):
-        i = idx % size[1]
-        j = idx // size[1]
-        img[j * h:j * h + h, i * w:i * w + w, :] = image
-    return img
+    """Tiles N images row-major into one ``[rows * h, cols * w, c]`` grid (``size = (rows, cols)``); cells beyond N stay
+    black.  One reshape / transpose instead of a per-image copy loop."""
+    rows, cols = int(size[0]), int(size[1])
+    n, h, w, c = images.shape
+    cells = np.zeros((rows * cols, h, w, c), dtype=np.float64)
+    cells[:min(n, rows * cols)] = images[:rows * cols]
+    return cells.reshape(rows, cols, h, w, c).transpose(0, 2, 1, 3, 4).reshape(rows * h, cols * w, c)
 
 
 def to_uint8_minmax(arr: np.ndarray) -> np.ndarray:
