@@ -33,11 +33,12 @@ def plans() -> Dict[Tuple[int, int, int, int, int, int], Tuple[int, int, int, fl
     return dict(_done)
 
 
-def _time_us(fn, reps: int = 6) -> float:
+def _time_us(fn, reps: int = 8) -> float:
+    """Best of three event-timed bursts after two warm-up launches (the minimum rejects interference)."""
     for _ in range(2):
         fn()
     best = float("inf")
-    for _ in range(2):
+    for _ in range(3):
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
         for _ in range(reps):
